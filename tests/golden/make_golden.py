@@ -1,0 +1,175 @@
+"""Generate the golden fixtures by running the UNMODIFIED reference (read-only import
+from /root/reference through oracle/reference_bridge.py).  Run in the build container:
+
+    python tests/golden/make_golden.py
+
+Writes tests/golden/*.npz.  Each fixture stores the seeds/config needed to regenerate
+the weights (oracle/weights.py) and inputs, the reference's outputs, and the raw
+quaternion field(s) the reference's ``rot_to_quat`` returned (its eigenvector sign is
+LAPACK-defined, SURVEY.md 0.5, so consumers replay it in 'follow' mode).
+"""
+import os
+import sys
+
+import numpy as np
+import torch
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.dirname(os.path.dirname(HERE)))
+
+from oracle import genie_oracle as O, weights as W, reference_bridge as R  # noqa: E402
+
+
+def motif_spec(n, seed):
+    """A synthetic two-segment motif for a sample of length n (masks as in
+    utils/motif_utils.py:59-129: sequence mask on motif residues, structure mask on
+    same-group motif pairs)."""
+    rng = np.random.RandomState(seed)
+    fsm = np.zeros(n, bool)
+    grp = np.zeros(n, int)
+    a0 = rng.randint(0, n // 3)
+    fsm[a0:a0 + 4] = True
+    grp[a0:a0 + 4] = 1
+    b0 = rng.randint(n // 2, n - 4)
+    fsm[b0:b0 + 3] = True
+    grp[b0:b0 + 3] = 1
+    fst = (fsm[:, None] & fsm[None, :]) & (grp[:, None] == grp[None, :])
+    aa = np.zeros((n, 20), int)
+    aa[np.arange(n), rng.randint(0, 20, n)] = 1
+    aa = aa * fsm[:, None]
+    pos = rng.randn(n, 3) * 6.0 * fsm[:, None]
+    return {'fixed_sequence_mask': fsm, 'fixed_structure_mask': fst, 'aatype': aa, 'atom_positions': pos}
+
+
+CASES = {
+    # name: (cfg overrides, chain lengths per sample, motif?, weight kind, seed, timesteps)
+    'uncond_base_ragged': (dict(), [[24], [17]], False, 'activated', 11, [777, 3]),
+    'uncond_stock': (dict(), [[16], [16]], False, 'stock_like', 12, [1000, 1]),
+    'motif_base': (dict(), [[22], [19], [24], [15]], True, 'activated', 13, [500, 500, 42, 999]),  # B != 3: cross-dim quirk
+    'triatt': (dict(include_tri_att=True, n_pair_transform_layer=2, n_structure_layer=2),
+               [[18], [12]], False, 'activated', 14, [250, 900]),
+    'multichain': (dict(n_pair_transform_layer=1, n_structure_layer=1), [[9, 7], [5, 4, 6]], False,
+                   'activated', 15, [10, 20]),
+}
+
+
+def gen_forward_case(name):
+    over, lengths, with_motif, kind, seed, tsteps = CASES[name]
+    cfg = O.OracleConfig(**over)
+    sd = W.make_state_dict(cfg, seed, kind)
+    model = R.build_denoiser(cfg, sd)
+    ns = R.load()
+    motif = [motif_spec(sum(l), seed * 100 + i) for i, l in enumerate(lengths)] if with_motif else None
+    feats = O.make_features(lengths, motif)
+    g = torch.Generator().manual_seed(seed + 1000)
+    B, N = feats['residue_mask'].shape
+    trans = torch.randn(B, N, 3, generator=g) * 4.0
+    rots = ns.compute_frenet_frames(trans, feats['chain_index'], feats['residue_mask'])
+    ts = torch.tensor(tsteps, dtype=torch.int32)
+    with torch.no_grad(), R.QuatRecorder() as rec:
+        out = model(ns.T(rots, trans), ts, feats)
+    assert len(rec.records) == 1
+    np.savez_compressed(
+        os.path.join(HERE, 'fwd_%s.npz' % name),
+        cfg_over=repr(over), lengths=repr(lengths), with_motif=with_motif, kind=kind, seed=seed,
+        weights_checksum=W.checksum(sd),
+        trans=trans.numpy(), rots=rots.numpy(), timesteps=ts.numpy(),
+        quat=rec.records[0].numpy(),
+        z=out['z'].numpy(), s=out['s'].numpy(), p=out['p'].numpy(), states=out['states'].numpy(),
+        out_trans=out['ts'].trans.numpy(), out_rots=out['ts'].rots.numpy())
+    print(name, 'z absmax', float(out['z'].abs().max()), 'p absmax', float(out['p'].abs().max()))
+
+
+def gen_primitives():
+    ns = R.load()
+    g = torch.Generator().manual_seed(5)
+    # schedule (ddpm.py:36-66) for T = 1000 and T = 50
+    d = {}
+    for T_ in (1000, 50):
+        betas = ns.cosine_beta_schedule(T_)
+        alphas = 1. - betas
+        ac = torch.cumprod(alphas, 0)
+        d['sched%d_alphas' % T_] = alphas.numpy()
+        d['sched%d_sqrt_alphas' % T_] = torch.sqrt(alphas).numpy()
+        d['sched%d_sqrt_betas' % T_] = torch.sqrt(betas).numpy()
+        d['sched%d_sqrt_one_minus_alphas_cumprod' % T_] = torch.sqrt(1. - ac).numpy()
+    # sinusoidal encodings (encoding.py:5-25) at the three call sites' (N, D)
+    v = torch.tensor([0, 1, 2, 17, 255, 256, 999, 1000], dtype=torch.int32)
+    d['enc_v'] = v.numpy()
+    d['enc_pos'] = ns.sinusoidal_encoding(v, 256, 256).numpy()
+    d['enc_chain'] = ns.sinusoidal_encoding(v, 1, 64).numpy()
+    d['enc_time'] = ns.sinusoidal_encoding(v, 1000, 512).numpy()
+    # Frenet frames (geo_utils.py:21-85) incl. multi-chain and padding; B != 3 (cross dim quirk)
+    coords = torch.randn(4, 14, 3, generator=g) * 3
+    chains = torch.zeros(4, 14, dtype=torch.int32)
+    chains[1, 6:] = 1
+    chains[2, 4:9] = 1
+    chains[2, 9:] = 2
+    mask = torch.ones(4, 14, dtype=torch.int32)
+    mask[2, 12:] = 0
+    mask[3, 5:] = 0
+    d['fr_coords'], d['fr_chains'], d['fr_mask'] = coords.numpy(), chains.numpy(), mask.numpy()
+    d['fr_rots'] = ns.compute_frenet_frames(coords, chains, mask).numpy()
+    # quaternions: |q| of rot_to_quat is sign-free; store q for follow-mode comparison
+    q = torch.randn(64, 4, generator=g)
+    q = q / q.norm(dim=-1, keepdim=True)
+    rot = ns.quat_to_rot(q)
+    d['q_in'], d['q_rot'] = q.numpy(), rot.numpy()
+    d['q_out'] = ns.rot_to_quat(rot).numpy()
+    np.savez_compressed(os.path.join(HERE, 'primitives.npz'), **d)
+    print('primitives ok')
+
+
+def gen_trajectory():
+    """BaseSampler._sample (sampler/base.py:216-289) run unmodified through
+    UnconditionalSampler with n_timestep = 6, L = 14, B = 2 and torch.randn_like inside
+    genie.sampler.base rebound to consume a seeded tape (module-attribute patch)."""
+    ns = R.load()
+    from genie.config import Config
+    from genie.diffusion.genie import Genie
+    from genie.sampler.unconditional import UnconditionalSampler
+    import genie.sampler.base as base
+    T_, L, B, seed, scale = 6, 14, 2, 21, 0.6
+    cfg = O.OracleConfig(n_timestep=T_, n_pair_transform_layer=2, n_structure_layer=3)
+    sd = W.make_state_dict(cfg, seed, 'activated')
+    config = Config(os.path.join(R.REFERENCE_ROOT, 'results/base/configuration'))
+    config.diffusion['n_timestep'] = T_
+    config.model['n_pair_transform_layer'] = 2
+    config.model['n_structure_layer'] = 3
+    genie = Genie(config).eval()
+    genie.model.load_state_dict(sd)
+    sampler = UnconditionalSampler(genie)
+    g = torch.Generator().manual_seed(seed + 1)
+    tape = torch.randn(T_ + 1, B, L, 3, generator=g)          # tape[T] = x_T, tape[t] (t>=2) = noise at step t
+    draws = [tape[T_]] + [tape[t] for t in range(T_, 1, -1)]
+
+    class FakeTorch:
+        def __getattr__(self, k):
+            return getattr(torch, k)
+
+        def randn_like(self, x):
+            return draws.pop(0).to(x.dtype)
+
+    orig = base.torch
+    base.torch = FakeTorch()
+    try:
+        with R.QuatRecorder() as rec:
+            out = sampler._sample({'length': L, 'scale': scale, 'num_samples': B, 'outdir': '/tmp/_g',
+                                   'prefix': 'x', 'offset': 0})
+    finally:
+        base.torch = orig
+    assert not draws and len(rec.records) == T_
+    final = np.stack([o['atom_positions'] for o in out])
+    np.savez_compressed(
+        os.path.join(HERE, 'traj_uncond.npz'), T=T_, L=L, B=B, seed=seed, scale=scale,
+        weights_checksum=W.checksum(sd), tape=tape.numpy(),
+        quats=torch.stack(rec.records).numpy(), final=final.astype(np.float32))
+    print('traj ok', np.abs(final).max())
+
+
+if __name__ == '__main__':
+    torch.set_num_threads(8)
+    gen_primitives()
+    for c in CASES:
+        gen_forward_case(c)
+    gen_trajectory()
