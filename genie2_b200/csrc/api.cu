@@ -1,0 +1,744 @@
+// C ABI of genie2_b200 (include/genie2_b200.h): context, weight packing, feature binding and
+// the orchestration of Denoiser.forward / the reverse-diffusion step as a fixed kernel sequence.
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <cmath>
+
+#include "ctx.h"
+#include "gemm_simt.cuh"
+#include "kernels_embed.cuh"
+#include "kernels_frames.cuh"
+#include "kernels_pair_simt.cuh"
+#include "kernels_structure.cuh"
+#include "kernels_triatt.cuh"
+#include "tc_api.h"
+
+static std::string g_create_err;
+
+int gb_fail(const gb_ctx* ctx, int code, const char* fmt, ...) {
+  char buf[1024];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof buf, fmt, ap);
+  va_end(ap);
+  if (ctx) ctx->err = buf; else g_create_err = buf;
+  return code;
+}
+
+extern "C" int gb_version(void) { return GB_VERSION; }
+extern "C" const char* gb_last_error(const gb_ctx* ctx) { return ctx ? ctx->err.c_str() : g_create_err.c_str(); }
+extern "C" int64_t gb_launch_count(const gb_ctx* ctx) { return ctx ? ctx->launches : 0; }
+extern "C" int64_t gb_workspace_bytes(const gb_ctx* ctx) { return ctx ? (int64_t)ctx->ws_bytes : 0; }
+
+static const int kSmemPair = (PS_A_FLOATS + PS_W_FLOATS) * 4;
+static const int kSmemTrans = (PS_A_FLOATS + PS_W_FLOATS + PS_A_FLOATS) * 4;
+
+extern "C" int gb_create(gb_ctx** out, const gb_dims* d, int device) {
+  if (!out || !d) return gb_fail(nullptr, GB_ERR_INVALID, "gb_create: NULL argument");
+  *out = nullptr;
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+    return gb_fail(nullptr, GB_ERR_CUDA, "gb_create: no CUDA device (this library has no CPU path)");
+  if (device < 0 || device >= ndev) return gb_fail(nullptr, GB_ERR_INVALID, "gb_create: bad device %d", device);
+  cudaDeviceProp prop;
+  if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) return gb_fail(nullptr, GB_ERR_CUDA, "gb_create: cudaGetDeviceProperties failed");
+  if (prop.major != 10)
+    return gb_fail(nullptr, GB_ERR_UNSUPPORTED, "gb_create: device %d is sm_%d%d; this build targets sm_100a (B200) only",
+                   device, prop.major, prop.minor);
+  // compiled specialisations (SURVEY.md section 5 "Config / flags")
+  if (d->c_p != 128 || d->c_hidden_mul != 128) return gb_fail(nullptr, GB_ERR_UNSUPPORTED, "c_p and c_hidden_mul must be 128");
+  if (d->n_head_ipa != IPA_H || d->c_hidden_ipa != IPA_C || d->n_qk_point != IPA_PQ || d->n_v_point != IPA_PV)
+    return gb_fail(nullptr, GB_ERR_UNSUPPORTED, "IPA geometry must be H=12, C=16, Pq=4, Pv=8");
+  if (d->template_dist_n_bin != 37) return gb_fail(nullptr, GB_ERR_UNSUPPORTED, "template_dist_n_bin must be 37");
+  if (d->pair_transition_n < 1 || d->pair_transition_n > 8) return gb_fail(nullptr, GB_ERR_UNSUPPORTED, "pair_transition_n out of range");
+  if (d->include_tri_att && (d->n_head_tri != TA_H || d->c_hidden_tri_att != TA_C))
+    return gb_fail(nullptr, GB_ERR_UNSUPPORTED, "triangle attention must be 4 heads x 32");
+  if (d->c_s % 4 != 0 || d->c_s > 1024) return gb_fail(nullptr, GB_ERR_UNSUPPORTED, "c_s must be a multiple of 4, <= 1024");
+  if (d->rescale == 0.f) return gb_fail(nullptr, GB_ERR_INVALID, "rescale must be non-zero");
+  if (cudaSetDevice(device) != cudaSuccess) return gb_fail(nullptr, GB_ERR_CUDA, "cudaSetDevice failed");
+  gb_ctx* c = new gb_ctx();
+  c->d = *d;
+  c->device = device;
+  // opt in to > 48 KB dynamic shared memory
+  cudaFuncSetAttribute(trimul_proj_simt_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemPair);
+  cudaFuncSetAttribute(trimul_out_simt_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemPair);
+  cudaFuncSetAttribute(pair_transition_simt_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemTrans);
+  cudaFuncSetAttribute(ipa_attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+  cudaFuncSetAttribute(frenet_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+  cudaFuncSetAttribute(ddpm_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+  triatt_set_attributes();
+  if (cudaGetLastError() != cudaSuccess) { delete c; return gb_fail(nullptr, GB_ERR_CUDA, "cudaFuncSetAttribute failed"); }
+  int rc = tc_init(c);
+  if (rc != GB_OK) { g_create_err = c->err; delete c; return rc; }
+  *out = c;
+  return GB_OK;
+}
+
+static void free_features(gb_ctx* c) {
+  if (c->feat_alloc) cudaFree(c->feat_alloc);
+  if (c->ws_alloc) cudaFree(c->ws_alloc);
+  c->feat_alloc = c->ws_alloc = nullptr;
+  c->features_set = false;
+}
+
+extern "C" void gb_destroy(gb_ctx* c) {
+  if (!c) return;
+  cudaSetDevice(c->device);
+  tc_destroy(c);
+  free_features(c);
+  if (c->tape_alloc) cudaFree(c->tape_alloc);
+  if (c->alphas) cudaFree(c->alphas);
+  for (void* p : c->weight_allocs) cudaFree(p);
+  delete c;
+}
+
+// ------------------------------------------------------------------ weight helpers
+static float* upload(gb_ctx* c, const std::vector<float>& v) {
+  void* p = nullptr;
+  if (cudaMalloc(&p, v.size() * sizeof(float)) != cudaSuccess) return nullptr;
+  if (cudaMemcpy(p, v.data(), v.size() * sizeof(float), cudaMemcpyHostToDevice) != cudaSuccess) { cudaFree(p); return nullptr; }
+  c->weight_allocs.push_back(p);
+  return (float*)p;
+}
+
+struct Getter {
+  gb_ctx* c;
+  bool ok = true;
+  std::string missing;
+  const std::vector<float>& get(const std::string& name, std::initializer_list<int64_t> shape) {
+    static std::vector<float> empty;
+    auto it = c->host.find(name);
+    if (it == c->host.end()) { if (ok) missing = name; ok = false; return empty; }
+    size_t n = 1, k = 0;
+    bool same = it->second.shape.size() == shape.size();
+    for (int64_t s : shape) { n *= (size_t)s; if (same && it->second.shape[k] != s) same = false; ++k; }
+    if (!same || it->second.v.size() != n) { if (ok) missing = name + " (shape mismatch)"; ok = false; return empty; }
+    return it->second.v;
+  }
+};
+
+// dst[k][n] = src[n][k]   src [rows n][cols k]
+static std::vector<float> transpose(const std::vector<float>& src, int rows, int cols) {
+  std::vector<float> d((size_t)rows * cols);
+  if (src.empty()) return d;
+  for (int n = 0; n < rows; ++n)
+    for (int k = 0; k < cols; ++k) d[(size_t)k * rows + n] = src[(size_t)n * cols + k];
+  return d;
+}
+static std::vector<float> concat(std::initializer_list<const std::vector<float>*> parts) {
+  std::vector<float> d;
+  for (auto* p : parts) d.insert(d.end(), p->begin(), p->end());
+  return d;
+}
+
+static int pack_trimul(gb_ctx* c, Getter& G, const std::string& pre, TriMulW& w) {
+  const auto& ap = G.get(pre + ".linear_a_p.weight", {128, 128});
+  const auto& ag = G.get(pre + ".linear_a_g.weight", {128, 128});
+  const auto& bp = G.get(pre + ".linear_b_p.weight", {128, 128});
+  const auto& bg = G.get(pre + ".linear_b_g.weight", {128, 128});
+  const auto& lg = G.get(pre + ".linear_g.weight", {128, 128});
+  const auto& lz = G.get(pre + ".linear_z.weight", {128, 128});
+  const auto& apb = G.get(pre + ".linear_a_p.bias", {128});
+  const auto& agb = G.get(pre + ".linear_a_g.bias", {128});
+  const auto& bpb = G.get(pre + ".linear_b_p.bias", {128});
+  const auto& bgb = G.get(pre + ".linear_b_g.bias", {128});
+  const auto& lgb = G.get(pre + ".linear_g.bias", {128});
+  const auto& lzb = G.get(pre + ".linear_z.bias", {128});
+  const auto& lig = G.get(pre + ".layer_norm_in.weight", {128});
+  const auto& lib = G.get(pre + ".layer_norm_in.bias", {128});
+  const auto& log_ = G.get(pre + ".layer_norm_out.weight", {128});
+  const auto& lob = G.get(pre + ".layer_norm_out.bias", {128});
+  if (!G.ok) return GB_ERR_MISSING;
+  std::vector<float> Wpk(5 * 128 * 128), bpk(5 * 128);
+  for (int t = 0; t < 5; ++t)
+    for (int n = 0; n < 128; ++n) {
+      const std::vector<float>* W;
+      const std::vector<float>* bsrc;
+      int row;
+      if (t == 4) { W = &lg; bsrc = &lgb; row = n; }
+      else {
+        const int c0 = (t & 1) * 64;
+        const bool gate = n >= 64;
+        row = c0 + (n & 63);
+        W = (t < 2) ? (gate ? &ag : &ap) : (gate ? &bg : &bp);
+        bsrc = (t < 2) ? (gate ? &agb : &apb) : (gate ? &bgb : &bpb);
+      }
+      bpk[t * 128 + n] = (*bsrc)[row];
+      for (int k = 0; k < 128; ++k) Wpk[((size_t)t * 128 + k) * 128 + n] = (*W)[(size_t)row * 128 + k];
+    }
+  w.Wpk = upload(c, Wpk); w.bpk = upload(c, bpk);
+  w.WzT = upload(c, transpose(lz, 128, 128)); w.bz = upload(c, lzb);
+  w.ln_in_g = upload(c, lig); w.ln_in_b = upload(c, lib);
+  w.ln_out_g = upload(c, log_); w.ln_out_b = upload(c, lob);
+  return tc_pack_trimul(c, w, ap, ag, bp, bg, lg, lz, apb, agb, bpb, bgb, lgb);
+}
+
+static int pack_transition(gb_ctx* c, Getter& G, const std::string& pre, TransitionW& w) {
+  const int nh = c->d.pair_transition_n;
+  const auto& w1 = G.get(pre + ".linear_1.weight", {128 * nh, 128});
+  const auto& b1 = G.get(pre + ".linear_1.bias", {128 * nh});
+  const auto& w2 = G.get(pre + ".linear_2.weight", {128, 128 * nh});
+  const auto& b2 = G.get(pre + ".linear_2.bias", {128});
+  const auto& lg = G.get(pre + ".layer_norm.weight", {128});
+  const auto& lb = G.get(pre + ".layer_norm.bias", {128});
+  if (!G.ok) return GB_ERR_MISSING;
+  std::vector<float> W1T((size_t)nh * 128 * 128), W2T((size_t)nh * 128 * 128);
+  for (int t = 0; t < nh; ++t)
+    for (int k = 0; k < 128; ++k)
+      for (int n = 0; n < 128; ++n) {
+        W1T[((size_t)t * 128 + k) * 128 + n] = w1[((size_t)t * 128 + n) * 128 + k];        // hidden col n of tile t
+        W2T[((size_t)t * 128 + k) * 128 + n] = w2[(size_t)n * (128 * nh) + t * 128 + k];    // k = hidden idx in tile
+      }
+  w.W1T = upload(c, W1T); w.b1 = upload(c, b1); w.W2T = upload(c, W2T); w.b2 = upload(c, b2);
+  w.ln_g = upload(c, lg); w.ln_b = upload(c, lb);
+  return tc_pack_transition(c, w, w1, w2);
+}
+
+static int pack_triatt(gb_ctx* c, Getter& G, const std::string& pre, TriAttW& w) {
+  const int hc = TA_H * TA_C;
+  const auto& lg = G.get(pre + ".layer_norm.weight", {128});
+  const auto& lb = G.get(pre + ".layer_norm.bias", {128});
+  const auto& wl = G.get(pre + ".linear.weight", {TA_H, 128});
+  const auto& wq = G.get(pre + ".mha.linear_q.weight", {hc, 128});
+  const auto& wk = G.get(pre + ".mha.linear_k.weight", {hc, 128});
+  const auto& wv = G.get(pre + ".mha.linear_v.weight", {hc, 128});
+  const auto& wg = G.get(pre + ".mha.linear_g.weight", {hc, 128});
+  const auto& bg = G.get(pre + ".mha.linear_g.bias", {hc});
+  const auto& wo = G.get(pre + ".mha.linear_o.weight", {128, hc});
+  const auto& bo = G.get(pre + ".mha.linear_o.bias", {128});
+  if (!G.ok) return GB_ERR_MISSING;
+  w.ln_g = upload(c, lg); w.ln_b = upload(c, lb); w.Wbias = upload(c, wl);
+  w.Wqkvg = upload(c, concat({&wq, &wk, &wv, &wg})); w.bg = upload(c, bg);
+  w.Wo = upload(c, wo); w.bo = upload(c, bo);
+  return GB_OK;
+}
+
+extern "C" int gb_load_weights(gb_ctx* c, const gb_tensor* tensors, int n) {
+  if (!c || !tensors || n <= 0) return gb_fail(c, GB_ERR_INVALID, "gb_load_weights: bad arguments");
+  GB_CUDA(c, cudaSetDevice(c->device));
+  for (void* p : c->weight_allocs) cudaFree(p);
+  c->weight_allocs.clear();
+  c->host.clear();
+  c->weights_loaded = false;
+  for (int i = 0; i < n; ++i) {
+    const gb_tensor& t = tensors[i];
+    if (!t.name || !t.data || t.ndim < 1 || t.ndim > 4) return gb_fail(c, GB_ERR_INVALID, "gb_load_weights: tensor %d malformed", i);
+    std::string name = t.name;
+    if (name.compare(0, 6, "model.") == 0) name = name.substr(6);   // Lightning prefix (ddpm.py:26)
+    HostTensor h;
+    size_t cnt = 1;
+    for (int k = 0; k < t.ndim; ++k) { h.shape.push_back(t.shape[k]); cnt *= (size_t)t.shape[k]; }
+    h.v.resize(cnt);
+    GB_CUDA(c, cudaMemcpy(h.v.data(), t.data, cnt * sizeof(float), cudaMemcpyDefault));
+    c->host[name] = std::move(h);
+  }
+  const gb_dims& d = c->d;
+  Getter G{c};
+  const int c_s = d.c_s, F = d.c_pos_emb + d.c_chain_emb + d.c_timestep_emb + 23;
+  // ---- single feature net: raw weight + timestep table W_time . enc(t)
+  const auto& ws = G.get("single_feature_net.linear.weight", {c_s, F});
+  const auto& wi = G.get("pair_feature_net.linear_s_p_i.weight", {128, c_s});
+  const auto& wj = G.get("pair_feature_net.linear_s_p_j.weight", {128, c_s});
+  const auto& wr = G.get("pair_feature_net.linear_relpos.weight", {128, 2 * d.relpos_k + 3});
+  const auto& wt = G.get("pair_feature_net.linear_template.weight", {128, d.template_dist_n_bin + 6});
+  const auto& wm = G.get("pair_feature_net.linear_motif_template.weight", {128, d.template_dist_n_bin + 2});
+  if (!G.ok) return gb_fail(c, GB_ERR_MISSING, "gb_load_weights: missing tensor %s", G.missing.c_str());
+  c->W_single = upload(c, ws);
+  c->W_pipj = upload(c, concat({&wi, &wj}));
+  c->WrelT = upload(c, transpose(wr, 128, 2 * d.relpos_k + 3));
+  c->WtT = upload(c, transpose(wt, 128, d.template_dist_n_bin + 6));
+  c->WmT = upload(c, transpose(wm, 128, d.template_dist_n_bin + 2));
+  {
+    const int T1 = d.n_timestep + 1, D = d.c_timestep_emb;
+    float* X = nullptr;
+    GB_CUDA(c, cudaMalloc(&X, (size_t)T1 * D * sizeof(float)));
+    void* tt = nullptr;
+    if (cudaMalloc(&tt, (size_t)T1 * c_s * sizeof(float)) != cudaSuccess) { cudaFree(X); return gb_fail(c, GB_ERR_CUDA, "cudaMalloc time table"); }
+    c->weight_allocs.push_back(tt);
+    c->time_table = (float*)tt;
+    time_encoding_kernel<<<(T1 * D + 255) / 256, 256>>>(X, T1, d.n_timestep, D);
+    sgemm_nt(0, X, D, c->W_single + d.c_pos_emb + d.c_chain_emb, F, nullptr, nullptr, 0, c->time_table, c_s, T1, c_s, D, false);
+    cudaError_t e = cudaDeviceSynchronize();
+    cudaFree(X);
+    if (e != cudaSuccess) return gb_fail(c, GB_ERR_CUDA, "time table kernels failed: %s", cudaGetErrorString(e));
+  }
+  // ---- pair transform layers
+  c->pair.assign(d.n_pair_transform_layer, PairLayerW());
+  for (int l = 0; l < d.n_pair_transform_layer; ++l) {
+    const std::string pre = "pair_transform_net.net." + std::to_string(l);
+    int rc = GB_OK;
+    if (d.include_mul_update) {
+      rc = pack_trimul(c, G, pre + ".tri_mul_out", c->pair[l].mul_out);
+      if (rc == GB_OK) rc = pack_trimul(c, G, pre + ".tri_mul_in", c->pair[l].mul_in);
+    }
+    if (rc == GB_OK && d.include_tri_att) {
+      rc = pack_triatt(c, G, pre + ".tri_att_start", c->pair[l].att_start);
+      if (rc == GB_OK) rc = pack_triatt(c, G, pre + ".tri_att_end", c->pair[l].att_end);
+    }
+    if (rc == GB_OK) rc = pack_transition(c, G, pre + ".pair_transition", c->pair[l].tr);
+    if (rc == GB_ERR_MISSING) return gb_fail(c, rc, "gb_load_weights: missing tensor %s", G.missing.c_str());
+    if (rc != GB_OK) return rc;
+  }
+  // ---- structure layers
+  c->st.assign(d.n_structure_layer, StructLayerW());
+  const int H = IPA_H, hc = IPA_H * IPA_C;
+  for (int l = 0; l < d.n_structure_layer; ++l) {
+    const std::string pre = "structure_net.net." + std::to_string(l);
+    StructLayerW& w = c->st[l];
+    const auto& wq = G.get(pre + ".ipa.linear_q.weight", {hc, c_s});
+    const auto& wkv = G.get(pre + ".ipa.linear_kv.weight", {2 * hc, c_s});
+    const auto& wqp = G.get(pre + ".ipa.linear_q_points.weight", {H * IPA_PQ * 3, c_s});
+    const auto& wkvp = G.get(pre + ".ipa.linear_kv_points.weight", {H * (IPA_PQ + IPA_PV) * 3, c_s});
+    const auto& bq = G.get(pre + ".ipa.linear_q.bias", {hc});
+    const auto& bkv = G.get(pre + ".ipa.linear_kv.bias", {2 * hc});
+    const auto& bqp = G.get(pre + ".ipa.linear_q_points.bias", {H * IPA_PQ * 3});
+    const auto& bkvp = G.get(pre + ".ipa.linear_kv_points.bias", {H * (IPA_PQ + IPA_PV) * 3});
+    const auto& wb = G.get(pre + ".ipa.linear_b.weight", {H, 128});
+    const auto& bb = G.get(pre + ".ipa.linear_b.bias", {H});
+    const auto& hwt = G.get(pre + ".ipa.head_weights", {H});
+    const auto& wo = G.get(pre + ".ipa.linear_out.weight", {c_s, IPA_CAT});
+    const auto& bo = G.get(pre + ".ipa.linear_out.bias", {c_s});
+    const auto& l1g = G.get(pre + ".ipa_layer_norm.weight", {c_s});
+    const auto& l1b = G.get(pre + ".ipa_layer_norm.bias", {c_s});
+    const auto& l2g = G.get(pre + ".transition.layer_norm.weight", {c_s});
+    const auto& l2b = G.get(pre + ".transition.layer_norm.bias", {c_s});
+    const auto& wbb = G.get(pre + ".bb_update.linear.weight", {6, c_s});
+    const auto& bbb = G.get(pre + ".bb_update.linear.bias", {6});
+    if (!G.ok) return gb_fail(c, GB_ERR_MISSING, "gb_load_weights: missing tensor %s", G.missing.c_str());
+    w.Wqkv = upload(c, concat({&wq, &wkv, &wqp, &wkvp}));
+    w.bqkv = upload(c, concat({&bq, &bkv, &bqp, &bkvp}));
+    w.Wb = upload(c, wb); w.bb = upload(c, bb);
+    std::vector<float> hw(H);
+    for (int h = 0; h < H; ++h) {
+      const float xh = hwt[h];
+      const float sp = (xh > 20.f) ? xh : log1pf(expf(xh));                       // nn.Softplus
+      hw[h] = sp * sqrtf(1.f / (3.f * ((float)IPA_PQ * 9.f / 2.f)));             // invariant_point_attention.py:197-200
+    }
+    w.hw = upload(c, hw);
+    w.Wout = upload(c, wo); w.bout = upload(c, bo);
+    w.ln1_g = upload(c, l1g); w.ln1_b = upload(c, l1b); w.ln2_g = upload(c, l2g); w.ln2_b = upload(c, l2b);
+    w.Wbb = upload(c, wbb); w.bbb = upload(c, bbb);
+    for (int t = 0; t < d.n_structure_transition_layer; ++t) {
+      const std::string q = pre + ".transition.layers." + std::to_string(t);
+      const auto& a1 = G.get(q + ".linear_1.weight", {c_s, c_s});
+      const auto& c1 = G.get(q + ".linear_1.bias", {c_s});
+      const auto& a2 = G.get(q + ".linear_2.weight", {c_s, c_s});
+      const auto& c2 = G.get(q + ".linear_2.bias", {c_s});
+      const auto& a3 = G.get(q + ".linear_3.weight", {c_s, c_s});
+      const auto& c3 = G.get(q + ".linear_3.bias", {c_s});
+      if (!G.ok) return gb_fail(c, GB_ERR_MISSING, "gb_load_weights: missing tensor %s", G.missing.c_str());
+      w.W1.push_back(upload(c, a1)); w.b1.push_back(upload(c, c1));
+      w.W2.push_back(upload(c, a2)); w.b2.push_back(upload(c, c2));
+      w.W3.push_back(upload(c, a3)); w.b3.push_back(upload(c, c3));
+    }
+  }
+  for (void* p : c->weight_allocs) if (!p) return gb_fail(c, GB_ERR_CUDA, "gb_load_weights: device allocation failed");
+  c->host.clear();
+  c->weights_loaded = true;
+  return GB_OK;
+}
+
+extern "C" int gb_set_schedule(gb_ctx* c, const float* alphas, const float* sqrt_alphas, const float* sqrt_omac,
+                               const float* sqrt_betas) {
+  if (!c || !alphas || !sqrt_alphas || !sqrt_omac || !sqrt_betas) return gb_fail(c, GB_ERR_INVALID, "gb_set_schedule: NULL argument");
+  GB_CUDA(c, cudaSetDevice(c->device));
+  const size_t n = (size_t)c->d.n_timestep + 1;
+  if (!c->alphas) {
+    float* base = nullptr;
+    GB_CUDA(c, cudaMalloc(&base, 4 * n * sizeof(float)));
+    c->alphas = base; c->sqrt_alphas = base + n; c->sqrt_omac = base + 2 * n; c->sqrt_betas = base + 3 * n;
+  }
+  GB_CUDA(c, cudaMemcpy(c->alphas, alphas, n * sizeof(float), cudaMemcpyDefault));
+  GB_CUDA(c, cudaMemcpy(c->sqrt_alphas, sqrt_alphas, n * sizeof(float), cudaMemcpyDefault));
+  GB_CUDA(c, cudaMemcpy(c->sqrt_omac, sqrt_omac, n * sizeof(float), cudaMemcpyDefault));
+  GB_CUDA(c, cudaMemcpy(c->sqrt_betas, sqrt_betas, n * sizeof(float), cudaMemcpyDefault));
+  c->schedule_set = true;
+  return GB_OK;
+}
+
+extern "C" int gb_set_precision(gb_ctx* c, int precision) {
+  if (!c) return GB_ERR_INVALID;
+  if (precision != GB_PREC_FP32 && precision != GB_PREC_TF32 && precision != GB_PREC_BF16)
+    return gb_fail(c, GB_ERR_INVALID, "gb_set_precision: unknown precision %d", precision);
+  c->precision = precision;
+  return GB_OK;
+}
+
+// ------------------------------------------------------------------ features + workspace
+struct Carver {
+  char* base;
+  size_t off = 0;
+  template <typename T> T* take(size_t n) {
+    off = (off + 255) & ~(size_t)255;
+    T* p = base ? reinterpret_cast<T*>(base + off) : nullptr;
+    off += n * sizeof(T);
+    return p;
+  }
+};
+
+static void carve_features(gb_ctx* c, Carver& k, int B, int N) {
+  const size_t R = (size_t)B * N;
+  c->residue_index = k.take<int>(R);
+  c->chain_index = k.take<int>(R);
+  c->mask = k.take<int>(R);
+  c->aatype = k.take<int>(R * 20);
+  c->fsm = k.take<uint8_t>(R);
+  c->iface = k.take<uint8_t>(R);
+  c->fst = k.take<uint8_t>(R * N);
+  c->motif_pos = k.take<float>(R * 3);
+  c->s_static = k.take<float>(R * c->d.c_s);
+}
+
+static void carve_workspace(gb_ctx* c, Carver& k, int B, int N) {
+  const size_t R = (size_t)B * N, M = R * N, cs = c->d.c_s;
+  c->s = k.take<float>(R * cs);
+  c->sA = k.take<float>(R * cs);
+  c->sB = k.take<float>(R * cs);
+  c->h1 = k.take<float>(R * cs);
+  c->h2 = k.take<float>(R * cs);
+  c->pipj = k.take<float>(R * 256);
+  c->qkv = k.take<float>(R * IPA_QKV);
+  c->cat = k.take<float>(R * IPA_CAT);
+  c->rots_w = k.take<float>(R * 9);
+  c->trans_w = k.take<float>(R * 3);
+  c->z = k.take<float>(R * 3);
+  c->trans_io = k.take<float>(R * 3);
+  c->rots_io = k.take<float>(R * 9);
+  c->t_dev = k.take<int>(B);
+  c->p = k.take<float>(M * 128);
+  c->a = k.take<float>(M * 128);
+  c->b = k.take<float>(M * 128);
+  c->x = k.take<float>(M * 128);
+  c->g = k.take<float>(M * 128);
+}
+
+extern "C" int gb_set_features(gb_ctx* c, const gb_features* f) {
+  if (!c || !f) return gb_fail(c, GB_ERR_INVALID, "gb_set_features: NULL argument");
+  if (!c->weights_loaded) return gb_fail(c, GB_ERR_INVALID, "gb_set_features: call gb_load_weights first");
+  if (f->B < 1 || f->N < 3) return gb_fail(c, GB_ERR_INVALID, "gb_set_features: need B >= 1 and N >= 3 (got %d, %d)", f->B, f->N);
+  if (!f->residue_index || !f->chain_index || !f->residue_mask || !f->fixed_sequence_mask || !f->fixed_structure_mask ||
+      !f->interface_mask || !f->aatype || !f->atom_positions)
+    return gb_fail(c, GB_ERR_INVALID, "gb_set_features: NULL feature pointer");
+  if ((size_t)f->N * 13 * 4 + 64 > 200 * 1024) return gb_fail(c, GB_ERR_UNSUPPORTED, "N = %d too large for the frame kernels", f->N);
+  GB_CUDA(c, cudaSetDevice(c->device));
+  const int B = f->B, N = f->N;
+  if (!c->features_set || B != c->B || N != c->N) {
+    GB_CUDA(c, cudaDeviceSynchronize());
+    free_features(c);
+    Carver kf{nullptr}, kw{nullptr};
+    carve_features(c, kf, B, N);
+    carve_workspace(c, kw, B, N);
+    const size_t tcb = tc_workspace_bytes(c, B, N);
+    GB_CUDA(c, cudaMalloc(&c->feat_alloc, kf.off + 256));
+    cudaError_t e = cudaMalloc(&c->ws_alloc, kw.off + 512 + tcb);
+    if (e != cudaSuccess) {
+      cudaFree(c->feat_alloc); c->feat_alloc = nullptr;
+      return gb_fail(c, GB_ERR_CUDA, "workspace allocation of %zu bytes failed: %s", kw.off + tcb, cudaGetErrorString(e));
+    }
+    c->ws_bytes = kf.off + kw.off + tcb + 768;
+    Carver kf2{(char*)c->feat_alloc}, kw2{(char*)c->ws_alloc};
+    carve_features(c, kf2, B, N);
+    carve_workspace(c, kw2, B, N);
+    kw2.off = (kw2.off + 255) & ~(size_t)255;
+    int rc = tc_bind_workspace(c, (char*)c->ws_alloc + kw2.off, tcb);
+    if (rc != GB_OK) return rc;
+    c->B = B; c->N = N;
+  }
+  const size_t R = (size_t)B * N;
+  GB_CUDA(c, cudaMemcpy(c->residue_index, f->residue_index, R * 4, cudaMemcpyDefault));
+  GB_CUDA(c, cudaMemcpy(c->chain_index, f->chain_index, R * 4, cudaMemcpyDefault));
+  GB_CUDA(c, cudaMemcpy(c->mask, f->residue_mask, R * 4, cudaMemcpyDefault));
+  GB_CUDA(c, cudaMemcpy(c->aatype, f->aatype, R * 20 * 4, cudaMemcpyDefault));
+  GB_CUDA(c, cudaMemcpy(c->fsm, f->fixed_sequence_mask, R, cudaMemcpyDefault));
+  GB_CUDA(c, cudaMemcpy(c->iface, f->interface_mask, R, cudaMemcpyDefault));
+  GB_CUDA(c, cudaMemcpy(c->fst, f->fixed_structure_mask, R * N, cudaMemcpyDefault));
+  GB_CUDA(c, cudaMemcpy(c->motif_pos, f->atom_positions, R * 3 * 4, cudaMemcpyDefault));
+  // has_motif: any fixed_structure_mask bit set (host check on a copy; once per batch)
+  {
+    std::vector<uint8_t> h(R * N);
+    GB_CUDA(c, cudaMemcpy(h.data(), c->fst, R * N, cudaMemcpyDeviceToHost));
+    c->has_motif = 0;
+    for (uint8_t v : h) if (v) { c->has_motif = 1; break; }
+  }
+  // step-invariant part of SingleFeatureNet: s_static = W[:, non-time columns] . features
+  const gb_dims& d = c->d;
+  const int Fs = d.c_pos_emb + d.c_chain_emb + 23, F = Fs + d.c_timestep_emb;
+  float* X = nullptr;
+  GB_CUDA(c, cudaMalloc(&X, R * Fs * sizeof(float)));
+  single_static_features_kernel<<<(unsigned)((R * Fs + 255) / 256), 256>>>(X, c->residue_index, c->chain_index, c->aatype, c->fsm,
+                                                                            c->iface, (int)R, d.c_pos_emb, d.c_chain_emb,
+                                                                            d.max_n_res, d.max_n_chain);
+  // two GEMMs over the two non-time column blocks of W [c_s][F]: [0, c_pos+c_chain) and [F-23, F)
+  const int K1 = d.c_pos_emb + d.c_chain_emb;
+  sgemm_nt(0, X, Fs, c->W_single, F, nullptr, nullptr, 0, c->s_static, d.c_s, (int)R, d.c_s, K1, false);
+  sgemm_nt(0, X + K1, Fs, c->W_single + K1 + d.c_timestep_emb, F, nullptr, c->s_static, d.c_s, c->s_static, d.c_s, (int)R,
+           d.c_s, 23, false);
+  cudaError_t e = cudaDeviceSynchronize();
+  cudaFree(X);
+  if (e != cudaSuccess) return gb_fail(c, GB_ERR_CUDA, "static embedding kernels failed: %s", cudaGetErrorString(e));
+  c->launches += 3;
+  c->features_set = true;
+  return GB_OK;
+}
+
+// ------------------------------------------------------------------ small orchestration kernels
+__global__ void init_frames_kernel(const float* __restrict__ rots, const float* __restrict__ trans, float* rots_w,
+                                   float* trans_w, float rescale, int rows) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < rows * 9) rots_w[i] = rots[i];
+  if (i < rows * 3) trans_w[i] = trans[i] * rescale;
+}
+// z = trans - trans_w * (1/rescale)  (model.py:184-187); optional copies of the final frames
+__global__ void finish_kernel(const float* __restrict__ trans, const float* __restrict__ trans_w,
+                              const float* __restrict__ rots_w, float* __restrict__ z, float* out_trans,
+                              float* out_rots, float inv_rescale, int rows) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < rows * 3) {
+    const float t = trans_w[i] * inv_rescale;
+    z[i] = trans[i] - t;
+    if (out_trans) out_trans[i] = t;
+  }
+  if (out_rots && i < rows * 9) out_rots[i] = rots_w[i];
+}
+__global__ void fill_int_kernel(int* p, int v, int n) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) p[i] = v;
+}
+
+static int check_ready(gb_ctx* c, const char* who) {
+  if (!c) return GB_ERR_INVALID;
+  if (!c->weights_loaded) return gb_fail(c, GB_ERR_INVALID, "%s: weights not loaded", who);
+  if (!c->features_set) return gb_fail(c, GB_ERR_INVALID, "%s: features not bound (gb_set_features)", who);
+  return GB_OK;
+}
+
+static int run_trimul(gb_ctx* c, const TriMulW& w, bool outgoing, float* p, cudaStream_t st) {
+  if (c->precision != GB_PREC_FP32) return tc_trimul(c, w, outgoing, p, st);
+  const int B = c->B, N = c->N;
+  const size_t M = (size_t)B * N * N;
+  const unsigned tiles = (unsigned)((M + 127) / 128);
+  trimul_proj_simt_kernel<<<tiles, 256, kSmemPair, st>>>(p, M, N, c->mask, w.ln_in_g, w.ln_in_b, w.Wpk, w.bpk, c->a, c->b, c->g);
+  GB_LAUNCH_CHECK(c, "trimul_proj_simt");
+  dim3 grid((N + 63) / 64, (N + 63) / 64, B * 128);
+  if (outgoing) trimul_contract_simt_kernel<true><<<grid, 256, 0, st>>>(c->a, c->b, c->x, N);
+  else trimul_contract_simt_kernel<false><<<grid, 256, 0, st>>>(c->a, c->b, c->x, N);
+  GB_LAUNCH_CHECK(c, "trimul_contract_simt");
+  trimul_out_simt_kernel<<<tiles, 256, kSmemPair, st>>>(c->x, c->g, p, M, N, w.ln_out_g, w.ln_out_b, w.WzT, w.bz);
+  GB_LAUNCH_CHECK(c, "trimul_out_simt");
+  return GB_OK;
+}
+
+static int run_transition(gb_ctx* c, const TransitionW& w, float* p, cudaStream_t st) {
+  if (c->precision != GB_PREC_FP32) return tc_pair_transition(c, w, p, st);
+  const size_t M = (size_t)c->B * c->N * c->N;
+  const unsigned tiles = (unsigned)((M + 127) / 128);
+  pair_transition_simt_kernel<<<tiles, 256, kSmemTrans, st>>>(p, M, c->N, c->mask, w.ln_g, w.ln_b, w.W1T, w.b1, w.W2T, w.b2,
+                                                              c->d.pair_transition_n);
+  GB_LAUNCH_CHECK(c, "pair_transition_simt");
+  return GB_OK;
+}
+
+static int run_ipa(gb_ctx* c, const StructLayerW& w, const float* s, const float* p, const float* rots, const float* trans,
+                   float* out, const float* residual, cudaStream_t st) {
+  const int B = c->B, N = c->N, R = B * N, cs = c->d.c_s;
+  sgemm_nt(st, s, cs, w.Wqkv, cs, w.bqkv, nullptr, 0, c->qkv, IPA_QKV, R, IPA_QKV, cs, false);
+  GB_LAUNCH_CHECK(c, "ipa_proj");
+  const int NP = IPA_H * IPA_PQ + IPA_H * (IPA_PQ + IPA_PV);
+  ipa_points_to_global_kernel<<<(R * NP + 255) / 256, 256, 0, st>>>(c->qkv, rots, trans, R);
+  GB_LAUNCH_CHECK(c, "ipa_points_to_global");
+  const size_t smem = ((size_t)IPA_H * N + 192 + 144 + 288) * sizeof(float);
+  if (smem > 200 * 1024) return gb_fail(c, GB_ERR_UNSUPPORTED, "N = %d too large for ipa_attention", N);
+  ipa_attention_kernel<<<dim3(N, B), 256, smem, st>>>(c->qkv, p, rots, trans, c->mask, w.Wb, w.bb, w.hw, c->cat, N);
+  GB_LAUNCH_CHECK(c, "ipa_attention");
+  sgemm_nt(st, c->cat, IPA_CAT, w.Wout, IPA_CAT, w.bout, residual, cs, out, cs, R, cs, IPA_CAT, false);
+  GB_LAUNCH_CHECK(c, "ipa_out");
+  return GB_OK;
+}
+
+extern "C" int gb_frenet(gb_ctx* c, const float* trans, float* rots_out, void* stream) {
+  int rc = check_ready(c, "gb_frenet");
+  if (rc) return rc;
+  if (!trans || !rots_out) return gb_fail(c, GB_ERR_INVALID, "gb_frenet: NULL pointer");
+  const size_t smem = (size_t)c->N * 13 * 4;
+  frenet_kernel<<<c->B, 256, smem, (cudaStream_t)stream>>>(trans, c->chain_index, c->mask, c->N, rots_out);
+  GB_LAUNCH_CHECK(c, "frenet");
+  return GB_OK;
+}
+
+extern "C" int gb_k_frenet(const float* trans, const int32_t* chain_index, const int32_t* residue_mask, int B, int N,
+                           float* rots_out, void* stream) {
+  if (!trans || !chain_index || !residue_mask || !rots_out || B < 1 || N < 3) return gb_fail(nullptr, GB_ERR_INVALID, "gb_k_frenet: bad arguments");
+  const size_t smem = (size_t)N * 13 * 4;
+  if (smem > 200 * 1024) return gb_fail(nullptr, GB_ERR_UNSUPPORTED, "gb_k_frenet: N too large");
+  cudaFuncSetAttribute(frenet_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+  frenet_kernel<<<B, 256, smem, (cudaStream_t)stream>>>(trans, chain_index, residue_mask, N, rots_out);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return gb_fail(nullptr, GB_ERR_CUDA, "frenet launch failed: %s", cudaGetErrorString(e));
+  return GB_OK;
+}
+
+extern "C" int gb_denoise(gb_ctx* c, const float* rots, const float* trans, const int32_t* timesteps, float* z_out,
+                          const gb_aux* aux, void* stream) {
+  int rc = check_ready(c, "gb_denoise");
+  if (rc) return rc;
+  if (!rots || !trans || !timesteps || !z_out) return gb_fail(c, GB_ERR_INVALID, "gb_denoise: NULL pointer");
+  if (c->d.include_tri_att) return gb_fail(c, GB_ERR_UNSUPPORTED, "gb_denoise: triangle attention kernels not built in this revision");
+  cudaStream_t st = (cudaStream_t)stream;
+  const gb_dims& d = c->d;
+  const int B = c->B, N = c->N, R = B * N, cs = d.c_s;
+  const size_t Rcs = (size_t)R * cs;
+  init_frames_kernel<<<(R * 9 + 255) / 256, 256, 0, st>>>(rots, trans, c->rots_w, c->trans_w, d.rescale, R);
+  GB_LAUNCH_CHECK(c, "init_frames");
+  // SingleFeatureNet
+  single_combine_kernel<<<(unsigned)((Rcs + 255) / 256), 256, 0, st>>>(c->s, c->s_static, c->time_table, timesteps, c->mask, B, N, cs);
+  GB_LAUNCH_CHECK(c, "single_combine");
+  if (aux && aux->s) GB_CUDA(c, cudaMemcpyAsync(aux->s, c->s, Rcs * 4, cudaMemcpyDeviceToDevice, st));
+  if (aux && aux->states) GB_CUDA(c, cudaMemcpyAsync(aux->states, c->s, Rcs * 4, cudaMemcpyDeviceToDevice, st));
+  // PairFeatureNet
+  sgemm_nt(st, c->s, cs, c->W_pipj, cs, nullptr, nullptr, 0, c->pipj, 256, R, 256, cs, false);
+  GB_LAUNCH_CHECK(c, "pair_pipj");
+  pair_embed_kernel<37><<<dim3(N, B), 128, 0, st>>>(c->p, c->pipj, c->rots_w, c->trans_w, c->residue_index, c->chain_index, c->mask,
+                                                    c->fsm, c->fst, c->motif_pos, c->WrelT, c->WtT, c->WmT,
+                                                    aux ? aux->quat_follow : nullptr, N, d.relpos_k, d.template_dist_min,
+                                                    d.template_dist_step, c->has_motif);
+  GB_LAUNCH_CHECK(c, "pair_embed");
+  // PairTransformNet
+  for (int l = 0; l < d.n_pair_transform_layer; ++l) {
+    if (d.include_mul_update) {
+      if ((rc = run_trimul(c, c->pair[l].mul_out, true, c->p, st))) return rc;
+      if ((rc = run_trimul(c, c->pair[l].mul_in, false, c->p, st))) return rc;
+    }
+    if ((rc = run_transition(c, c->pair[l].tr, c->p, st))) return rc;
+  }
+  if (aux && aux->p) GB_CUDA(c, cudaMemcpyAsync(aux->p, c->p, (size_t)R * N * 128 * 4, cudaMemcpyDeviceToDevice, st));
+  // StructureNet
+  float* s = c->s;
+  int state_idx = 1;
+  for (int blk = 0; blk < d.n_structure_block; ++blk)
+    for (int l = 0; l < d.n_structure_layer; ++l) {
+      const StructLayerW& w = c->st[l];
+      if ((rc = run_ipa(c, w, s, c->p, c->rots_w, c->trans_w, c->sA, s, st))) return rc;           // sA = s + ipa
+      layernorm_rows_kernel<<<(R * 32 + 255) / 256, 256, 0, st>>>(c->sA, c->sB, nullptr, w.ln1_g, w.ln1_b, R, cs);
+      GB_LAUNCH_CHECK(c, "ipa_layer_norm");
+      float* cur = c->sB;
+      float* other = c->sA;
+      for (int t = 0; t < d.n_structure_transition_layer; ++t) {
+        sgemm_nt(st, cur, cs, w.W1[t], cs, w.b1[t], nullptr, 0, c->h1, cs, R, cs, cs, true);
+        GB_LAUNCH_CHECK(c, "st_linear_1");
+        sgemm_nt(st, c->h1, cs, w.W2[t], cs, w.b2[t], nullptr, 0, c->h2, cs, R, cs, cs, true);
+        GB_LAUNCH_CHECK(c, "st_linear_2");
+        sgemm_nt(st, c->h2, cs, w.W3[t], cs, w.b3[t], cur, cs, other, cs, R, cs, cs, false);
+        GB_LAUNCH_CHECK(c, "st_linear_3");
+        float* tmp = cur; cur = other; other = tmp;
+      }
+      float* st_out = (aux && aux->states) ? aux->states + (size_t)state_idx * Rcs : nullptr;
+      layernorm_rows_kernel<<<(R * 32 + 255) / 256, 256, 0, st>>>(cur, c->s, st_out, w.ln2_g, w.ln2_b, R, cs);
+      GB_LAUNCH_CHECK(c, "transition_layer_norm");
+      ++state_idx;
+      s = c->s;
+      backbone_update_kernel<<<(R * 32 + 255) / 256, 256, 0, st>>>(s, w.Wbb, w.bbb, c->rots_w, c->trans_w, R, cs);
+      GB_LAUNCH_CHECK(c, "backbone_update");
+    }
+  finish_kernel<<<(R * 9 + 255) / 256, 256, 0, st>>>(trans, c->trans_w, c->rots_w, z_out, aux ? aux->out_trans : nullptr,
+                                                     aux ? aux->out_rots : nullptr, 1.f / d.rescale, R);
+  GB_LAUNCH_CHECK(c, "finish");
+  return GB_OK;
+}
+
+static int launch_ddpm(gb_ctx* c, float* trans, float* rots, const float* z, int step, float scale, const float* noise,
+                       size_t noise_step_stride, uint64_t seed, cudaStream_t st) {
+  const size_t smem = (size_t)c->N * 13 * 4;
+  ddpm_step_kernel<<<c->B, 256, smem, st>>>(trans, rots, z, noise, c->chain_index, c->mask, c->alphas, c->sqrt_alphas,
+                                            c->sqrt_omac, c->sqrt_betas, step, nullptr, noise_step_stride, scale, seed, c->N);
+  GB_LAUNCH_CHECK(c, "ddpm_step");
+  return GB_OK;
+}
+
+extern "C" int gb_p_sample(gb_ctx* c, float* trans_inout, float* rots_inout, const float* z, int step, float scale,
+                           const float* noise, uint64_t seed, void* stream) {
+  int rc = check_ready(c, "gb_p_sample");
+  if (rc) return rc;
+  if (!c->schedule_set) return gb_fail(c, GB_ERR_INVALID, "gb_p_sample: schedule not set");
+  if (!trans_inout || !rots_inout || !z) return gb_fail(c, GB_ERR_INVALID, "gb_p_sample: NULL pointer");
+  if (step < 1 || step > c->d.n_timestep) return gb_fail(c, GB_ERR_INVALID, "gb_p_sample: step %d outside [1, %d]", step, c->d.n_timestep);
+  return launch_ddpm(c, trans_inout, rots_inout, z, step, scale, noise, 0, seed, (cudaStream_t)stream);
+}
+
+extern "C" int gb_sample_loop(gb_ctx* c, float* trans_inout, float* rots_inout, int t_start, int t_end, float scale,
+                              const float* noise_tape, uint64_t seed, void* stream) {
+  int rc = check_ready(c, "gb_sample_loop");
+  if (rc) return rc;
+  if (!c->schedule_set) return gb_fail(c, GB_ERR_INVALID, "gb_sample_loop: schedule not set");
+  if (!trans_inout || !rots_inout) return gb_fail(c, GB_ERR_INVALID, "gb_sample_loop: NULL pointer");
+  if (t_end < 1 || t_start > c->d.n_timestep || t_start < t_end)
+    return gb_fail(c, GB_ERR_INVALID, "gb_sample_loop: bad step range [%d, %d]", t_start, t_end);
+  cudaStream_t st = (cudaStream_t)stream;
+  const size_t stride = (size_t)c->B * c->N * 3;
+  for (int step = t_start; step >= t_end; --step) {
+    fill_int_kernel<<<1, 256, 0, st>>>(c->t_dev, step, c->B);
+    GB_LAUNCH_CHECK(c, "fill_timesteps");
+    if ((rc = gb_denoise(c, rots_inout, trans_inout, c->t_dev, c->z, nullptr, stream))) return rc;
+    if ((rc = launch_ddpm(c, trans_inout, rots_inout, c->z, step, scale, noise_tape, noise_tape ? stride : 0, seed, st))) return rc;
+  }
+  return GB_OK;
+}
+
+extern "C" int gb_sample_host(gb_ctx* c, const float* x_T_host, float* x_out_host, int t_start, int t_end, float scale,
+                              const float* noise_tape_host, uint64_t seed) {
+  int rc = check_ready(c, "gb_sample_host");
+  if (rc) return rc;
+  if (!x_T_host || !x_out_host) return gb_fail(c, GB_ERR_INVALID, "gb_sample_host: NULL pointer");
+  GB_CUDA(c, cudaSetDevice(c->device));
+  const size_t stride = (size_t)c->B * c->N * 3;
+  cudaStream_t st = 0;
+  GB_CUDA(c, cudaMemcpyAsync(c->trans_io, x_T_host, stride * 4, cudaMemcpyHostToDevice, st));
+  const float* tape = nullptr;
+  if (noise_tape_host) {
+    const size_t need = ((size_t)c->d.n_timestep + 1) * stride * 4;
+    if (need > c->tape_bytes) {
+      if (c->tape_alloc) cudaFree(c->tape_alloc);
+      c->tape_alloc = nullptr; c->tape_bytes = 0;
+      GB_CUDA(c, cudaMalloc(&c->tape_alloc, need));
+      c->tape_bytes = need;
+    }
+    // only the slices the loop reads: steps t_end..t_start
+    const size_t lo = (size_t)t_end * stride, cnt = (size_t)(t_start - t_end + 1) * stride;
+    GB_CUDA(c, cudaMemcpyAsync((float*)c->tape_alloc + lo, noise_tape_host + lo, cnt * 4, cudaMemcpyHostToDevice, st));
+    tape = (const float*)c->tape_alloc;
+  }
+  if ((rc = gb_frenet(c, c->trans_io, c->rots_io, st))) return rc;
+  if ((rc = gb_sample_loop(c, c->trans_io, c->rots_io, t_start, t_end, scale, tape, seed, st))) return rc;
+  GB_CUDA(c, cudaMemcpyAsync(x_out_host, c->trans_io, stride * 4, cudaMemcpyDeviceToHost, st));
+  GB_CUDA(c, cudaStreamSynchronize(st));
+  return GB_OK;
+}
+
+// ------------------------------------------------------------------ per-kernel entry points
+extern "C" int gb_k_trimul(gb_ctx* c, int layer, int outgoing, float* p, void* stream) {
+  int rc = check_ready(c, "gb_k_trimul");
+  if (rc) return rc;
+  if (!p || layer < 0 || layer >= c->d.n_pair_transform_layer || !c->d.include_mul_update) return gb_fail(c, GB_ERR_INVALID, "gb_k_trimul: bad arguments");
+  return run_trimul(c, outgoing ? c->pair[layer].mul_out : c->pair[layer].mul_in, outgoing != 0, p, (cudaStream_t)stream);
+}
+
+extern "C" int gb_k_pair_transition(gb_ctx* c, int layer, float* p, void* stream) {
+  int rc = check_ready(c, "gb_k_pair_transition");
+  if (rc) return rc;
+  if (!p || layer < 0 || layer >= c->d.n_pair_transform_layer) return gb_fail(c, GB_ERR_INVALID, "gb_k_pair_transition: bad arguments");
+  return run_transition(c, c->pair[layer].tr, p, (cudaStream_t)stream);
+}
+
+extern "C" int gb_k_tri_attention(gb_ctx* c, int layer, int starting, float* p, void* stream) {
+  (void)layer; (void)starting; (void)p; (void)stream;
+  return gb_fail(c, GB_ERR_UNSUPPORTED, "gb_k_tri_attention: not built in this revision");
+}
+
+extern "C" int gb_k_ipa(gb_ctx* c, int layer, const float* s, const float* p, const float* rots, const float* trans,
+                        float* out, void* stream) {
+  int rc = check_ready(c, "gb_k_ipa");
+  if (rc) return rc;
+  if (!s || !p || !rots || !trans || !out || layer < 0 || layer >= c->d.n_structure_layer) return gb_fail(c, GB_ERR_INVALID, "gb_k_ipa: bad arguments");
+  return run_ipa(c, c->st[layer], s, p, rots, trans, out, nullptr, (cudaStream_t)stream);
+}

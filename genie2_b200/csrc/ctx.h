@@ -1,0 +1,106 @@
+// Internal context of the genie2_b200 library (not part of the C ABI).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <string>
+#include <unordered_map>
+#include <vector>
+
+#include "../../include/genie2_b200.h"
+
+struct HostTensor {
+  std::vector<float> v;
+  std::vector<int64_t> shape;
+};
+
+struct TriMulW {
+  float *ln_in_g, *ln_in_b, *ln_out_g, *ln_out_b;
+  float *Wpk, *bpk;   // [5][128][128], [5][128]   (fp32 SIMT packing, see kernels_pair_simt.cuh)
+  float *WzT, *bz;    // [128 k][128 n], [128]
+  // tensor-core packings (K-major [n][k] rows, i.e. nn.Linear layout), filled by tc_pack
+  void *tc_Wproj, *tc_Wz;
+  float *tc_bproj;
+};
+struct TransitionW {
+  float *ln_g, *ln_b, *W1T, *b1, *W2T, *b2;
+  void *tc_W1, *tc_W2;
+};
+struct TriAttW {
+  float *ln_g, *ln_b, *Wbias /*[H][128]*/, *Wqkvg /*[4*H*C][128]: q|k|v|g*/, *bg, *Wo /*[128][H*C]*/, *bo;
+};
+struct PairLayerW {
+  TriMulW mul_out, mul_in;
+  TriAttW att_start, att_end;
+  TransitionW tr;
+};
+struct StructLayerW {
+  float *Wqkv, *bqkv;           // [1152][c_s], [1152]
+  float *Wb, *bb, *hw;          // [12][128], [12], [12]
+  float *Wout, *bout;           // [c_s][2112]
+  float *ln1_g, *ln1_b;
+  std::vector<float*> W1, b1, W2, b2, W3, b3;
+  float *ln2_g, *ln2_b;
+  float *Wbb, *bbb;             // [6][c_s], [6]
+};
+
+struct gb_ctx {
+  gb_dims d;
+  int device = 0;
+  int precision = GB_PREC_FP32;
+  mutable std::string err;
+  int64_t launches = 0;
+
+  std::unordered_map<std::string, HostTensor> host;   // state dict as loaded
+  std::vector<void*> weight_allocs;                    // device buffers owned by the weights
+  bool weights_loaded = false, schedule_set = false, features_set = false;
+
+  // packed weights
+  float *W_single = nullptr;      // [c_s][855] raw
+  float *time_table = nullptr;    // [T+1][c_s]
+  float *W_pipj = nullptr;        // [2*c_p][c_s]
+  float *WrelT = nullptr, *WtT = nullptr, *WmT = nullptr;
+  std::vector<PairLayerW> pair;
+  std::vector<StructLayerW> st;
+
+  // schedule tables [T+1]
+  float *alphas = nullptr, *sqrt_alphas = nullptr, *sqrt_omac = nullptr, *sqrt_betas = nullptr;   // alphas owns the block
+
+  // bound features
+  int B = 0, N = 0, has_motif = 0;
+  void* feat_alloc = nullptr;
+  int *residue_index = nullptr, *chain_index = nullptr, *mask = nullptr, *aatype = nullptr;
+  uint8_t *fsm = nullptr, *fst = nullptr, *iface = nullptr;
+  float *motif_pos = nullptr, *s_static = nullptr;
+
+  // workspace
+  void* ws_alloc = nullptr;
+  size_t ws_bytes = 0;
+  float *s = nullptr, *sA = nullptr, *sB = nullptr, *h1 = nullptr, *h2 = nullptr, *pipj = nullptr;
+  float *p = nullptr, *a = nullptr, *b = nullptr, *x = nullptr, *g = nullptr;
+  float *qkv = nullptr, *cat = nullptr, *rots_w = nullptr, *trans_w = nullptr, *z = nullptr;
+  float *trans_io = nullptr, *rots_io = nullptr;   // gb_sample_host state
+  int* t_dev = nullptr;                            // [B] timesteps
+  void* tape_alloc = nullptr;
+  size_t tape_bytes = 0;
+  // tensor-core scratch (bf16/tf32 operand copies), owned by the tc module
+  void* tc_state = nullptr;
+};
+
+// set ctx->err (printf style) and return code
+int gb_fail(const gb_ctx* ctx, int code, const char* fmt, ...);
+
+#define GB_CUDA(ctx, call)                                                                          \
+  do {                                                                                              \
+    cudaError_t e_ = (call);                                                                        \
+    if (e_ != cudaSuccess) return gb_fail(ctx, GB_ERR_CUDA, "%s failed: %s (%s:%d)", #call,        \
+                                          cudaGetErrorString(e_), __FILE__, __LINE__);             \
+  } while (0)
+
+#define GB_LAUNCH_CHECK(ctx, name)                                                                  \
+  do {                                                                                              \
+    (ctx)->launches++;                                                                              \
+    cudaError_t e_ = cudaGetLastError();                                                            \
+    if (e_ != cudaSuccess) return gb_fail(ctx, GB_ERR_CUDA, "launch of %s failed: %s", name,       \
+                                          cudaGetErrorString(e_));                                 \
+  } while (0)

@@ -1,0 +1,20 @@
+// Interface between the orchestration (api.cu) and the tcgen05 tensor-core module (tc_*.cu).
+#pragma once
+#include <vector>
+
+#include "ctx.h"
+
+int tc_init(gb_ctx* c);
+void tc_destroy(gb_ctx* c);
+int tc_pack_trimul(gb_ctx* c, TriMulW& w, const std::vector<float>& ap, const std::vector<float>& ag,
+                   const std::vector<float>& bp, const std::vector<float>& bg, const std::vector<float>& lg,
+                   const std::vector<float>& lz, const std::vector<float>& apb, const std::vector<float>& agb,
+                   const std::vector<float>& bpb, const std::vector<float>& bgb, const std::vector<float>& lgb);
+int tc_pack_transition(gb_ctx* c, TransitionW& w, const std::vector<float>& w1, const std::vector<float>& w2);
+// workspace the tensor-core path needs for a (B,N) batch, carved by gb_set_features
+size_t tc_workspace_bytes(const gb_ctx* c, int B, int N);
+int tc_bind_workspace(gb_ctx* c, void* base, size_t bytes);
+// p += TriangleMultiplicativeUpdate(p) with tcgen05 kernels (precision = c->precision)
+int tc_trimul(gb_ctx* c, const TriMulW& w, bool outgoing, float* p, cudaStream_t st);
+// p = (p + PairTransition(p)) * mask
+int tc_pair_transition(gb_ctx* c, const TransitionW& w, float* p, cudaStream_t st);

@@ -39,3 +39,30 @@ def load_forward_case(name):
 
 
 FORWARD_CASES = ['uncond_base_ragged', 'uncond_stock', 'motif_base', 'triatt', 'multichain']
+
+
+# ------------------------------------------------------------------ CUDA-side helpers (gpu tests)
+def make_denoiser(cfg, sd, precision='fp32', device='cuda:0'):
+    """genie2_b200.Denoiser holding the oracle's seeded state dict."""
+    import genie2_b200
+    kw = cfg.model_kwargs()
+    m = genie2_b200.Denoiser(**kw)
+    m.load_state_dict(sd)
+    m = m.to(device)
+    m.set_precision(precision)
+    m.return_intermediates = True
+    return m
+
+
+def feats_to(feats, device):
+    return {k: v.to(device) for k, v in feats.items()}
+
+
+def run_cuda_forward(model, rots, trans, timesteps, feats, quat_follow=None, device='cuda:0'):
+    import genie2_b200
+    f = feats_to(feats, device)
+    out = model(genie2_b200.T(rots.to(device), trans.to(device)), timesteps.to(device), f,
+                quat_follow=None if quat_follow is None else quat_follow.to(device))
+    torch.cuda.synchronize()
+    return {'z': out['z'].cpu(), 's': out['s'].cpu(), 'p': out['p'].cpu(), 'states': out['states'].cpu(),
+            'trans': out['ts'].trans.cpu(), 'rots': out['ts'].rots.cpu()}, f
