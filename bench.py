@@ -1,0 +1,355 @@
+"""Benchmark of the reverse-diffusion sampling hot path (contract: see the task brief).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--precision fp32|tf32|bf16] [--impl reference]
+
+A "step" is one reverse-diffusion step over one batch: denoiser eval (Denoiser.forward) + DDPM
+posterior update + Frenet frames of x_{t-1}, i.e. one iteration of the loop at
+genie/sampler/base.py:239-282.  Workload at every N: BASELINE.json configs[1] -- unconditional,
+L=256, batch 4, scale 0.6, base configuration, seeded "activated" random-init weights, synthetic
+x_T ~ N(0,1).  With N > 1 every rank runs its own independent batch (the reference's
+process-per-GPU farm, utils/multiprocessor.py:59-100; no collective on the data path): weak scaling.
+
+value  = denoiser evals/s summed over ranks, state resident in HBM (gb_sample_loop).
+e2e    = the same through the host-buffer entry point gb_sample_host: every step uploads x_t
+         [B,N,3] from pinned host memory and downloads x_{t-1}.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+L, B, SCALE, T_STEPS = 256, 4, 0.6, 1000
+METRIC = 'denoiser evals/sec at L=256 batch 4'
+UNIT = 'evals/s'
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=None)
+    ap.add_argument('--warmup', type=int, default=None)
+    ap.add_argument('--precision', default=os.environ.get('GB_BENCH_PRECISION', 'auto'))
+    ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
+    ap.add_argument('--no-cpu-baseline', action='store_true')
+    return ap.parse_args()
+
+
+def peaks():
+    p = os.path.join(ROOT, 'MEASURED_PEAKS.json')
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return {'hbm': d['hbm_gbs'], 'tensor_burst': d['bf16_tflops'],
+                'tensor_sustained': d.get('bf16_tflops_sustained', d['bf16_tflops']), 'src': 'measured'}
+    return {'hbm': 6650.0, 'tensor_burst': 1590.0, 'tensor_sustained': 1400.0, 'src': 'fallback'}
+
+
+def flops_per_eval(n, b):
+    """algorithmic FLOPs of one denoiser eval (base config)."""
+    return b * (2560.0 * n ** 3 + 3378304.0 * n ** 2 + 28022016.0 * n)
+
+
+# ------------------------------------------------------------------------------- CPU oracle legs
+def oracle_stepper(n_threads=None):
+    """Time the CPU oracle (port of the reference's fp32 eager path) on ONE sample of the
+    workload: a full denoiser eval + posterior step at L=256, batch 1."""
+    import torch
+    from oracle import genie_oracle as O, weights as W
+    if n_threads:
+        torch.set_num_threads(n_threads)
+    cfg = O.OracleConfig()
+    sd = W.make_state_dict(cfg, 0, 'activated')
+    feats = O.make_features([[L]])
+    g = torch.Generator().manual_seed(1)
+    x = torch.randn(1, L, 3, generator=g)
+    sched = O.setup_schedule(T_STEPS)
+
+    def step(x, t):
+        r = O.compute_frenet_frames(x, feats['chain_index'], feats['residue_mask'])
+        tt = torch.full((1,), t, dtype=torch.int32)
+        z = O.denoiser_forward(sd, cfg, r, x, tt, feats, 'canonical')['z']
+        _, x2 = O.p_sample(sched, x, z, t, SCALE, torch.randn(1, L, 3, generator=g), feats)
+        return x2
+
+    return step, x, torch.get_num_threads()
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU algorithm (oracle port; the Python reference itself
+    cannot travel to the GPU box) on the host cores.  One step = one reverse step of ONE sample
+    (L=256, batch 1) -- a bounded quarter of the batch-4 workload; evals/s is quoted for batch 4."""
+    rank = int(os.environ.get('RANK', '0'))
+    if rank != 0:
+        return
+    import torch
+    K = args.steps if args.steps is not None else 3
+    W_ = args.warmup if args.warmup is not None else 1
+    step, x, threads = oracle_stepper()
+    with torch.no_grad():
+        t = T_STEPS
+        for _ in range(W_):
+            x = step(x, t)
+            t -= 1
+        t0 = time.perf_counter()
+        for _ in range(K):
+            x = step(x, t)
+            t -= 1
+        dt = time.perf_counter() - t0
+    per_sample = dt / K
+    value = 1.0 / (B * per_sample)
+    line = {
+        'impl': 'reference', 'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': args.gpus, 'steps': K, 'warmup': W_,
+        'ms_per_step': per_sample * B * 1e3, 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None,
+        'dtype': 'f32', 'data': 'synthetic',
+        'config': {'workload': 'unconditional L=256 batch 4, base config, 1000-step schedule, scale 0.6',
+                   'sample': 'one reverse step of 1 of the 4 samples per step; batch-4 rate = 1/(4 t)'},
+        'cpu_baseline': {'value': value, 'unit': UNIT, 'cores': threads, 'kind': 'port',
+                         'sample': '%d reverse steps at L=256 batch 1 (oracle/genie_oracle.py, torch CPU fp32)' % K},
+        'e2e': {'value': value, 'unit': UNIT, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
+        'seconds_per_1000_step_sample': 1000.0 * per_sample * B,
+        'gpu_launches': 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------- clocks
+class ClockSampler:
+    """nvidia-smi clocks/throttle reasons sampled every 200 ms during the timed region."""
+    Q = ('clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,'
+         'clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap')
+
+    def __init__(self, index):
+        self.f = tempfile.NamedTemporaryFile('w+', suffix='.csv', delete=False)
+        self.p = None
+        try:
+            self.p = subprocess.Popen(['nvidia-smi', '-i', str(index), '--query-gpu=' + self.Q,
+                                       '--format=csv,noheader,nounits', '-lms', '200'], stdout=self.f, stderr=subprocess.DEVNULL)
+        except OSError:
+            pass
+
+    def stop(self):
+        if self.p is None:
+            return {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': ['nvidia-smi unavailable']}
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.p.kill()
+        self.f.flush()
+        rows = [r.strip().split(', ') for r in open(self.f.name) if r.strip()]
+        os.unlink(self.f.name)
+        sm, mx, reasons = [], None, set()
+        names = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
+        for r in rows:
+            if len(r) < 6:
+                continue
+            try:
+                sm.append(float(r[0]))
+                mx = float(r[1])
+            except ValueError:
+                continue
+            for nme, v in zip(names, r[2:6]):
+                if v.strip().lower().startswith('active'):
+                    reasons.add(nme)
+        sm.sort()
+        return {'sm_mhz': sm[len(sm) // 2] if sm else None, 'sm_max_mhz': mx, 'reasons': sorted(reasons), 'samples': len(sm)}
+
+
+# ------------------------------------------------------------------------------- B200 arm
+def pick_precision(genie, requested):
+    """'auto' = the fastest GEMM mode this build has that holds the 1e-3 per-step gate on z
+    (tests/test_gpu_tensorcore.py): tf32 tensor cores if built, else the fp32 CUDA-core path."""
+    import torch
+    order = [requested] if requested != 'auto' else ['tf32', 'fp32']
+    for prec in order:
+        try:
+            genie.model.set_precision(prec)
+            probe_forward(genie)
+            return prec
+        except RuntimeError as e:
+            if 'not built' not in str(e) or requested != 'auto':
+                raise
+    raise RuntimeError('no usable precision')
+
+
+_PROBE = {}
+
+
+def probe_forward(genie):
+    import torch
+    import genie2_b200
+    from oracle import genie_oracle as O   # feature construction only (host side)
+    dev = genie.device
+    if 'f' not in _PROBE:
+        f = O.make_features([[32]])
+        _PROBE['f'] = {k: v.to(dev) for k, v in f.items()}
+    x = torch.randn(1, 32, 3, device=dev)
+    ts = genie2_b200.T(genie2_b200.compute_frenet_frames(genie.model, _PROBE['f'], x), x)
+    genie.model(ts, torch.full((1,), 5, dtype=torch.int32, device=dev), _PROBE['f'])
+    torch.cuda.synchronize()
+
+
+def dominant_kernel_roofline(genie, ctx, lib, prec, pk, reps=10):
+    """CUDA-event time of the kernel with the largest share of the step (profiles/): the fused
+    pair transition.  Algorithmic FLOPs per launch = B*N^2 * 262,144 (LN-free GEMM
+    terms 2*128*512*2 per pixel); the p tensor it streams (B*N^2*128*4 B = 134 MB) exceeds L2."""
+    import torch
+    from genie2_b200 import _lib
+    dev = genie.device
+    M = B * L * L
+    p = torch.randn(B, L, L, 128, device=dev)
+    stream = torch.cuda.current_stream(dev).cuda_stream
+    for _ in range(3):
+        _lib.check(lib.gb_k_pair_transition(ctx, 0, p.data_ptr(), stream), ctx, 'gb_k_pair_transition')
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(reps + 1)]
+    ev[0].record()
+    for i in range(reps):
+        _lib.check(lib.gb_k_pair_transition(ctx, i % 5, p.data_ptr(), stream), ctx, 'gb_k_pair_transition')
+        ev[i + 1].record()
+    torch.cuda.synchronize()
+    ms = sorted(ev[i].elapsed_time(ev[i + 1]) for i in range(reps))[reps // 2]
+    flops = M * 262144.0
+    achieved = flops / (ms * 1e-3) / 1e12
+    peak = pk['tensor_burst']
+    return {'kernel': 'pair_transition (%s)' % prec, 'bound': 'tensor', 'achieved': achieved, 'peak': peak, 'unit': 'TFLOP/s',
+            'frac': achieved / peak, 'traffic': None, 'ms_per_launch': ms, 'peak_source': pk['src'] + ' bf16 burst',
+            'hbm_gbs': 2.0 * M * 128 * 4 / (ms * 1e-3) / 1e9}
+
+
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+    import genie2_b200
+    from genie2_b200 import _lib
+    from oracle import genie_oracle as O, weights as W     # seeded weights / synthetic features (host) + cpu_baseline leg
+
+    world = int(os.environ.get('WORLD_SIZE', '1'))
+    rank = int(os.environ.get('RANK', '0'))
+    local = int(os.environ.get('LOCAL_RANK', '0'))
+    if not torch.cuda.is_available():
+        raise RuntimeError('bench.py needs a CUDA device: the hot path has no CPU fallback')
+    torch.cuda.set_device(local)
+    dev = torch.device('cuda', local)
+    if world > 1:
+        dist.init_process_group('nccl', device_id=dev)
+    K = args.steps if args.steps is not None else 50
+    W_ = args.warmup if args.warmup is not None else 5
+    W_ = max(W_, 3)
+    if K + W_ > T_STEPS:
+        raise SystemExit('steps + warmup must be <= %d' % T_STEPS)
+
+    lib = _lib.load()
+    cfg = O.OracleConfig()
+    sd = W.make_state_dict(cfg, 0, 'activated')
+    genie = genie2_b200.Genie(genie2_b200.Config())
+    genie.model.load_state_dict(sd)
+    genie = genie.to(dev)
+    genie.setup_schedule()
+    prec = pick_precision(genie, args.precision)
+    feats = {k: v.to(dev) for k, v in O.make_features([[L]] * B).items()}
+    ctx = genie.model.bind_features(feats, dev)
+    genie.bind_schedule(ctx)
+    g = torch.Generator().manual_seed(1 + rank)
+    x_host = torch.randn(B, L, 3, generator=g).pin_memory()
+    x = x_host.to(dev)
+    rots = genie2_b200.compute_frenet_frames(genie.model, feats, x)
+    stream = torch.cuda.current_stream(dev).cuda_stream
+
+    def loop(t_start, n):
+        _lib.check(lib.gb_sample_loop(ctx, x.data_ptr(), rots.data_ptr(), t_start, t_start - n + 1, SCALE, None, 1234 + rank, stream),
+                   ctx, 'gb_sample_loop')
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-resident throughput
+    loop(T_STEPS, W_)
+    barrier()
+    clocks = ClockSampler(local)
+    l0 = genie.model.launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    loop(T_STEPS - W_, K)
+    e1.record()
+    barrier()
+    launches = genie.model.launch_count() - l0
+    ms = e0.elapsed_time(e1)
+    clk = clocks.stop()
+    finite = bool(torch.isfinite(x).all())
+
+    # ---- end to end through host buffers: one gb_sample_host call per step
+    out_host = torch.empty_like(x_host).pin_memory()
+    cur, nxt = x_host, out_host
+    t = T_STEPS
+    for _ in range(3):
+        _lib.check(lib.gb_sample_host(ctx, cur.data_ptr(), nxt.data_ptr(), t, t, SCALE, None, 99 + rank), ctx, 'gb_sample_host')
+        cur, nxt, t = nxt, cur, t - 1
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(K):
+        _lib.check(lib.gb_sample_host(ctx, cur.data_ptr(), nxt.data_ptr(), t, t, SCALE, None, 99 + rank), ctx, 'gb_sample_host')
+        cur, nxt, t = nxt, cur, t - 1
+    barrier()
+    e2e_s = time.perf_counter() - t0
+
+    times = torch.tensor([ms, e2e_s * 1e3], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(times, op=dist.ReduceOp.MAX)
+    ms, e2e_ms = float(times[0]), float(times[1])
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    pk = peaks()
+    value = world * K / (ms * 1e-3)
+    e2e_value = world * K / (e2e_ms * 1e-3)
+    roof = dominant_kernel_roofline(genie, ctx, lib, prec, pk)
+    fl = flops_per_eval(L, B)
+    line = {
+        'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': world, 'steps': K, 'warmup': W_, 'ms_per_step': ms / K,
+        'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None,
+        'dtype': {'fp32': 'f32', 'tf32': 'tf32 (fp32 storage, fp32 accumulate)', 'bf16': 'bf16'}[prec], 'data': 'synthetic',
+        'config': {'workload': 'unconditional L=256 batch 4, base config, 1000-step schedule, scale 0.6 (BASELINE configs[1])',
+                   'per_gpu_batch': B, 'length': L, 'precision': prec, 'weights': 'seeded activated random init',
+                   'l2': 'no explicit flush: per-step working set (p,a,b,x,g >= 5 x 134 MB) exceeds the 126 MB L2',
+                   'parallelism': 'independent batches per GPU, no collective' if world > 1 else 'single GPU'},
+        'seconds_per_1000_step_sample': 1000.0 * ms / K * 1e-3,
+        'e2e': {'value': e2e_value, 'unit': UNIT, 'h2d_bytes_per_step': B * L * 3 * 4, 'd2h_bytes_per_step': B * L * 3 * 4,
+                'api': 'gb_sample_host (one call per step, pinned host buffers, synchronous)'},
+        'gpu_launches': int(launches),
+        'clocks': clk,
+        'roofline': roof,
+        'whole_eval': {'algorithmic_tflop_per_eval': fl / 1e12, 'achieved_tflops': fl / (ms / K * 1e-3) / 1e12,
+                       'frac_of_tensor_sustained': fl / (ms / K * 1e-3) / 1e12 / pk['tensor_sustained']},
+        'finite': finite,
+    }
+    if not args.no_cpu_baseline and world == 1:
+        step, xc, threads = oracle_stepper()
+        with torch.no_grad():
+            xc = step(xc, T_STEPS)
+            t0 = time.perf_counter()
+            n = 2
+            for i in range(n):
+                xc = step(xc, T_STEPS - 1 - i)
+            dt = (time.perf_counter() - t0) / n
+        line['cpu_baseline'] = {'value': 1.0 / (B * dt), 'unit': UNIT, 'cores': threads, 'kind': 'port',
+                                'sample': '%d reverse steps of one L=256 sample (oracle port, torch CPU fp32); batch-4 rate = 1/(4 t)' % n}
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == '__main__':
+    a = parse()
+    if a.impl == 'reference':
+        run_reference(a)
+    else:
+        run_b200(a)
