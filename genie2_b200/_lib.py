@@ -68,6 +68,7 @@ SYMBOLS = {
     'gb_k_pair_transition': (C.c_int, [_P, C.c_int, _P, _P]),
     'gb_k_tri_attention': (C.c_int, [_P, C.c_int, C.c_int, _P, _P]),
     'gb_k_ipa': (C.c_int, [_P, C.c_int, _P, _P, _P, _P, _P, _P]),
+    'gb_dbg_tc_copy': (C.c_int, [_P, C.c_int, _P, C.c_int64]),
 }
 
 _lib = None

@@ -442,7 +442,7 @@ extern "C" int gb_set_features(gb_ctx* c, const gb_features* f) {
     carve_features(c, kf2, B, N);
     carve_workspace(c, kw2, B, N);
     kw2.off = (kw2.off + 255) & ~(size_t)255;
-    int rc = tc_bind_workspace(c, (char*)c->ws_alloc + kw2.off, tcb);
+    int rc = tc_bind_workspace(c, (char*)c->ws_alloc + kw2.off, tcb, B, N);
     if (rc != GB_OK) return rc;
     c->B = B; c->N = N;
   }

@@ -13,7 +13,7 @@ int tc_pack_trimul(gb_ctx* c, TriMulW& w, const std::vector<float>& ap, const st
 int tc_pack_transition(gb_ctx* c, TransitionW& w, const std::vector<float>& w1, const std::vector<float>& w2);
 // workspace the tensor-core path needs for a (B,N) batch, carved by gb_set_features
 size_t tc_workspace_bytes(const gb_ctx* c, int B, int N);
-int tc_bind_workspace(gb_ctx* c, void* base, size_t bytes);
+int tc_bind_workspace(gb_ctx* c, void* base, size_t bytes, int B, int N);
 // p += TriangleMultiplicativeUpdate(p) with tcgen05 kernels (precision = c->precision)
 int tc_trimul(gb_ctx* c, const TriMulW& w, bool outgoing, float* p, cudaStream_t st);
 // p = (p + PairTransition(p)) * mask

@@ -1,0 +1,715 @@
+// tcgen05 / TMEM implementation of the pair stack (GB_PREC_BF16): bf16 operands, fp32
+// accumulation in tensor memory, fp32 LayerNorm statistics, fp32 residual stream p.
+//   K4 trimul_proj_tc      LN_in -> [a_p|a_g], [b_p|b_g], g GEMMs -> gated/masked a, b (bf16 tile
+//                          images, the operand format of K5) and the output gate g (bf16)
+//   K5 trimul_contract_tc  per (sample, channel): X = A . B^T, operands streamed with cp.async.bulk
+//   K6 trimul_out_tc       LN_out over channels -> linear_z -> * g -> p +=
+//   K7 pair_transition_tc  LN -> 128->512 -> ReLU -> 512->128, hidden never leaves the SM
+// Reference: modules/triangular_multiplicative_update.py:57-110, modules/pair_transition.py:48-87.
+#include <string.h>
+
+#include <vector>
+
+#include "common.cuh"
+#include "tc_api.h"
+#include "tc_common.cuh"
+
+using namespace tc;
+
+typedef __nv_bfloat16 bf16;
+
+struct TcState {
+  int Np = 0;            // N rounded up to a multiple of 64
+  bf16 *a = nullptr, *b = nullptr;   // [B][128][Np/64][Np][64] tile images
+  bf16 *x = nullptr;                 // [B][128][Np][Np]
+  bf16 *g = nullptr;                 // [B*N*N][128]
+  size_t ab_bytes = 0;
+};
+
+// ---------------------------------------------------------------------------------------------
+// shared helpers
+// ---------------------------------------------------------------------------------------------
+// dynamic shared memory base rounded up to 1024 bytes (SWIZZLE_128B atoms)
+__device__ __forceinline__ uint8_t* smem_base_1024(uint8_t* raw) {
+  const uint32_t a = smem_u32(raw);
+  return raw + (((a + 1023u) & ~1023u) - a);
+}
+
+// LayerNorm(128) of up to 128 pixel rows -> bf16 A operand image [2 kb][128 rows][64].
+// Warp w normalises rows 16w..16w+15, four at a time (four 512-byte coalesced loads in flight);
+// lane l holds channels 4l..4l+3.  src_row(m) returns the fp32 row pointer or nullptr (zero row).
+template <typename RowFn>
+__device__ __forceinline__ void ln_rows_to_image(uint8_t* A, RowFn src_row, const float* __restrict__ gamma,
+                                                 const float* __restrict__ beta) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const float4 g4 = ld4(gamma + lane * 4), b4 = ld4(beta + lane * 4);
+  const uint32_t kb = lane >> 4, chunk = (lane & 15) >> 1, half = lane & 1;
+#pragma unroll
+  for (int it = 0; it < 4; ++it) {
+    float4 v[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const float* r = src_row(warp * 16 + it * 4 + u);
+      v[u] = r ? ld4(r + lane * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const uint32_t m = warp * 16 + it * 4 + u;
+      const float mean = warp_sum(v[u].x + v[u].y + v[u].z + v[u].w) * (1.f / 128.f);
+      const float dx = v[u].x - mean, dy = v[u].y - mean, dz = v[u].z - mean, dw = v[u].w - mean;
+      const float rstd = rsqrtf(warp_sum(dx * dx + dy * dy + dz * dz + dw * dw) * (1.f / 128.f) + 1e-5f);
+      uint2 o;
+      o.x = pack_bf16(dx * rstd * g4.x + b4.x, dy * rstd * g4.y + b4.y);
+      o.y = pack_bf16(dz * rstd * g4.z + b4.z, dw * rstd * g4.w + b4.w);
+      *reinterpret_cast<uint2*>(A + kb * 16384u + m * 128u + ((chunk ^ (m & 7u)) << 4) + half * 8u) = o;
+    }
+  }
+}
+
+// fp32 staging tile [128 rows][128 cols] with 16-byte chunks XOR-swizzled by the row, so that a
+// thread-per-row writer (TMEM epilogue) and a warp-per-row reader are both bank-conflict free.
+__device__ __forceinline__ float4* stage_ptr(uint8_t* S, uint32_t m, uint32_t chunk) {
+  return reinterpret_cast<float4*>(S + m * 512u + ((chunk ^ (m & 31u)) << 4));
+}
+// this thread's 32 TMEM columns [col0, col0+32) (+ bias) -> staging row m
+__device__ __forceinline__ void tmem_to_stage(uint8_t* S, uint32_t taddr, uint32_t m, uint32_t col0,
+                                              const float* __restrict__ bias) {
+  uint32_t v[32];
+  tmem_ld32(taddr, v);
+  tmem_ld_wait();
+#pragma unroll
+  for (int q = 0; q < 8; ++q) {
+    float4 o;
+    o.x = __uint_as_float(v[4 * q + 0]) + bias[col0 + 4 * q + 0];
+    o.y = __uint_as_float(v[4 * q + 1]) + bias[col0 + 4 * q + 1];
+    o.z = __uint_as_float(v[4 * q + 2]) + bias[col0 + 4 * q + 2];
+    o.w = __uint_as_float(v[4 * q + 3]) + bias[col0 + 4 * q + 3];
+    *stage_ptr(S, m, (col0 >> 2) + q) = o;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// K7 pair_transition_tc:  p = (p + (W2 relu(W1 LN(p) + b1) + b2) * mask) * mask
+//   W1img [nchunk][2 kb][128 hidden rows][64]   W2img [nchunk][2 kb][128 out rows][64 hidden]
+// 256 threads, 2 CTAs / SM (97 KB shared, 256 TMEM columns each) so that one CTA's LayerNorm /
+// epilogue overlaps the other's MMAs.  Shared: A 32K | H 32K | W 32K | barriers.
+// ---------------------------------------------------------------------------------------------
+#define K7_SMEM (3 * 32768 + 1024 + 64 + 512)
+
+__global__ void __launch_bounds__(256, 2) pair_transition_tc_kernel(
+    float* __restrict__ p, uint32_t M, int N, const int* __restrict__ rmask, const float* __restrict__ ln_g,
+    const float* __restrict__ ln_b, const bf16* __restrict__ W1img, const float* __restrict__ b1,
+    const bf16* __restrict__ W2img, const float* __restrict__ b2, int nchunk) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* sm = smem_base_1024(smem_raw);
+  uint8_t* A = sm;
+  uint8_t* H = sm + 32768;
+  uint8_t* W = sm + 65536;
+  uint64_t* bar_w = reinterpret_cast<uint64_t*>(sm + 98304);
+  uint64_t* bar_mma = bar_w + 1;
+  uint32_t* tslot = reinterpret_cast<uint32_t*>(bar_w + 2);
+  float* rowmask = reinterpret_cast<float*>(sm + 98304 + 64);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const uint32_t row0 = blockIdx.x * 128u;
+
+  if (tid == 0) {
+    mbar_init(bar_w, 1);
+    mbar_init(bar_mma, 1);
+    fence_mbar_init();
+    mbar_expect_tx(bar_w, 32768);
+    bulk_g2s(W, W1img, 32768, bar_w);
+  }
+  if (warp == 1) tmem_alloc(tslot, 256);
+  if (tid < 128) {
+    const uint32_t row = row0 + tid;
+    float mk = 0.f;
+    if (row < M) {
+      const uint32_t NN = (uint32_t)N * N, b = row / NN, rem = row - b * NN, i = rem / N, j = rem - i * N;
+      mk = (float)(rmask[b * N + i] * rmask[b * N + j]);
+    }
+    rowmask[tid] = mk;
+  }
+  ln_rows_to_image(A, [&](int m) -> const float* { return (row0 + m < M) ? p + (size_t)(row0 + m) * 128 : nullptr; }, ln_g, ln_b);
+  fence_proxy_async();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tslot;
+  const uint32_t q = warp & 3, h = warp >> 2, m = q * 32 + lane;
+  const uint32_t t_lane = tmem + ((q * 32u) << 16);
+  uint32_t wph = 0, mph = 0;
+
+  for (int c = 0; c < nchunk; ++c) {
+    if (tid == 0) {                         // hidden chunk c = A . W1[c]^T -> TMEM cols [0,128)
+      mbar_wait(bar_w, wph);
+      tc_fence_after();
+      umma_tile(tmem, smem_u32(A), smem_u32(W), 128, 2, false);
+      umma_commit(bar_mma);
+    }
+    wph ^= 1;
+    __syncwarp();
+    mbar_wait(bar_mma, mph);
+    mph ^= 1;
+    tc_fence_after();
+    if (tid == 0) {                         // W is free again: fetch W2[c] behind the epilogue
+      mbar_expect_tx(bar_w, 32768);
+      bulk_g2s(W, W2img + (size_t)c * 16384, 32768, bar_w);
+    }
+    __syncwarp();
+    // relu(hidden + b1) -> bf16 H image; this warp: rows 32q.., hidden columns [64h, 64h+64) = k-block h
+#pragma unroll
+    for (int cc = 0; cc < 2; ++cc) {
+      uint32_t v[32];
+      tmem_ld32(t_lane + h * 64 + cc * 32, v);
+      tmem_ld_wait();
+      const float* bb = b1 + c * 128 + h * 64 + cc * 32;
+#pragma unroll
+      for (int ch = 0; ch < 4; ++ch) {
+        uint4 o;
+        o.x = pack_bf16(fmaxf(__uint_as_float(v[8 * ch + 0]) + bb[8 * ch + 0], 0.f), fmaxf(__uint_as_float(v[8 * ch + 1]) + bb[8 * ch + 1], 0.f));
+        o.y = pack_bf16(fmaxf(__uint_as_float(v[8 * ch + 2]) + bb[8 * ch + 2], 0.f), fmaxf(__uint_as_float(v[8 * ch + 3]) + bb[8 * ch + 3], 0.f));
+        o.z = pack_bf16(fmaxf(__uint_as_float(v[8 * ch + 4]) + bb[8 * ch + 4], 0.f), fmaxf(__uint_as_float(v[8 * ch + 5]) + bb[8 * ch + 5], 0.f));
+        o.w = pack_bf16(fmaxf(__uint_as_float(v[8 * ch + 6]) + bb[8 * ch + 6], 0.f), fmaxf(__uint_as_float(v[8 * ch + 7]) + bb[8 * ch + 7], 0.f));
+        const uint32_t chunk = cc * 4 + ch;
+        *reinterpret_cast<uint4*>(H + h * 16384u + m * 128u + ((chunk ^ (m & 7u)) << 4)) = o;
+      }
+    }
+    fence_proxy_async();
+    tc_fence_before();
+    __syncthreads();
+    if (tid == 0) {                         // out += H . W2[c]^T -> TMEM cols [128,256)
+      mbar_wait(bar_w, wph);
+      tc_fence_after();
+      umma_tile(tmem + 128, smem_u32(H), smem_u32(W), 128, 2, c > 0);
+      umma_commit(bar_mma);
+    }
+    wph ^= 1;
+    __syncwarp();
+    mbar_wait(bar_mma, mph);
+    mph ^= 1;
+    tc_fence_after();
+    if (tid == 0 && c + 1 < nchunk) {
+      mbar_expect_tx(bar_w, 32768);
+      bulk_g2s(W, W1img + (size_t)(c + 1) * 16384, 32768, bar_w);
+    }
+    __syncwarp();
+  }
+  // epilogue: out (+ b2) -> fp32 staging over A|H (both dead), then coalesced residual update of p
+  uint8_t* S = sm;
+  tmem_to_stage(S, t_lane + 128 + h * 64, m, h * 64, b2);
+  tmem_to_stage(S, t_lane + 128 + h * 64 + 32, m, h * 64 + 32, b2);
+  tc_fence_before();
+  __syncthreads();
+  for (int r = warp; r < 128; r += 8) {
+    const uint32_t row = row0 + r;
+    if (row >= M) break;
+    const uint32_t cl = lane ^ (r & 31);
+    const float4 v = *reinterpret_cast<const float4*>(S + r * 512u + (lane << 4));
+    const float mk = rowmask[r];
+    float* dst = p + (size_t)row * 128 + cl * 4;
+    float4 pv = ld4(dst);
+    pv.x = (pv.x + v.x * mk) * mk;
+    pv.y = (pv.y + v.y * mk) * mk;
+    pv.z = (pv.z + v.z * mk) * mk;
+    pv.w = (pv.w + v.w * mk) * mk;
+    st4(dst, pv);
+  }
+  if (warp == 1) tmem_dealloc(tmem, 256);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Pixel tiles of the triangle kernels: a CTA owns 128 pixels = 2 consecutive rows x 64 consecutive
+// columns of one sample's N x N pair map; tile-local pixel m = 64 * ii + jj.
+//   tile -> (b, t2, jb);  row = 2 * t2 + ii,  col = 64 * jb + jj
+// K4 reads pixel (row, col) for the outgoing update and pixel (col, row) for the incoming one, so
+// that in both cases it emits A[row][k = col] (and B likewise) K-major and K5 is a plain A . B^T:
+//   outgoing x_ij = sum_k a_ik b_jk ;  incoming x_ij = sum_k a_ki b_kj = sum_k aT_ik bT_jk.
+// ---------------------------------------------------------------------------------------------
+struct PixTile { uint32_t b, t2, jb; };
+__device__ __forceinline__ PixTile pix_tile(uint32_t blk, int N, int Np) {
+  const uint32_t njb = Np >> 6, nt2 = (N + 1) >> 1;
+  PixTile t;
+  t.jb = blk % njb;
+  const uint32_t r = blk / njb;
+  t.t2 = r % nt2;
+  t.b = r / nt2;
+  return t;
+}
+
+// ---------------------------------------------------------------------------------------------
+// K4 trimul_proj_tc (triangular_multiplicative_update.py:97-103,107)
+//   Wimg: [a: 2 kb x 256 rows (a_p | a_g) x 64] 64K | [b: likewise] 64K | [g: 2 kb x 128 x 64] 32K
+//   bias: a_p | a_g | b_p | b_g | g   (5 x 128)
+//   a_out / b_out: [B][128 ch][Np/64 kb][Np rows][64] tile images (bf16);  g_out [B*N*N][128] bf16
+// Shared: A 32K | W 64K | barriers; 256 TMEM columns; 2 CTAs / SM.
+// ---------------------------------------------------------------------------------------------
+#define K4_SMEM (32768 + 65536 + 1024 + 64)
+
+// gated, masked projection of this thread's pixel for 32 channels -> 2-byte stores into the image
+__device__ __forceinline__ void k4_store_gated(uint32_t t_proj, const float* __restrict__ bp, const float* __restrict__ bg,
+                                               float mk, bool valid, bf16* __restrict__ dst, size_t ch_stride) {
+  uint32_t vp[32], vg[32];
+  tmem_ld32(t_proj, vp);
+  tmem_ld32(t_proj + 128, vg);
+  tmem_ld_wait();
+  if (!valid) return;
+#pragma unroll
+  for (int e = 0; e < 32; ++e) {
+    const float v = (__uint_as_float(vp[e]) + bp[e]) * sigmoidf_(__uint_as_float(vg[e]) + bg[e]) * mk;
+    dst[(size_t)e * ch_stride] = __float2bfloat16_rn(v);
+  }
+}
+
+__global__ void __launch_bounds__(256, 2) trimul_proj_tc_kernel(
+    const float* __restrict__ p, int N, int Np, const int* __restrict__ rmask, const float* __restrict__ ln_g,
+    const float* __restrict__ ln_b, const bf16* __restrict__ Wimg, const float* __restrict__ bias,
+    bf16* __restrict__ a_out, bf16* __restrict__ b_out, bf16* __restrict__ g_out, int incoming) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* sm = smem_base_1024(smem_raw);
+  uint8_t* A = sm;
+  uint8_t* W = sm + 32768;
+  uint64_t* bar_w = reinterpret_cast<uint64_t*>(sm + 98304);
+  uint64_t* bar_mma = bar_w + 1;
+  uint32_t* tslot = reinterpret_cast<uint32_t*>(bar_w + 2);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const PixTile T = pix_tile(blockIdx.x, N, Np);
+
+  if (tid == 0) {
+    mbar_init(bar_w, 1);
+    mbar_init(bar_mma, 1);
+    fence_mbar_init();
+    mbar_expect_tx(bar_w, 65536);
+    bulk_g2s(W, Wimg, 65536, bar_w);
+  }
+  if (warp == 1) tmem_alloc(tslot, 256);
+  const size_t sample = (size_t)T.b * N * N;
+  auto pixel_of = [&](uint32_t mm, bool& ok) -> size_t {   // source pixel (flat index into [B*N*N])
+    const uint32_t row = 2 * T.t2 + (mm >> 6), col = 64 * T.jb + (mm & 63);
+    ok = row < (uint32_t)N && col < (uint32_t)N;
+    return sample + (incoming ? (size_t)col * N + row : (size_t)row * N + col);
+  };
+  ln_rows_to_image(A, [&](int mm) -> const float* { bool ok; const size_t px = pixel_of(mm, ok); return ok ? p + px * 128 : nullptr; },
+                   ln_g, ln_b);
+  fence_proxy_async();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tslot;
+  const uint32_t q = warp & 3, h = warp >> 2, m = q * 32 + lane;
+  const uint32_t t_lane = tmem + ((q * 32u) << 16);
+  bool valid;
+  const size_t px = pixel_of(m, valid);
+  float mk = 0.f;
+  if (valid) {
+    const uint32_t row = 2 * T.t2 + (m >> 6), col = 64 * T.jb + (m & 63);
+    mk = (float)(rmask[T.b * N + row] * rmask[T.b * N + col]);
+  }
+  // destination of this pixel inside a channel plane of the operand image: row = 2 t2 + ii, k = col
+  const uint32_t orow = 2 * T.t2 + (m >> 6), jj = m & 63;
+  const size_t ch_stride = (size_t)(Np >> 6) * Np * 64;
+  const size_t img_off = ((size_t)T.b * 128 * (Np >> 6) + T.jb) * Np * 64 + (size_t)orow * 64 + (((jj >> 3) ^ (orow & 7)) << 3) + (jj & 7);
+
+  for (int part = 0; part < 2; ++part) {     // part 0 -> a, part 1 -> b
+    if (tid == 0) {
+      mbar_wait(bar_w, part);
+      tc_fence_after();
+      umma_tile(tmem, smem_u32(A), smem_u32(W), 256, 2, false);
+      umma_commit(bar_mma);
+    }
+    __syncwarp();
+    mbar_wait(bar_mma, part);
+    tc_fence_after();
+    if (tid == 0) {
+      const uint32_t bytes = part == 0 ? 65536u : 32768u;
+      mbar_expect_tx(bar_w, bytes);
+      bulk_g2s(W, Wimg + (size_t)(part + 1) * 32768, bytes, bar_w);
+    }
+    __syncwarp();
+    bf16* dst = (part == 0 ? a_out : b_out) + img_off;
+    const float* bp = bias + part * 256;
+#pragma unroll 1
+    for (int cc = 0; cc < 2; ++cc) {
+      const int c0 = h * 64 + cc * 32;       // channels [c0, c0+32)
+      k4_store_gated(t_lane + c0, bp + c0, bp + 128 + c0, mk, valid, dst + (size_t)c0 * ch_stride, ch_stride);
+    }
+    tc_fence_before();
+    __syncthreads();
+  }
+  // output gate g = sigmoid(linear_g(LN z)), pixel-major bf16
+  if (tid == 0) {
+    mbar_wait(bar_w, 0);
+    tc_fence_after();
+    umma_tile(tmem, smem_u32(A), smem_u32(W), 128, 2, false);
+    umma_commit(bar_mma);
+  }
+  __syncwarp();
+  mbar_wait(bar_mma, 0);
+  tc_fence_after();
+#pragma unroll 1
+  for (int cc = 0; cc < 2; ++cc) {
+    const int c0 = h * 64 + cc * 32;
+    uint32_t v[32];
+    tmem_ld32(t_lane + c0, v);
+    tmem_ld_wait();
+    if (valid) {
+      const float* bgp = bias + 512 + c0;
+      uint4* dst = reinterpret_cast<uint4*>(g_out + px * 128 + c0);
+#pragma unroll
+      for (int k4 = 0; k4 < 4; ++k4) {
+        uint4 o;
+        o.x = pack_bf16(sigmoidf_(__uint_as_float(v[8 * k4 + 0]) + bgp[8 * k4 + 0]), sigmoidf_(__uint_as_float(v[8 * k4 + 1]) + bgp[8 * k4 + 1]));
+        o.y = pack_bf16(sigmoidf_(__uint_as_float(v[8 * k4 + 2]) + bgp[8 * k4 + 2]), sigmoidf_(__uint_as_float(v[8 * k4 + 3]) + bgp[8 * k4 + 3]));
+        o.z = pack_bf16(sigmoidf_(__uint_as_float(v[8 * k4 + 4]) + bgp[8 * k4 + 4]), sigmoidf_(__uint_as_float(v[8 * k4 + 5]) + bgp[8 * k4 + 5]));
+        o.w = pack_bf16(sigmoidf_(__uint_as_float(v[8 * k4 + 6]) + bgp[8 * k4 + 6]), sigmoidf_(__uint_as_float(v[8 * k4 + 7]) + bgp[8 * k4 + 7]));
+        dst[k4] = o;
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem, 256);
+}
+
+// ---------------------------------------------------------------------------------------------
+// K5 trimul_contract_tc (triangular_multiplicative_update.py:57-82 with the operand orientation
+// fixed by K4): per (sample b, channel c): X[i][j] = sum_k A[i][k] B[j][k].
+// One CTA per (b, c, 128-row block, column block of NJ <= 256): warp 0 streams 64-wide k-blocks
+// of A (128 rows, 16 KB) and B (NJ rows) into a ring with cp.async.bulk, warp 1 issues the MMAs
+// into a 128 x NJ fp32 TMEM accumulator, all 8 warps run the epilogue (bf16 x, channel-major).
+// ---------------------------------------------------------------------------------------------
+#define K5_STAGES 2
+#define K5_STAGE_BYTES (16384 + 32768)
+#define K5_SMEM (K5_STAGES * K5_STAGE_BYTES + 1024 + 128)
+
+__global__ void __launch_bounds__(256, 2) trimul_contract_tc_kernel(const bf16* __restrict__ a, const bf16* __restrict__ b,
+                                                                    bf16* __restrict__ x, int N, int Np, int NJ) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* sm = smem_base_1024(smem_raw);
+  uint64_t* full = reinterpret_cast<uint64_t*>(sm + K5_STAGES * K5_STAGE_BYTES);
+  uint64_t* empty = full + K5_STAGES;
+  uint64_t* done = empty + K5_STAGES;
+  uint32_t* tslot = reinterpret_cast<uint32_t*>(done + 1);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int nkb = Np >> 6, nib = (Np + 127) >> 7, njb = (Np + NJ - 1) / NJ;
+  uint32_t blk = blockIdx.x;
+  const uint32_t jb = blk % njb; blk /= njb;
+  const uint32_t ib = blk % nib; blk /= nib;       // blk = b * 128 + c
+  const uint32_t nj = min((uint32_t)NJ, (uint32_t)Np - jb * NJ);   // columns of this block (multiple of 64)
+  const bf16* A0 = a + (size_t)blk * nkb * Np * 64 + (size_t)ib * 128 * 64;
+  const bf16* B0 = b + (size_t)blk * nkb * Np * 64 + (size_t)jb * NJ * 64;
+  const uint32_t a_rows = min(128u, (uint32_t)Np - ib * 128u);      // rows present in the plane (64 or 128)
+
+  if (tid == 0) {
+    for (int s = 0; s < K5_STAGES; ++s) { mbar_init(full + s, 1); mbar_init(empty + s, 1); }
+    mbar_init(done, 1);
+    fence_mbar_init();
+  }
+  if (warp == 2) tmem_alloc(tslot, 256);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tslot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      for (int kb = 0; kb < nkb; ++kb) {
+        const int s = kb % K5_STAGES;
+        if (kb >= K5_STAGES) mbar_wait(empty + s, ((kb / K5_STAGES) - 1) & 1);
+        uint8_t* st = sm + s * K5_STAGE_BYTES;
+        mbar_expect_tx(full + s, (a_rows + nj) * 128u);
+        bulk_g2s(st, A0 + (size_t)kb * Np * 64, a_rows * 128u, full + s);
+        bulk_g2s(st + 16384, B0 + (size_t)kb * Np * 64, nj * 128u, full + s);
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    if (lane == 0) {
+      const uint32_t idesc = umma_idesc(128, nj);
+      for (int kb = 0; kb < nkb; ++kb) {
+        const int s = kb % K5_STAGES;
+        mbar_wait(full + s, (kb / K5_STAGES) & 1);
+        tc_fence_after();
+        const uint32_t sa = smem_u32(sm + s * K5_STAGE_BYTES), sb = sa + 16384;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) umma(tmem, umma_desc(sa + k * 32), umma_desc(sb + k * 32), idesc, (kb | k) ? 1u : 0u);
+        umma_commit(empty + s);
+      }
+      umma_commit(done);
+    }
+    __syncwarp();
+  }
+  mbar_wait(done, 0);
+  tc_fence_after();
+  __syncwarp();
+  // epilogue: thread = output row i (TMEM lane); warps 0-3 take even 32-column groups, 4-7 odd ones
+  const uint32_t q = warp & 3, h = warp >> 2, i = ib * 128 + q * 32 + lane;
+  const uint32_t t_lane = tmem + ((q * 32u) << 16);
+  bf16* xrow = x + ((size_t)blk * Np + i) * Np + (size_t)jb * NJ;
+  for (uint32_t c0 = h * 32; c0 < nj; c0 += 64) {
+    uint32_t v[32];
+    tmem_ld32(t_lane + c0, v);
+    tmem_ld_wait();
+    if (i < (uint32_t)N) {
+      uint4* dst = reinterpret_cast<uint4*>(xrow + c0);
+#pragma unroll
+      for (int k4 = 0; k4 < 4; ++k4) {
+        uint4 o;
+        o.x = pack_bf16(__uint_as_float(v[8 * k4 + 0]), __uint_as_float(v[8 * k4 + 1]));
+        o.y = pack_bf16(__uint_as_float(v[8 * k4 + 2]), __uint_as_float(v[8 * k4 + 3]));
+        o.z = pack_bf16(__uint_as_float(v[8 * k4 + 4]), __uint_as_float(v[8 * k4 + 5]));
+        o.w = pack_bf16(__uint_as_float(v[8 * k4 + 6]), __uint_as_float(v[8 * k4 + 7]));
+        dst[k4] = o;
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) tmem_dealloc(tmem, 256);
+}
+
+// ---------------------------------------------------------------------------------------------
+// K6 trimul_out_tc (triangular_multiplicative_update.py:105-108 + residual, pair_transform_net.py:111-112)
+//   p[pixel] += (W_z LN_out(x[:, pixel]) + b_z) * g[pixel]
+// x is channel-major bf16 [B][128][Np][Np]; thread t loads pixel t & 127, channels [64 (t>>7), +64).
+// Shared: A 32K | Wz 32K (reused as the 64K fp32 staging tile) ; 128 TMEM columns ; 3 CTAs / SM.
+// ---------------------------------------------------------------------------------------------
+#define K6_SMEM (65536 + 1024 + 64 + 2048)
+
+__global__ void __launch_bounds__(256, 2) trimul_out_tc_kernel(
+    const bf16* __restrict__ x, const bf16* __restrict__ g, float* __restrict__ p, int N, int Np,
+    const float* __restrict__ ln_g, const float* __restrict__ ln_b, const bf16* __restrict__ Wzimg,
+    const float* __restrict__ bz) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* sm = smem_base_1024(smem_raw);
+  uint8_t* A = sm;
+  uint8_t* W = sm + 32768;
+  uint64_t* bar_w = reinterpret_cast<uint64_t*>(sm + 65536);
+  uint64_t* bar_mma = bar_w + 1;
+  uint32_t* tslot = reinterpret_cast<uint32_t*>(bar_w + 2);
+  float* red = reinterpret_cast<float*>(sm + 65536 + 64);     // [2 halves][128] partial sums, [128] pixel index
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const PixTile T = pix_tile(blockIdx.x, N, Np);
+  if (tid == 0) {
+    mbar_init(bar_w, 1);
+    mbar_init(bar_mma, 1);
+    fence_mbar_init();
+    mbar_expect_tx(bar_w, 32768);
+    bulk_g2s(W, Wzimg, 32768, bar_w);
+  }
+  if (warp == 1) tmem_alloc(tslot, 128);
+  {
+    const uint32_t mm = tid & 127, hh = tid >> 7;
+    const uint32_t row = 2 * T.t2 + (mm >> 6), col = 64 * T.jb + (mm & 63);
+    const bool ok = row < (uint32_t)N && col < (uint32_t)N;
+    const bf16* src = x + (((size_t)T.b * 128 + hh * 64) * Np + row) * Np + col;
+    const size_t cs = (size_t)Np * Np;
+    float v[64];
+    float sum = 0.f;
+#pragma unroll
+    for (int c = 0; c < 64; ++c) {
+      v[c] = ok ? __bfloat162float(src[(size_t)c * cs]) : 0.f;
+      sum += v[c];
+    }
+    red[hh * 128 + mm] = sum;
+    __syncthreads();
+    const float mean = (red[mm] + red[128 + mm]) * (1.f / 128.f);
+    float d2 = 0.f;
+#pragma unroll
+    for (int c = 0; c < 64; ++c) { v[c] -= mean; d2 = fmaf(v[c], v[c], d2); }
+    red[256 + hh * 128 + mm] = d2;
+    __syncthreads();
+    const float rstd = rsqrtf((red[256 + mm] + red[384 + mm]) * (1.f / 128.f) + 1e-5f);
+    const float* gg = ln_g + hh * 64;
+    const float* bb = ln_b + hh * 64;
+#pragma unroll
+    for (int ch = 0; ch < 8; ++ch) {
+      uint4 o;
+      o.x = pack_bf16(v[8 * ch + 0] * rstd * gg[8 * ch + 0] + bb[8 * ch + 0], v[8 * ch + 1] * rstd * gg[8 * ch + 1] + bb[8 * ch + 1]);
+      o.y = pack_bf16(v[8 * ch + 2] * rstd * gg[8 * ch + 2] + bb[8 * ch + 2], v[8 * ch + 3] * rstd * gg[8 * ch + 3] + bb[8 * ch + 3]);
+      o.z = pack_bf16(v[8 * ch + 4] * rstd * gg[8 * ch + 4] + bb[8 * ch + 4], v[8 * ch + 5] * rstd * gg[8 * ch + 5] + bb[8 * ch + 5]);
+      o.w = pack_bf16(v[8 * ch + 6] * rstd * gg[8 * ch + 6] + bb[8 * ch + 6], v[8 * ch + 7] * rstd * gg[8 * ch + 7] + bb[8 * ch + 7]);
+      *reinterpret_cast<uint4*>(A + hh * 16384u + mm * 128u + (((uint32_t)ch ^ (mm & 7u)) << 4)) = o;
+    }
+  }
+  fence_proxy_async();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tslot;
+  if (tid == 0) {
+    mbar_wait(bar_w, 0);
+    tc_fence_after();
+    umma_tile(tmem, smem_u32(A), smem_u32(W), 128, 2, false);
+    umma_commit(bar_mma);
+  }
+  __syncwarp();
+  mbar_wait(bar_mma, 0);
+  tc_fence_after();
+  const uint32_t q = warp & 3, h = warp >> 2, m = q * 32 + lane;
+  const uint32_t t_lane = tmem + ((q * 32u) << 16);
+  uint8_t* S = sm;
+  tmem_to_stage(S, t_lane + h * 64, m, h * 64, bz);
+  tmem_to_stage(S, t_lane + h * 64 + 32, m, h * 64 + 32, bz);
+  tc_fence_before();
+  __syncthreads();
+  for (int r = warp; r < 128; r += 8) {
+    const uint32_t row = 2 * T.t2 + (r >> 6), col = 64 * T.jb + (r & 63);
+    if (row >= (uint32_t)N || col >= (uint32_t)N) continue;
+    const size_t px = ((size_t)T.b * N + row) * N + col;
+    const uint32_t cl = lane ^ (r & 31);
+    const float4 v = *reinterpret_cast<const float4*>(S + r * 512u + (lane << 4));
+    const uint2 gv = *reinterpret_cast<const uint2*>(g + px * 128 + cl * 4);
+    const float2 g01 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&gv.x));
+    const float2 g23 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&gv.y));
+    float* dst = p + px * 128 + cl * 4;
+    float4 pv = ld4(dst);
+    pv.x += v.x * g01.x;
+    pv.y += v.y * g01.y;
+    pv.z += v.z * g23.x;
+    pv.w += v.w * g23.y;
+    st4(dst, pv);
+  }
+  if (warp == 1) tmem_dealloc(tmem, 128);
+}
+
+// ---------------------------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------------------------
+static uint16_t f2bf(float f) {   // round to nearest even
+  uint32_t u;
+  memcpy(&u, &f, 4);
+  if ((u & 0x7fffffffu) > 0x7f800000u) return 0x7fc0;
+  u += 0x7fffu + ((u >> 16) & 1u);
+  return (uint16_t)(u >> 16);
+}
+
+// rows x K (K % 64 == 0) fp32 matrix given by at(r, k) -> tile images [K/64][rows][64]
+template <typename F>
+static void pack_image(uint16_t* dst, int rows, int K, F at) {
+  for (int kb = 0; kb < K / 64; ++kb)
+    for (int r = 0; r < rows; ++r)
+      for (int k = 0; k < 64; ++k)
+        dst[(size_t)kb * rows * 64 + sw128_off(r, k) / 2] =
+            f2bf(at(r, kb * 64 + k));
+}
+
+static void* upload_bytes(gb_ctx* c, const void* src, size_t bytes) {
+  void* p = nullptr;
+  if (cudaMalloc(&p, bytes) != cudaSuccess) return nullptr;
+  if (cudaMemcpy(p, src, bytes, cudaMemcpyHostToDevice) != cudaSuccess) { cudaFree(p); return nullptr; }
+  c->weight_allocs.push_back(p);
+  return p;
+}
+
+int tc_init(gb_ctx* c) {
+  cudaError_t e;
+  if ((e = cudaFuncSetAttribute(pair_transition_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, K7_SMEM)) != cudaSuccess ||
+      (e = cudaFuncSetAttribute(trimul_proj_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, K4_SMEM)) != cudaSuccess ||
+      (e = cudaFuncSetAttribute(trimul_contract_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, K5_SMEM)) != cudaSuccess ||
+      (e = cudaFuncSetAttribute(trimul_out_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, K6_SMEM)) != cudaSuccess)
+    return gb_fail(c, GB_ERR_CUDA, "tc_init: cudaFuncSetAttribute failed: %s", cudaGetErrorString(e));
+  c->tc_state = new TcState();
+  return GB_OK;
+}
+
+void tc_destroy(gb_ctx* c) {
+  delete static_cast<TcState*>(c->tc_state);
+  c->tc_state = nullptr;
+}
+
+int tc_pack_trimul(gb_ctx* c, TriMulW& w, const std::vector<float>& ap, const std::vector<float>& ag,
+                   const std::vector<float>& bp, const std::vector<float>& bg, const std::vector<float>& lg,
+                   const std::vector<float>& lz, const std::vector<float>& apb, const std::vector<float>& agb,
+                   const std::vector<float>& bpb, const std::vector<float>& bgb, const std::vector<float>& lgb) {
+  std::vector<uint16_t> img(5 * 128 * 128);
+  pack_image(img.data(), 256, 128, [&](int r, int k) { return r < 128 ? ap[(size_t)r * 128 + k] : ag[(size_t)(r - 128) * 128 + k]; });
+  pack_image(img.data() + 32768, 256, 128, [&](int r, int k) { return r < 128 ? bp[(size_t)r * 128 + k] : bg[(size_t)(r - 128) * 128 + k]; });
+  pack_image(img.data() + 65536, 128, 128, [&](int r, int k) { return lg[(size_t)r * 128 + k]; });
+  w.tc_Wproj = upload_bytes(c, img.data(), img.size() * 2);
+  std::vector<uint16_t> wz(128 * 128);
+  pack_image(wz.data(), 128, 128, [&](int r, int k) { return lz[(size_t)r * 128 + k]; });
+  w.tc_Wz = upload_bytes(c, wz.data(), wz.size() * 2);
+  std::vector<float> bias;
+  for (const std::vector<float>* v : {&apb, &agb, &bpb, &bgb, &lgb}) bias.insert(bias.end(), v->begin(), v->end());
+  w.tc_bproj = (float*)upload_bytes(c, bias.data(), bias.size() * 4);
+  if (!w.tc_Wproj || !w.tc_Wz || !w.tc_bproj) return gb_fail(c, GB_ERR_CUDA, "tc_pack_trimul: device allocation failed");
+  return GB_OK;
+}
+
+int tc_pack_transition(gb_ctx* c, TransitionW& w, const std::vector<float>& w1, const std::vector<float>& w2) {
+  const int nh = c->d.pair_transition_n, HID = 128 * nh;
+  std::vector<uint16_t> i1((size_t)nh * 128 * 128), i2((size_t)nh * 128 * 128);
+  for (int t = 0; t < nh; ++t) {
+    pack_image(i1.data() + (size_t)t * 16384, 128, 128, [&](int r, int k) { return w1[(size_t)(t * 128 + r) * 128 + k]; });
+    pack_image(i2.data() + (size_t)t * 16384, 128, 128, [&](int r, int k) { return w2[(size_t)r * HID + t * 128 + k]; });
+  }
+  w.tc_W1 = upload_bytes(c, i1.data(), i1.size() * 2);
+  w.tc_W2 = upload_bytes(c, i2.data(), i2.size() * 2);
+  if (!w.tc_W1 || !w.tc_W2) return gb_fail(c, GB_ERR_CUDA, "tc_pack_transition: device allocation failed");
+  return GB_OK;
+}
+
+static size_t align256(size_t v) { return (v + 255) & ~(size_t)255; }
+
+size_t tc_workspace_bytes(const gb_ctx*, int B, int N) {
+  const size_t Np = (size_t)((N + 63) / 64) * 64;
+  const size_t plane = (size_t)B * 128 * Np * Np * 2;
+  return 3 * align256(plane) + align256((size_t)B * N * N * 128 * 2) + 1024;
+}
+
+int tc_bind_workspace(gb_ctx* c, void* base, size_t bytes, int B, int N) {
+  TcState* s = static_cast<TcState*>(c->tc_state);
+  const size_t Np = (size_t)((N + 63) / 64) * 64;
+  const size_t plane = align256((size_t)B * 128 * Np * Np * 2);
+  if (bytes < 3 * plane + align256((size_t)B * N * N * 128 * 2)) return gb_fail(c, GB_ERR_INVALID, "tc_bind_workspace: too small");
+  char* q = static_cast<char*>(base);
+  s->Np = (int)Np;
+  s->a = reinterpret_cast<bf16*>(q);
+  s->b = reinterpret_cast<bf16*>(q + plane);
+  s->x = reinterpret_cast<bf16*>(q + 2 * plane);
+  s->g = reinterpret_cast<bf16*>(q + 3 * plane);
+  s->ab_bytes = 2 * plane;
+  // the k-padding (N <= k < Np) of the operand images is never written by K4 and must read as zero
+  if (cudaMemset(q, 0, 3 * plane) != cudaSuccess) return gb_fail(c, GB_ERR_CUDA, "tc_bind_workspace: memset failed");
+  return GB_OK;
+}
+
+int tc_trimul(gb_ctx* c, const TriMulW& w, bool outgoing, float* p, cudaStream_t st) {
+  if (c->precision != GB_PREC_BF16) return gb_fail(c, GB_ERR_UNSUPPORTED, "tensor-core path: only bf16 precision is built in this revision");
+  TcState* s = static_cast<TcState*>(c->tc_state);
+  const int B = c->B, N = c->N, Np = s->Np;
+  const unsigned tiles = (unsigned)B * ((N + 1) / 2) * (Np / 64);
+  trimul_proj_tc_kernel<<<tiles, 256, K4_SMEM, st>>>(p, N, Np, c->mask, w.ln_in_g, w.ln_in_b, (const bf16*)w.tc_Wproj, w.tc_bproj,
+                                                     s->a, s->b, s->g, outgoing ? 0 : 1);
+  GB_LAUNCH_CHECK(c, "trimul_proj_tc");
+  const int NJ = 256;
+  const unsigned cgrid = (unsigned)B * 128 * ((Np + 127) / 128) * ((Np + NJ - 1) / NJ);
+  trimul_contract_tc_kernel<<<cgrid, 256, K5_SMEM, st>>>(s->a, s->b, s->x, N, Np, NJ);
+  GB_LAUNCH_CHECK(c, "trimul_contract_tc");
+  trimul_out_tc_kernel<<<tiles, 256, K6_SMEM, st>>>(s->x, s->g, p, N, Np, w.ln_out_g, w.ln_out_b, (const bf16*)w.tc_Wz, w.bz);
+  GB_LAUNCH_CHECK(c, "trimul_out_tc");
+  return GB_OK;
+}
+
+int tc_pair_transition(gb_ctx* c, const TransitionW& w, float* p, cudaStream_t st) {
+  if (c->precision != GB_PREC_BF16) return gb_fail(c, GB_ERR_UNSUPPORTED, "tensor-core path: only bf16 precision is built in this revision");
+  const size_t M = (size_t)c->B * c->N * c->N;
+  if (M >= (1ull << 31)) return gb_fail(c, GB_ERR_UNSUPPORTED, "pair map too large");
+  pair_transition_tc_kernel<<<(unsigned)((M + 127) / 128), 256, K7_SMEM, st>>>(p, (uint32_t)M, c->N, c->mask, w.ln_g, w.ln_b,
+                                                                              (const bf16*)w.tc_W1, w.b1, (const bf16*)w.tc_W2, w.b2,
+                                                                              c->d.pair_transition_n);
+  GB_LAUNCH_CHECK(c, "pair_transition_tc");
+  return GB_OK;
+}
+
+extern "C" int gb_dbg_tc_copy(gb_ctx* c, int which, void* dst, int64_t bytes) {
+  if (!c || !c->tc_state || !c->features_set) return GB_ERR_INVALID;
+  TcState* s = static_cast<TcState*>(c->tc_state);
+  if (!dst) return s->Np;
+  const size_t plane = (size_t)c->B * 128 * s->Np * s->Np * 2, gb = (size_t)c->B * c->N * c->N * 128 * 2;
+  const void* src = which == 0 ? (void*)s->a : which == 1 ? (void*)s->b : which == 2 ? (void*)s->x : which == 3 ? (void*)s->g : nullptr;
+  const size_t have = which == 3 ? gb : plane;
+  if (!src || bytes < 0 || (size_t)bytes > have) return gb_fail(c, GB_ERR_INVALID, "gb_dbg_tc_copy: bad arguments");
+  GB_CUDA(c, cudaMemcpy(dst, src, (size_t)bytes, cudaMemcpyDeviceToDevice));
+  return s->Np;
+}
