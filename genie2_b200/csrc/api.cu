@@ -284,6 +284,7 @@ extern "C" int gb_load_weights(gb_ctx* c, const gb_tensor* tensors, int n) {
   // ---- structure layers
   c->st.assign(d.n_structure_layer, StructLayerW());
   const int H = IPA_H, hc = IPA_H * IPA_C;
+  std::vector<const std::vector<float>*> wb_all, bb_all;
   for (int l = 0; l < d.n_structure_layer; ++l) {
     const std::string pre = "structure_net.net." + std::to_string(l);
     StructLayerW& w = c->st[l];
@@ -320,6 +321,8 @@ extern "C" int gb_load_weights(gb_ctx* c, const gb_tensor* tensors, int n) {
     w.Wout = upload(c, wo); w.bout = upload(c, bo);
     w.ln1_g = upload(c, l1g); w.ln1_b = upload(c, l1b); w.ln2_g = upload(c, l2g); w.ln2_b = upload(c, l2b);
     w.Wbb = upload(c, wbb); w.bbb = upload(c, bbb);
+    std::vector<const std::vector<float>*> w123;
+    wb_all.push_back(&wb); bb_all.push_back(&bb);
     for (int t = 0; t < d.n_structure_transition_layer; ++t) {
       const std::string q = pre + ".transition.layers." + std::to_string(t);
       const auto& a1 = G.get(q + ".linear_1.weight", {c_s, c_s});
@@ -332,7 +335,14 @@ extern "C" int gb_load_weights(gb_ctx* c, const gb_tensor* tensors, int n) {
       w.W1.push_back(upload(c, a1)); w.b1.push_back(upload(c, c1));
       w.W2.push_back(upload(c, a2)); w.b2.push_back(upload(c, c2));
       w.W3.push_back(upload(c, a3)); w.b3.push_back(upload(c, c3));
+      w123.push_back(&a1); w123.push_back(&a2); w123.push_back(&a3);
     }
+    int rc = tc_pack_struct_layer(c, l, concat({&wq, &wkv, &wqp, &wkvp}), wo, w123);
+    if (rc != GB_OK) return rc;
+  }
+  {
+    int rc = tc_pack_ipa_bias(c, wb_all, bb_all);
+    if (rc != GB_OK) return rc;
   }
   for (void* p : c->weight_allocs) if (!p) return gb_fail(c, GB_ERR_CUDA, "gb_load_weights: device allocation failed");
   c->host.clear();
@@ -557,6 +567,19 @@ static int run_ipa(gb_ctx* c, const StructLayerW& w, const float* s, const float
   return GB_OK;
 }
 
+int simt_points_to_global(gb_ctx* c, cudaStream_t st) {
+  const int R = c->B * c->N, NP = IPA_H * IPA_PQ + IPA_H * (IPA_PQ + IPA_PV);
+  ipa_points_to_global_kernel<<<(R * NP + 255) / 256, 256, 0, st>>>(c->qkv, c->rots_w, c->trans_w, R);
+  GB_LAUNCH_CHECK(c, "ipa_points_to_global");
+  return GB_OK;
+}
+int simt_backbone_update(gb_ctx* c, const StructLayerW& w, cudaStream_t st) {
+  const int R = c->B * c->N;
+  backbone_update_kernel<<<(R * 32 + 255) / 256, 256, 0, st>>>(c->s, w.Wbb, w.bbb, c->rots_w, c->trans_w, R, c->d.c_s);
+  GB_LAUNCH_CHECK(c, "backbone_update");
+  return GB_OK;
+}
+
 extern "C" int gb_frenet(gb_ctx* c, const float* trans, float* rots_out, void* stream) {
   int rc = check_ready(c, "gb_frenet");
   if (rc) return rc;
@@ -616,6 +639,10 @@ extern "C" int gb_denoise(gb_ctx* c, const float* rots, const float* trans, cons
   // StructureNet
   float* s = c->s;
   int state_idx = 1;
+  const bool tc_struct = c->precision == GB_PREC_BF16 && tc_struct_supported(c, N);
+  if (tc_struct) {
+    if ((rc = tc_structure_net(c, aux ? aux->states : nullptr, st))) return rc;
+  } else
   for (int blk = 0; blk < d.n_structure_block; ++blk)
     for (int l = 0; l < d.n_structure_layer; ++l) {
       const StructLayerW& w = c->st[l];

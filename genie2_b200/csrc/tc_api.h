@@ -18,3 +18,17 @@ int tc_bind_workspace(gb_ctx* c, void* base, size_t bytes, int B, int N);
 int tc_trimul(gb_ctx* c, const TriMulW& w, bool outgoing, float* p, cudaStream_t st);
 // p = (p + PairTransition(p)) * mask
 int tc_pair_transition(gb_ctx* c, const TransitionW& w, float* p, cudaStream_t st);
+
+// ---- structure network on tensor cores (tc_struct.cu)
+int tc_struct_init(gb_ctx* c);
+bool tc_struct_supported(const gb_ctx* c, int N);
+size_t tc_struct_workspace_bytes(const gb_ctx* c, int B, int N);
+int tc_struct_bind(gb_ctx* c, void* base, size_t bytes, int B, int N);
+int tc_pack_struct_layer(gb_ctx* c, int l, const std::vector<float>& wqkv, const std::vector<float>& wout,
+                         const std::vector<const std::vector<float>*>& w123);
+int tc_pack_ipa_bias(gb_ctx* c, const std::vector<const std::vector<float>*>& wb, const std::vector<const std::vector<float>*>& bb);
+// StructureNet.forward on c->s / c->p / c->rots_w / c->trans_w (bf16 mode); states_out may be NULL
+int tc_structure_net(gb_ctx* c, float* states_out, cudaStream_t st);
+// SIMT kernels of api.cu the tensor-core structure net reuses
+int simt_points_to_global(gb_ctx* c, cudaStream_t st);
+int simt_backbone_update(gb_ctx* c, const StructLayerW& w, cudaStream_t st);

@@ -134,4 +134,27 @@ __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
   return *reinterpret_cast<uint32_t*>(&v);
 }
 
+// ------------------------------------------------------------------ kernel-side conveniences
+// dynamic shared memory base rounded up to 1024 bytes (SWIZZLE_128B atoms)
+__device__ __forceinline__ uint8_t* smem_base_1024(uint8_t* raw) {
+  const uint32_t a = smem_u32(raw);
+  return raw + (((a + 1023u) & ~1023u) - a);
+}
+
+
+// Pixel tile of the triangle / IPA-prep kernels: 128 pixels = 2 consecutive rows x 64 consecutive
+// columns of one sample's N x N pair map; tile-local pixel m = 64 * ii + jj,
+// row = 2 * t2 + ii, col = 64 * jb + jj.
+struct PixTile { uint32_t b, t2, jb; };
+__device__ __forceinline__ PixTile pix_tile(uint32_t blk, int N, int Np) {
+  const uint32_t njb = Np >> 6, nt2 = (N + 1) >> 1;
+  PixTile t;
+  t.jb = blk % njb;
+  const uint32_t r = blk / njb;
+  t.t2 = r % nt2;
+  t.b = r / nt2;
+  return t;
+}
+
+
 }  // namespace tc

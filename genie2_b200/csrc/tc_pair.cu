@@ -13,28 +13,16 @@
 #include "common.cuh"
 #include "tc_api.h"
 #include "tc_common.cuh"
+#include "tc_host.h"
+#include "tc_state.h"
 
 using namespace tc;
 
-typedef __nv_bfloat16 bf16;
 
-struct TcState {
-  int Np = 0;            // N rounded up to a multiple of 64
-  bf16 *a = nullptr, *b = nullptr;   // [B][128][Np/64][Np][64] tile images
-  bf16 *x = nullptr;                 // [B][128][Np][Np]
-  bf16 *g = nullptr;                 // [B*N*N][128]
-  size_t ab_bytes = 0;
-};
 
 // ---------------------------------------------------------------------------------------------
 // shared helpers
 // ---------------------------------------------------------------------------------------------
-// dynamic shared memory base rounded up to 1024 bytes (SWIZZLE_128B atoms)
-__device__ __forceinline__ uint8_t* smem_base_1024(uint8_t* raw) {
-  const uint32_t a = smem_u32(raw);
-  return raw + (((a + 1023u) & ~1023u) - a);
-}
-
 // LayerNorm(128) of up to 128 pixel rows -> bf16 A operand image [2 kb][128 rows][64].
 // Warp w normalises rows 16w..16w+15, four at a time (four 512-byte coalesced loads in flight);
 // lane l holds channels 4l..4l+3.  src_row(m) returns the fp32 row pointer or nullptr (zero row).
@@ -225,17 +213,6 @@ __global__ void __launch_bounds__(256, 2) pair_transition_tc_kernel(
 // that in both cases it emits A[row][k = col] (and B likewise) K-major and K5 is a plain A . B^T:
 //   outgoing x_ij = sum_k a_ik b_jk ;  incoming x_ij = sum_k a_ki b_kj = sum_k aT_ik bT_jk.
 // ---------------------------------------------------------------------------------------------
-struct PixTile { uint32_t b, t2, jb; };
-__device__ __forceinline__ PixTile pix_tile(uint32_t blk, int N, int Np) {
-  const uint32_t njb = Np >> 6, nt2 = (N + 1) >> 1;
-  PixTile t;
-  t.jb = blk % njb;
-  const uint32_t r = blk / njb;
-  t.t2 = r % nt2;
-  t.b = r / nt2;
-  return t;
-}
-
 // ---------------------------------------------------------------------------------------------
 // K4 trimul_proj_tc (triangular_multiplicative_update.py:97-103,107)
 //   Wimg: [a: 2 kb x 256 rows (a_p | a_g) x 64] 64K | [b: likewise] 64K | [g: 2 kb x 128 x 64] 32K
@@ -575,32 +552,6 @@ __global__ void __launch_bounds__(256, 2) trimul_out_tc_kernel(
 // ---------------------------------------------------------------------------------------------
 // host side
 // ---------------------------------------------------------------------------------------------
-static uint16_t f2bf(float f) {   // round to nearest even
-  uint32_t u;
-  memcpy(&u, &f, 4);
-  if ((u & 0x7fffffffu) > 0x7f800000u) return 0x7fc0;
-  u += 0x7fffu + ((u >> 16) & 1u);
-  return (uint16_t)(u >> 16);
-}
-
-// rows x K (K % 64 == 0) fp32 matrix given by at(r, k) -> tile images [K/64][rows][64]
-template <typename F>
-static void pack_image(uint16_t* dst, int rows, int K, F at) {
-  for (int kb = 0; kb < K / 64; ++kb)
-    for (int r = 0; r < rows; ++r)
-      for (int k = 0; k < 64; ++k)
-        dst[(size_t)kb * rows * 64 + sw128_off(r, k) / 2] =
-            f2bf(at(r, kb * 64 + k));
-}
-
-static void* upload_bytes(gb_ctx* c, const void* src, size_t bytes) {
-  void* p = nullptr;
-  if (cudaMalloc(&p, bytes) != cudaSuccess) return nullptr;
-  if (cudaMemcpy(p, src, bytes, cudaMemcpyHostToDevice) != cudaSuccess) { cudaFree(p); return nullptr; }
-  c->weight_allocs.push_back(p);
-  return p;
-}
-
 int tc_init(gb_ctx* c) {
   cudaError_t e;
   if ((e = cudaFuncSetAttribute(pair_transition_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, K7_SMEM)) != cudaSuccess ||
@@ -609,7 +560,7 @@ int tc_init(gb_ctx* c) {
       (e = cudaFuncSetAttribute(trimul_out_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, K6_SMEM)) != cudaSuccess)
     return gb_fail(c, GB_ERR_CUDA, "tc_init: cudaFuncSetAttribute failed: %s", cudaGetErrorString(e));
   c->tc_state = new TcState();
-  return GB_OK;
+  return tc_struct_init(c);
 }
 
 void tc_destroy(gb_ctx* c) {
@@ -651,10 +602,10 @@ int tc_pack_transition(gb_ctx* c, TransitionW& w, const std::vector<float>& w1, 
 
 static size_t align256(size_t v) { return (v + 255) & ~(size_t)255; }
 
-size_t tc_workspace_bytes(const gb_ctx*, int B, int N) {
+size_t tc_workspace_bytes(const gb_ctx* c, int B, int N) {
   const size_t Np = (size_t)((N + 63) / 64) * 64;
   const size_t plane = (size_t)B * 128 * Np * Np * 2;
-  return 3 * align256(plane) + align256((size_t)B * N * N * 128 * 2) + 1024;
+  return 3 * align256(plane) + align256((size_t)B * N * N * 128 * 2) + 1024 + tc_struct_workspace_bytes(c, B, N);
 }
 
 int tc_bind_workspace(gb_ctx* c, void* base, size_t bytes, int B, int N) {
@@ -671,7 +622,8 @@ int tc_bind_workspace(gb_ctx* c, void* base, size_t bytes, int B, int N) {
   s->ab_bytes = 2 * plane;
   // the k-padding (N <= k < Np) of the operand images is never written by K4 and must read as zero
   if (cudaMemset(q, 0, 3 * plane) != cudaSuccess) return gb_fail(c, GB_ERR_CUDA, "tc_bind_workspace: memset failed");
-  return GB_OK;
+  const size_t used = 3 * plane + align256((size_t)B * N * N * 128 * 2);
+  return tc_struct_bind(c, q + used, bytes - used, B, N);
 }
 
 int tc_trimul(gb_ctx* c, const TriMulW& w, bool outgoing, float* p, cudaStream_t st) {

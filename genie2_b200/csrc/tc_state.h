@@ -1,0 +1,28 @@
+// State of the tensor-core modules (tc_pair.cu, tc_struct.cu), hung off gb_ctx::tc_state.
+#pragma once
+#include <cuda_bf16.h>
+
+#include <vector>
+
+typedef __nv_bfloat16 bf16;
+
+struct TcStructW {                 // per structure layer, bf16 operand images [K/64][N][64]
+  bf16 *Wqkv = nullptr, *Wout = nullptr;
+  std::vector<bf16*> W1, W2, W3;
+};
+
+struct TcState {
+  int Np = 0;                        // N rounded up to a multiple of 64
+  bf16 *a = nullptr, *b = nullptr;   // [B][128][Np/64][Np][64] tile images
+  bf16 *x = nullptr;                 // [B][128][Np][Np]
+  bf16 *g = nullptr;                 // [B*N*N][128]
+  size_t ab_bytes = 0;
+  // structure net
+  int Rp = 0;                        // B*N rounded up to a multiple of 128
+  bf16 *s_img = nullptr, *cat_img = nullptr, *ln1_img = nullptr, *h1_img = nullptr, *h2_img = nullptr;
+  bf16* z_img = nullptr;             // [B][N][2][Np][64]
+  float* pbias = nullptr;            // [L][B][N][12][Np]
+  bf16* Wb_img = nullptr;            // [2][96][64]  rows l*12+h, scaled by sqrt(1/3)
+  float* bias96 = nullptr;
+  std::vector<TcStructW> st;
+};

@@ -1,0 +1,681 @@
+// tcgen05 / TMEM implementation of the structure network for GB_PREC_BF16
+// (structure_net.py:76-116, invariant_point_attention.py:100-260, structure_transition.py:34-70).
+// Activations that feed a GEMM are kept as bf16 operand tile images [K/64][Rp rows][64]
+// (tc_common.cuh) written by the producing kernel's epilogue, so every GEMM moves both operands
+// with cp.async.bulk and never converts in its main loop.
+//   gemm_img_tc_kernel      C = A_img . W_img^T (+bias)(+residual)(relu) -> fp32 and/or bf16 image
+//   ln_img_kernel           row LayerNorm (or plain copy) -> fp32 and/or bf16 image
+//   ipa_prep_tc_kernel      once per eval: pair bias of all layers (one 128->96 GEMM over p) and
+//                           the bf16 copy of p laid out as MN-major operand images per query row
+//   ipa_attention_tc_kernel G query rows per CTA: logits / softmax / o / o_pt on CUDA cores,
+//                           o_pair = a . z on tensor cores (z^T as MN-major A, probabilities as B)
+#include <vector>
+
+#include "common.cuh"
+#include "ipa_dims.h"
+#include "tc_api.h"
+#include "tc_common.cuh"
+#include "tc_host.h"
+#include "tc_state.h"
+
+using namespace tc;
+
+// ---------------------------------------------------------------------------------------------
+// gemm_img_tc_kernel: one CTA = 128 rows x 64 output columns; warp 0 streams k-blocks of A (16 KB)
+// and W (8 KB) through an 8-stage mbarrier ring, warp 1 issues the MMAs, all warps run the epilogue.
+// ---------------------------------------------------------------------------------------------
+#define GI_STAGES 8
+#define GI_STAGE_BYTES (16384 + 8192)
+#define GI_SMEM (GI_STAGES * GI_STAGE_BYTES + 1024 + 256)
+
+struct GemmImgArgs {
+  const bf16* A;      // [nkb][Rp][64]
+  const bf16* W;      // [nkb][Nw][64]
+  const float* bias;  // [Nw] or null
+  const float* res;   // fp32 residual [R][ldr] or null
+  float* C;           // fp32 out [R][ldc] or null
+  bf16* O;            // bf16 image out [Nw/64][Rp][64] or null
+  int Rp, Nw, nkb, R, ldc, ldr, relu;
+};
+
+__global__ void __launch_bounds__(256, 1) gemm_img_tc_kernel(const GemmImgArgs g) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* sm = smem_base_1024(smem_raw);
+  uint64_t* full = reinterpret_cast<uint64_t*>(sm + GI_STAGES * GI_STAGE_BYTES);
+  uint64_t* empty = full + GI_STAGES;
+  uint64_t* done = empty + GI_STAGES;
+  uint32_t* tslot = reinterpret_cast<uint32_t*>(done + 1);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const uint32_t n0 = blockIdx.x * 64u, m0 = blockIdx.y * 128u;
+  if (tid == 0) {
+    for (int s = 0; s < GI_STAGES; ++s) { mbar_init(full + s, 1); mbar_init(empty + s, 1); }
+    mbar_init(done, 1);
+    fence_mbar_init();
+  }
+  if (warp == 2) tmem_alloc(tslot, 64);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tslot;
+  if (warp == 0) {
+    if (lane == 0) {
+      for (int kb = 0; kb < g.nkb; ++kb) {
+        const int s = kb % GI_STAGES;
+        if (kb >= GI_STAGES) mbar_wait(empty + s, ((kb / GI_STAGES) - 1) & 1);
+        uint8_t* st = sm + s * GI_STAGE_BYTES;
+        mbar_expect_tx(full + s, GI_STAGE_BYTES);
+        bulk_g2s(st, g.A + ((size_t)kb * g.Rp + m0) * 64, 16384, full + s);
+        bulk_g2s(st + 16384, g.W + ((size_t)kb * g.Nw + n0) * 64, 8192, full + s);
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    if (lane == 0) {
+      const uint32_t idesc = umma_idesc(128, 64);
+      for (int kb = 0; kb < g.nkb; ++kb) {
+        const int s = kb % GI_STAGES;
+        mbar_wait(full + s, (kb / GI_STAGES) & 1);
+        tc_fence_after();
+        const uint32_t sa = smem_u32(sm + s * GI_STAGE_BYTES), sb = sa + 16384;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) umma(tmem, umma_desc(sa + k * 32), umma_desc(sb + k * 32), idesc, (kb | k) ? 1u : 0u);
+        umma_commit(empty + s);
+      }
+      umma_commit(done);
+    }
+    __syncwarp();
+  }
+  mbar_wait(done, 0);
+  tc_fence_after();
+  __syncwarp();
+  const uint32_t q = warp & 3, h = warp >> 2, m = m0 + q * 32 + lane, c0 = n0 + h * 32;
+  uint32_t v[32];
+  tmem_ld32(tmem + ((q * 32u) << 16) + h * 32, v);
+  tmem_ld_wait();
+  if (m < (uint32_t)g.R) {
+    float o[32];
+#pragma unroll
+    for (int e = 0; e < 32; ++e) {
+      float t = __uint_as_float(v[e]) + (g.bias ? g.bias[c0 + e] : 0.f);
+      if (g.relu) t = fmaxf(t, 0.f);
+      o[e] = t;
+    }
+    if (g.res) {
+      const float4* r4 = reinterpret_cast<const float4*>(g.res + (size_t)m * g.ldr + c0);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) { const float4 r = r4[e]; o[4 * e] += r.x; o[4 * e + 1] += r.y; o[4 * e + 2] += r.z; o[4 * e + 3] += r.w; }
+    }
+    if (g.C) {
+      float4* c4 = reinterpret_cast<float4*>(g.C + (size_t)m * g.ldc + c0);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) c4[e] = make_float4(o[4 * e], o[4 * e + 1], o[4 * e + 2], o[4 * e + 3]);
+    }
+    if (g.O) {
+      uint8_t* row = reinterpret_cast<uint8_t*>(g.O + ((size_t)blockIdx.x * g.Rp + m) * 64);
+#pragma unroll
+      for (int ch = 0; ch < 4; ++ch) {
+        uint4 w;
+        w.x = pack_bf16(o[8 * ch + 0], o[8 * ch + 1]);
+        w.y = pack_bf16(o[8 * ch + 2], o[8 * ch + 3]);
+        w.z = pack_bf16(o[8 * ch + 4], o[8 * ch + 5]);
+        w.w = pack_bf16(o[8 * ch + 6], o[8 * ch + 7]);
+        *reinterpret_cast<uint4*>(row + (((h * 4 + ch) ^ (m & 7u)) << 4)) = w;
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) tmem_dealloc(tmem, 64);
+}
+
+// ---------------------------------------------------------------------------------------------
+// ln_img_kernel: one warp per row of [R, C] (C % 128 == 0, C <= 512): optional LayerNorm, then any
+// of: fp32 out, second fp32 out (the 'states' list), bf16 operand image [C/64][Rp][64].
+// ---------------------------------------------------------------------------------------------
+__global__ void ln_img_kernel(const float* __restrict__ in, float* __restrict__ out, float* __restrict__ out2,
+                              bf16* __restrict__ img, const float* __restrict__ gamma, const float* __restrict__ beta,
+                              int R, int C, int Rp, int normalize) {
+  const int row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (row >= R) return;
+  const int nq = C >> 7;
+  float4 v[4];
+  float sum = 0.f;
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    v[q] = q < nq ? ld4(in + (size_t)row * C + (q * 32 + lane) * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
+    sum += v[q].x + v[q].y + v[q].z + v[q].w;
+  }
+  if (normalize) {
+    const float mean = warp_sum(sum) / (float)C;
+    float d2 = 0.f;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      if (q >= nq) break;
+      v[q].x -= mean; v[q].y -= mean; v[q].z -= mean; v[q].w -= mean;
+      d2 += v[q].x * v[q].x + v[q].y * v[q].y + v[q].z * v[q].z + v[q].w * v[q].w;
+    }
+    const float rstd = rsqrtf(warp_sum(d2) / (float)C + 1e-5f);
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      if (q >= nq) break;
+      const float4 g4 = ld4(gamma + (q * 32 + lane) * 4), b4 = ld4(beta + (q * 32 + lane) * 4);
+      v[q].x = v[q].x * rstd * g4.x + b4.x; v[q].y = v[q].y * rstd * g4.y + b4.y;
+      v[q].z = v[q].z * rstd * g4.z + b4.z; v[q].w = v[q].w * rstd * g4.w + b4.w;
+    }
+  }
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    if (q >= nq) break;
+    const int c = (q * 32 + lane) * 4;
+    if (out) st4(out + (size_t)row * C + c, v[q]);
+    if (out2) st4(out2 + (size_t)row * C + c, v[q]);
+    if (img) {
+      uint2 o;
+      o.x = pack_bf16(v[q].x, v[q].y);
+      o.y = pack_bf16(v[q].z, v[q].w);
+      uint8_t* dst = reinterpret_cast<uint8_t*>(img + ((size_t)(c >> 6) * Rp + row) * 64);
+      *reinterpret_cast<uint2*>(dst + (((uint32_t)((c & 63) >> 3) ^ (row & 7u)) << 4) + ((c & 7) >> 2) * 8) = o;
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// ipa_prep_tc_kernel (once per denoiser eval, after the pair stack).  p does not change across the
+// structure layers, so for all layers l at once:
+//   pbias[l][b][i][h][j] = sqrt(1/3) * (linear_b_l(z_ij)[h]) + 1e5 * (m_i m_j - 1)
+//                                          (invariant_point_attention.py:184-190,206-212)
+//   z_img[b][i][mb][j][64]  bf16 copy of z_ij[64 mb ..], chunk-swizzled by j & 7: for a fixed query
+//                           row i this is the MN-major (channel-contiguous) A operand of o_pair.
+// One CTA = 128 pixels (2 rows x 64 cols); Wb image [2 kb][96 rows = l*12+h][64]; bias96 pre-scaled.
+// ---------------------------------------------------------------------------------------------
+#define PREP_SMEM (32768 + 24576 + 1024 + 64)
+
+__global__ void __launch_bounds__(256, 2) ipa_prep_tc_kernel(const float* __restrict__ p, int B, int N, int Np,
+                                                             const int* __restrict__ rmask, const bf16* __restrict__ Wimg,
+                                                             const float* __restrict__ bias96, float* __restrict__ pbias,
+                                                             bf16* __restrict__ z_img, int ncol) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* sm = smem_base_1024(smem_raw);
+  uint8_t* A = sm;
+  uint8_t* W = sm + 32768;
+  uint64_t* bar_w = reinterpret_cast<uint64_t*>(sm + 32768 + 24576);
+  uint64_t* bar_mma = bar_w + 1;
+  uint32_t* tslot = reinterpret_cast<uint32_t*>(bar_w + 2);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const PixTile T = pix_tile(blockIdx.x, N, Np);
+  if (tid == 0) {
+    mbar_init(bar_w, 1);
+    mbar_init(bar_mma, 1);
+    fence_mbar_init();
+    mbar_expect_tx(bar_w, 24576);
+    bulk_g2s(W, Wimg, 24576, bar_w);
+  }
+  if (warp == 1) tmem_alloc(tslot, 128);
+  {
+    const uint32_t kb = lane >> 4, chunk = (lane & 15) >> 1, half = lane & 1;
+#pragma unroll
+    for (int it = 0; it < 4; ++it) {
+      float4 v[4];
+      bool ok[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const uint32_t m = warp * 16 + it * 4 + u, i = 2 * T.t2 + (m >> 6), j = 64 * T.jb + (m & 63);
+        ok[u] = i < (uint32_t)N && j < (uint32_t)N;
+        v[u] = ok[u] ? ld4(p + (((size_t)T.b * N + i) * N + j) * 128 + lane * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const uint32_t m = warp * 16 + it * 4 + u, i = 2 * T.t2 + (m >> 6), j = 64 * T.jb + (m & 63);
+        uint2 o;
+        o.x = pack_bf16(v[u].x, v[u].y);
+        o.y = pack_bf16(v[u].z, v[u].w);
+        const uint32_t inrow = ((chunk ^ (m & 7u)) << 4) + half * 8u;
+        *reinterpret_cast<uint2*>(A + kb * 16384u + m * 128u + inrow) = o;
+        if (ok[u]) {
+          uint8_t* zr = reinterpret_cast<uint8_t*>(z_img) + ((((size_t)T.b * N + i) * 2 + kb) * Np + j) * 128;
+          *reinterpret_cast<uint2*>(zr + inrow) = o;
+        }
+      }
+    }
+  }
+  fence_proxy_async();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tslot;
+  if (tid == 0) {
+    mbar_wait(bar_w, 0);
+    tc_fence_after();
+    umma_tile(tmem, smem_u32(A), smem_u32(W), 96, 2, false);
+    umma_commit(bar_mma);
+  }
+  __syncwarp();
+  mbar_wait(bar_mma, 0);
+  tc_fence_after();
+  const uint32_t q = warp & 3, h = warp >> 2, m = q * 32 + lane;
+  const uint32_t i = 2 * T.t2 + (m >> 6), j = 64 * T.jb + (m & 63);
+  const bool valid = i < (uint32_t)N && j < (uint32_t)N;
+  float mterm = 0.f;
+  if (valid) mterm = 1e5f * ((float)(rmask[T.b * N + i] * rmask[T.b * N + j]) - 1.f);
+  for (int cc = h; cc < 3; cc += 2) {          // warps 0-3: column chunks 0 and 2; warps 4-7: chunk 1
+    uint32_t v[32];
+    tmem_ld32(tmem + ((q * 32u) << 16) + cc * 32, v);
+    tmem_ld_wait();
+    if (valid) {
+#pragma unroll
+      for (int e = 0; e < 32; ++e) {
+        const int n = cc * 32 + e;
+        if (n < ncol) {
+          const int l = n / 12, hh = n - l * 12;
+          pbias[((((size_t)l * B + T.b) * N + i) * 12 + hh) * Np + j] = __uint_as_float(v[e]) + bias96[n] + mterm;
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem, 128);
+}
+
+// ---------------------------------------------------------------------------------------------
+// ipa_attention_tc_kernel (invariant_point_attention.py:181-259), Np <= 256.
+// One CTA = IA_G consecutive query rows i0.. of sample b (256 threads):
+//   1. logits: thread j owns key j; per head it loads k / k_pts of its key once (registers) and scores
+//      it against the IA_G queries (q, q_pts broadcast from shared memory); + precomputed pair bias.
+//   2. softmax over j per (head, query) in shared memory; probabilities are kept fp32 (for o, o_pt)
+//      and written as bf16 B-operand images a_img[g] = [Np/64 kb][16 rows = head][64 j].
+//   3. warp 0 streams z_img of each query row in 64-key chunks (2 x 8 KB, cp.async.bulk, 4-deep ring),
+//      warp 1 issues D_g[c][h] += zT[c][j] . a_g[h][j]  (M = 128 channels, N = 16, MN-major A),
+//      warps 2-7 meanwhile accumulate o and o_pt on CUDA cores.
+//   4. epilogue: inverse frame + norms for o_pt; everything is written as bf16 straight into the
+//      operand image of the output projection (cat_img, K = 2112: o | o_pt.x | .y | .z | |o_pt| | o_pair).
+// ---------------------------------------------------------------------------------------------
+#define IA_G 4
+#define IA_ZRING 4
+#define IA_OFF_AIMG 65536
+#define IA_OFF_P (IA_OFF_AIMG + IA_G * 8192)
+#define IA_OFF_QS (IA_OFF_P + 12 * 256 * 16)
+#define IA_OFF_RED (IA_OFF_QS + IA_G * 12 * 28 * 4)
+#define IA_OFF_FR (IA_OFF_RED + IA_G * 288 * 4)
+#define IA_OFF_BAR (IA_OFF_FR + IA_G * 12 * 4)
+#define IA_SMEM (IA_OFF_BAR + 128 + 1024)
+
+// MN-major A descriptor: 64-channel blocks LBO bytes apart, 8-key groups 1024 B apart, SWIZZLE_128B
+__device__ __forceinline__ uint64_t umma_desc_mn(uint32_t saddr, uint32_t lbo_bytes) {
+  return (uint64_t)((saddr & 0x3FFFFu) >> 4) | ((uint64_t)(lbo_bytes >> 4) << 16) | (64ull << 32) | (1ull << 46) | (2ull << 61);
+}
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&v)[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+        "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+      : "r"(taddr)
+      : "memory");
+}
+// 2-byte store of element k of row r of a [.][Rp][64] operand image
+__device__ __forceinline__ void img_store(bf16* img, int Rp, uint32_t r, uint32_t k, float v) {
+  uint8_t* base = reinterpret_cast<uint8_t*>(img + ((size_t)(k >> 6) * Rp + r) * 64);
+  *reinterpret_cast<bf16*>(base + ((((k & 63) >> 3) ^ (r & 7u)) << 4) + ((k & 7) << 1)) = __float2bfloat16_rn(v);
+}
+
+__global__ void __launch_bounds__(256, 1) ipa_attention_tc_kernel(
+    const float* __restrict__ qkv, const float* __restrict__ pbias, const bf16* __restrict__ z_img,
+    const float* __restrict__ rots, const float* __restrict__ trans, const float* __restrict__ hw,
+    bf16* __restrict__ cat_img, int N, int Np, int Rp) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* sm = smem_base_1024(smem_raw);
+  uint8_t* zring = sm;
+  uint8_t* aimg = sm + IA_OFF_AIMG;
+  float* P = reinterpret_cast<float*>(sm + IA_OFF_P);          // [12 h][Np j][IA_G]
+  float* qs = reinterpret_cast<float*>(sm + IA_OFF_QS);        // [g][h][28]: q*sc (16) | q_pts c*4+p (12)
+  float* red = reinterpret_cast<float*>(sm + IA_OFF_RED);      // [g][288] o_pt, global frame
+  float* fr = reinterpret_cast<float*>(sm + IA_OFF_FR);        // [g][12] R (9) t (3)
+  uint64_t* full = reinterpret_cast<uint64_t*>(sm + IA_OFF_BAR);
+  uint64_t* empty = full + IA_ZRING;
+  uint64_t* done = empty + IA_ZRING;                           // [IA_G]
+  uint32_t* tslot = reinterpret_cast<uint32_t*>(done + IA_G);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int b = blockIdx.y, i0 = blockIdx.x * IA_G;
+  const int ng = min(IA_G, N - i0), nch = Np >> 6;
+  const size_t rowb = (size_t)b * N;
+
+  if (tid == 0) {
+    for (int s = 0; s < IA_ZRING; ++s) { mbar_init(full + s, 1); mbar_init(empty + s, 1); }
+    for (int g = 0; g < IA_G; ++g) mbar_init(done + g, 1);
+    fence_mbar_init();
+    // prefetch the first ring of z chunks: independent of everything this kernel computes
+    const int tot = ng * nch;
+    for (int it = 0; it < min(tot, IA_ZRING); ++it) {
+      const int g = it / nch, ch = it - g * nch;
+      const uint8_t* src = reinterpret_cast<const uint8_t*>(z_img) + ((rowb + i0 + g) * 2 * Np + ch * 64) * 128;
+      mbar_expect_tx(full + it, 16384);
+      bulk_g2s(zring + it * 16384, src, 8192, full + it);
+      bulk_g2s(zring + it * 16384 + 8192, src + (size_t)Np * 128, 8192, full + it);
+    }
+  }
+  if (warp == 2) tmem_alloc(tslot, 64);
+  // q, q_pts of the IA_G queries; a_img cleared (rows 12..15 and padded keys must read as zero)
+  const float sc_qk = sqrtf(1.f / (3.f * IPA_C));
+  for (int e = tid; e < IA_G * 12 * 28; e += 256) {
+    const int g = e / 336, r = e - g * 336, h = r / 28, x = r - h * 28;
+    float v = 0.f;
+    if (g < ng) {
+      const float* row = qkv + (rowb + i0 + g) * IPA_QKV;
+      v = x < 16 ? row[h * 16 + x] * sc_qk : row[IPA_OFF_QP + ((x - 16) >> 2) * 48 + h * 4 + ((x - 16) & 3)];
+    }
+    qs[e] = v;
+  }
+  for (int e = tid; e < IA_G * 8192 / 16; e += 256) reinterpret_cast<uint4*>(aimg)[e] = make_uint4(0, 0, 0, 0);
+  if (tid < IA_G * 12) {
+    const int g = tid / 12, x = tid - g * 12;
+    fr[tid] = g < ng ? (x < 9 ? rots[(rowb + i0 + g) * 9 + x] : trans[(rowb + i0 + g) * 3 + x - 9]) : 0.f;
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tslot;
+
+  // ---- 1. logits
+  {
+    const int j = tid;
+    const bool kv = j < N;
+    const float* krow = qkv + (rowb + (kv ? j : 0)) * IPA_QKV;
+    for (int h = 0; h < 12; ++h) {
+      float4 lg = make_float4(-3.0e38f, -3.0e38f, -3.0e38f, -3.0e38f);
+      if (kv) {
+        float k[28];
+#pragma unroll
+        for (int e = 0; e < 4; ++e) { const float4 t = ld4(krow + IPA_OFF_KV + h * 32 + e * 4); k[4 * e] = t.x; k[4 * e + 1] = t.y; k[4 * e + 2] = t.z; k[4 * e + 3] = t.w; }
+#pragma unroll
+        for (int c = 0; c < 3; ++c) { const float4 t = ld4(krow + IPA_OFF_KVP + c * 144 + h * 12); k[16 + 4 * c] = t.x; k[17 + 4 * c] = t.y; k[18 + 4 * c] = t.z; k[19 + 4 * c] = t.w; }
+        const float gam = -0.5f * hw[h];
+        float out[IA_G];
+#pragma unroll
+        for (int g = 0; g < IA_G; ++g) {
+          const float4* q4 = reinterpret_cast<const float4*>(qs + (g * 12 + h) * 28);
+          float qk = 0.f, d2 = 0.f;
+#pragma unroll
+          for (int e = 0; e < 4; ++e) { const float4 t = q4[e]; qk = fmaf(t.x, k[4 * e], qk); qk = fmaf(t.y, k[4 * e + 1], qk); qk = fmaf(t.z, k[4 * e + 2], qk); qk = fmaf(t.w, k[4 * e + 3], qk); }
+#pragma unroll
+          for (int e = 4; e < 7; ++e) {
+            const float4 t = q4[e];
+            const float dx = t.x - k[4 * e], dy = t.y - k[4 * e + 1], dz = t.z - k[4 * e + 2], dw = t.w - k[4 * e + 3];
+            d2 = fmaf(dx, dx, d2); d2 = fmaf(dy, dy, d2); d2 = fmaf(dz, dz, d2); d2 = fmaf(dw, dw, d2);
+          }
+          float pb = 0.f;
+          if (g < ng) pb = pbias[((rowb + i0 + g) * 12 + h) * Np + j];
+          out[g] = qk + pb + gam * d2;
+        }
+        lg = make_float4(out[0], out[1], out[2], out[3]);
+      }
+      if (j < Np) *reinterpret_cast<float4*>(P + ((size_t)h * Np + j) * IA_G) = lg;
+    }
+  }
+  __syncthreads();
+  // ---- 2. softmax over j; warp w owns heads w, w+8
+  for (int h = warp; h < 12; h += 8) {
+    float4 mx = make_float4(-3.0e38f, -3.0e38f, -3.0e38f, -3.0e38f);
+    for (int j = lane; j < Np; j += 32) {
+      const float4 t = *reinterpret_cast<const float4*>(P + ((size_t)h * Np + j) * IA_G);
+      mx.x = fmaxf(mx.x, t.x); mx.y = fmaxf(mx.y, t.y); mx.z = fmaxf(mx.z, t.z); mx.w = fmaxf(mx.w, t.w);
+    }
+    mx.x = warp_max(mx.x); mx.y = warp_max(mx.y); mx.z = warp_max(mx.z); mx.w = warp_max(mx.w);
+    float4 sum = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int j = lane; j < Np; j += 32) {
+      float4* pp = reinterpret_cast<float4*>(P + ((size_t)h * Np + j) * IA_G);
+      float4 t = *pp;
+      t.x = __expf(t.x - mx.x); t.y = __expf(t.y - mx.y); t.z = __expf(t.z - mx.z); t.w = __expf(t.w - mx.w);
+      sum.x += t.x; sum.y += t.y; sum.z += t.z; sum.w += t.w;
+      *pp = t;
+    }
+    const float ix = 1.f / warp_sum(sum.x), iy = 1.f / warp_sum(sum.y), iz = 1.f / warp_sum(sum.z), iw = 1.f / warp_sum(sum.w);
+    for (int j = lane; j < Np; j += 32) {
+      float4* pp = reinterpret_cast<float4*>(P + ((size_t)h * Np + j) * IA_G);
+      float4 t = *pp;
+      t.x *= ix; t.y *= iy; t.z *= iz; t.w *= iw;
+      *pp = t;
+      const uint32_t off = (j >> 6) * 2048u + h * 128u + (((((uint32_t)j & 63) >> 3) ^ ((uint32_t)h & 7u)) << 4) + ((j & 7) << 1);
+      *reinterpret_cast<bf16*>(aimg + off) = __float2bfloat16_rn(t.x);
+      *reinterpret_cast<bf16*>(aimg + 8192 + off) = __float2bfloat16_rn(t.y);
+      *reinterpret_cast<bf16*>(aimg + 16384 + off) = __float2bfloat16_rn(t.z);
+      *reinterpret_cast<bf16*>(aimg + 24576 + off) = __float2bfloat16_rn(t.w);
+    }
+  }
+  fence_proxy_async();
+  __syncthreads();
+  // ---- 3. role split
+  if (warp == 0) {
+    if (lane == 0) {
+      const int tot = ng * nch;
+      for (int it = IA_ZRING; it < tot; ++it) {
+        const int s = it % IA_ZRING, g = it / nch, ch = it - g * nch;
+        mbar_wait(empty + s, ((it / IA_ZRING) - 1) & 1);
+        const uint8_t* src = reinterpret_cast<const uint8_t*>(z_img) + ((rowb + i0 + g) * 2 * Np + ch * 64) * 128;
+        mbar_expect_tx(full + s, 16384);
+        bulk_g2s(zring + s * 16384, src, 8192, full + s);
+        bulk_g2s(zring + s * 16384 + 8192, src + (size_t)Np * 128, 8192, full + s);
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    if (lane == 0) {
+      const uint32_t idesc = umma_idesc(128, 16) | (1u << 15);     // A is MN-major
+      int it = 0;
+      for (int g = 0; g < ng; ++g) {
+        for (int ch = 0; ch < nch; ++ch, ++it) {
+          const int s = it % IA_ZRING;
+          mbar_wait(full + s, (it / IA_ZRING) & 1);
+          tc_fence_after();
+          const uint32_t za = smem_u32(zring + s * 16384), ab = smem_u32(aimg + g * 8192 + ch * 2048);
+#pragma unroll
+          for (int k = 0; k < 4; ++k)
+            umma(tmem + g * 16, umma_desc_mn(za + k * 2048, 8192), umma_desc(ab + k * 32), idesc, (ch | k) ? 1u : 0u);
+          umma_commit(empty + s);
+        }
+        umma_commit(done + g);
+      }
+    }
+    __syncwarp();
+  } else {
+    // o[h][16] and o_pt[h][8][3] (global frame): 480 outputs per query over 192 threads
+    for (int x = tid - 64; x < 480; x += 192) {
+      const int h = x / 40, e = x - h * 40;
+      const int off = e < 16 ? IPA_OFF_KV + h * 32 + 16 + e : IPA_OFF_KVP + ((e - 16) >> 3) * 144 + h * 12 + 4 + ((e - 16) & 7);
+      const float* src = qkv + rowb * IPA_QKV + off;
+      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int j = 0; j < N; ++j) {
+        const float v = src[(size_t)j * IPA_QKV];
+        const float4 a = *reinterpret_cast<const float4*>(P + ((size_t)h * Np + j) * IA_G);
+        acc.x = fmaf(a.x, v, acc.x); acc.y = fmaf(a.y, v, acc.y); acc.z = fmaf(a.z, v, acc.z); acc.w = fmaf(a.w, v, acc.w);
+      }
+      const float o4[4] = {acc.x, acc.y, acc.z, acc.w};
+      for (int g = 0; g < ng; ++g) {
+        if (e < 16) img_store(cat_img, Rp, (uint32_t)(rowb + i0 + g), h * 16 + e, o4[g]);
+        else red[g * 288 + ((e - 16) >> 3) * 96 + h * 8 + ((e - 16) & 7)] = o4[g];
+      }
+    }
+  }
+  __syncthreads();
+  // ---- 4. inverse frame + norm (invariant_point_attention.py:227-240)
+  for (int e = tid; e < ng * 96; e += 256) {
+    const int g = e / 96, pt = e - g * 96;
+    const float* R = fr + g * 12;
+    const float x = red[g * 288 + pt] - R[9], y = red[g * 288 + 96 + pt] - R[10], zc = red[g * 288 + 192 + pt] - R[11];
+    const float lx = R[0] * x + R[3] * y + R[6] * zc, ly = R[1] * x + R[4] * y + R[7] * zc, lz = R[2] * x + R[5] * y + R[8] * zc;
+    const uint32_t r = (uint32_t)(rowb + i0 + g);
+    img_store(cat_img, Rp, r, 192 + pt, lx);
+    img_store(cat_img, Rp, r, 288 + pt, ly);
+    img_store(cat_img, Rp, r, 384 + pt, lz);
+    img_store(cat_img, Rp, r, 480 + pt, sqrtf(lx * lx + ly * ly + lz * lz + 1e-8f));
+  }
+  // o_pair: TMEM lane = channel c, columns 16 g + h
+  {
+    const uint32_t q = warp & 3, c = q * 32 + lane;
+    for (int g = (warp >> 2); g < ng; g += 2) {
+      mbar_wait(done + g, 0);
+      tc_fence_after();
+      __syncwarp();
+      uint32_t v[16];
+      tmem_ld16(tmem + ((q * 32u) << 16) + g * 16, v);
+      tmem_ld_wait();
+      const uint32_t r = (uint32_t)(rowb + i0 + g);
+#pragma unroll
+      for (int h = 0; h < 12; ++h) img_store(cat_img, Rp, r, 576 + h * 128 + c, __uint_as_float(v[h]));
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) tmem_dealloc(tmem, 64);
+}
+
+// ---------------------------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------------------------
+static size_t al256(size_t v) { return (v + 255) & ~(size_t)255; }
+
+int tc_struct_init(gb_ctx* c) {
+  cudaError_t e;
+  if ((e = cudaFuncSetAttribute(gemm_img_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, GI_SMEM)) != cudaSuccess ||
+      (e = cudaFuncSetAttribute(ipa_prep_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PREP_SMEM)) != cudaSuccess ||
+      (e = cudaFuncSetAttribute(ipa_attention_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, IA_SMEM)) != cudaSuccess)
+    return gb_fail(c, GB_ERR_CUDA, "tc_struct_init: cudaFuncSetAttribute failed: %s", cudaGetErrorString(e));
+  return GB_OK;
+}
+
+bool tc_struct_supported(const gb_ctx* c, int N) {
+  const int cs = c->d.c_s;
+  return cs % 128 == 0 && cs <= 512 && N <= 256 && c->d.n_structure_layer * IPA_H <= 96;
+}
+
+size_t tc_struct_workspace_bytes(const gb_ctx* c, int B, int N) {
+  if (!tc_struct_supported(c, N)) return 0;
+  const size_t Np = (size_t)((N + 63) / 64) * 64, Rp = ((size_t)B * N + 127) / 128 * 128;
+  const size_t kcs = c->d.c_s / 64;
+  return 4 * al256(kcs * Rp * 128) + al256((size_t)(IPA_CAT / 64) * Rp * 128) + al256((size_t)B * N * 2 * Np * 128) +
+         al256((size_t)c->d.n_structure_layer * B * N * IPA_H * Np * 4) + 1024;
+}
+
+int tc_struct_bind(gb_ctx* c, void* base, size_t bytes, int B, int N) {
+  TcState* s = static_cast<TcState*>(c->tc_state);
+  s->Rp = 0;
+  if (!tc_struct_supported(c, N)) return GB_OK;
+  if (bytes < tc_struct_workspace_bytes(c, B, N) - 1024) return gb_fail(c, GB_ERR_INVALID, "tc_struct_bind: too small");
+  const size_t Np = (size_t)((N + 63) / 64) * 64, Rp = ((size_t)B * N + 127) / 128 * 128;
+  const size_t kcs = c->d.c_s / 64, act = al256(kcs * Rp * 128), cat = al256((size_t)(IPA_CAT / 64) * Rp * 128);
+  const size_t zb = al256((size_t)B * N * 2 * Np * 128);
+  char* q = static_cast<char*>(base);
+  s->s_img = reinterpret_cast<bf16*>(q);
+  s->ln1_img = reinterpret_cast<bf16*>(q + act);
+  s->h1_img = reinterpret_cast<bf16*>(q + 2 * act);
+  s->h2_img = reinterpret_cast<bf16*>(q + 3 * act);
+  s->cat_img = reinterpret_cast<bf16*>(q + 4 * act);
+  s->z_img = reinterpret_cast<bf16*>(q + 4 * act + cat);
+  s->pbias = reinterpret_cast<float*>(q + 4 * act + cat + zb);
+  s->Rp = (int)Rp;
+  // padded rows of the activation images and padded keys of z_img feed MMAs: keep them finite (zero)
+  if (cudaMemset(q, 0, 4 * act + cat + zb) != cudaSuccess) return gb_fail(c, GB_ERR_CUDA, "tc_struct_bind: memset failed");
+  return GB_OK;
+}
+
+// W [N][K] fp32 (nn.Linear layout) -> operand image [K/64][N][64]
+static bf16* pack_linear(gb_ctx* c, const std::vector<float>& w, int N, int K) {
+  std::vector<uint16_t> img((size_t)N * K);
+  pack_image(img.data(), N, K, [&](int r, int k) { return w[(size_t)r * K + k]; });
+  return (bf16*)upload_bytes(c, img.data(), img.size() * 2);
+}
+
+int tc_pack_struct_layer(gb_ctx* c, int l, const std::vector<float>& wqkv, const std::vector<float>& wout,
+                         const std::vector<const std::vector<float>*>& w123) {
+  TcState* s = static_cast<TcState*>(c->tc_state);
+  const int cs = c->d.c_s;
+  if (cs % 64 != 0) return GB_OK;
+  if ((int)s->st.size() <= l) s->st.resize(l + 1);
+  TcStructW& w = s->st[l];
+  w = TcStructW();
+  w.Wqkv = pack_linear(c, wqkv, IPA_QKV, cs);
+  w.Wout = pack_linear(c, wout, cs, IPA_CAT);
+  for (size_t t = 0; t + 2 < w123.size(); t += 3) {
+    w.W1.push_back(pack_linear(c, *w123[t], cs, cs));
+    w.W2.push_back(pack_linear(c, *w123[t + 1], cs, cs));
+    w.W3.push_back(pack_linear(c, *w123[t + 2], cs, cs));
+  }
+  if (!w.Wqkv || !w.Wout) return gb_fail(c, GB_ERR_CUDA, "tc_pack_struct_layer: device allocation failed");
+  return GB_OK;
+}
+
+// linear_b of every structure layer stacked into one 128 -> 96 projection, sqrt(1/3) folded in
+int tc_pack_ipa_bias(gb_ctx* c, const std::vector<const std::vector<float>*>& wb, const std::vector<const std::vector<float>*>& bb) {
+  TcState* s = static_cast<TcState*>(c->tc_state);
+  const int L = (int)wb.size();
+  if (L * IPA_H > 96) return GB_OK;
+  const float sc = sqrtf(1.f / 3.f);
+  std::vector<uint16_t> img(96 * 128);
+  pack_image(img.data(), 96, 128, [&](int r, int k) { return r < L * IPA_H ? sc * (*wb[r / IPA_H])[(size_t)(r % IPA_H) * 128 + k] : 0.f; });
+  std::vector<float> b96(96, 0.f);
+  for (int r = 0; r < L * IPA_H; ++r) b96[r] = sc * (*bb[r / IPA_H])[r % IPA_H];
+  s->Wb_img = (bf16*)upload_bytes(c, img.data(), img.size() * 2);
+  s->bias96 = (float*)upload_bytes(c, b96.data(), b96.size() * 4);
+  if (!s->Wb_img || !s->bias96) return gb_fail(c, GB_ERR_CUDA, "tc_pack_ipa_bias: device allocation failed");
+  return GB_OK;
+}
+
+static int gemm_img(gb_ctx* c, cudaStream_t st, const bf16* A, int K, const bf16* W, int Nw, const float* bias, const float* res,
+                    int ldr, float* C, int ldc, bf16* O, bool relu) {
+  TcState* s = static_cast<TcState*>(c->tc_state);
+  GemmImgArgs g;
+  g.A = A; g.W = W; g.bias = bias; g.res = res; g.C = C; g.O = O;
+  g.Rp = s->Rp; g.Nw = Nw; g.nkb = K / 64; g.R = c->B * c->N; g.ldc = ldc; g.ldr = ldr; g.relu = relu ? 1 : 0;
+  gemm_img_tc_kernel<<<dim3(Nw / 64, s->Rp / 128), 256, GI_SMEM, st>>>(g);
+  GB_LAUNCH_CHECK(c, "gemm_img_tc");
+  return GB_OK;
+}
+
+// StructureNet.forward (structure_net.py:189-243) on c->s / c->p / c->rots_w / c->trans_w, bf16 mode.
+int tc_structure_net(gb_ctx* c, float* states_out, cudaStream_t st) {
+  TcState* s = static_cast<TcState*>(c->tc_state);
+  const gb_dims& d = c->d;
+  const int B = c->B, N = c->N, R = B * N, cs = d.c_s, Np = s->Np, Rp = s->Rp;
+  if (!Rp || (int)s->st.size() < d.n_structure_layer || !s->Wb_img) return gb_fail(c, GB_ERR_INVALID, "tc_structure_net: not bound");
+  const size_t Rcs = (size_t)R * cs;
+  int rc;
+  const unsigned ptiles = (unsigned)B * ((N + 1) / 2) * (Np / 64);
+  ipa_prep_tc_kernel<<<ptiles, 256, PREP_SMEM, st>>>(c->p, B, N, Np, c->mask, s->Wb_img, s->bias96, s->pbias, s->z_img,
+                                                     d.n_structure_layer * IPA_H);
+  GB_LAUNCH_CHECK(c, "ipa_prep_tc");
+  const unsigned lnb = (unsigned)((R * 32 + 255) / 256);
+  ln_img_kernel<<<lnb, 256, 0, st>>>(c->s, nullptr, nullptr, s->s_img, nullptr, nullptr, R, cs, Rp, 0);
+  GB_LAUNCH_CHECK(c, "s_to_img");
+  int state_idx = 1;
+  for (int blk = 0; blk < d.n_structure_block; ++blk)
+    for (int l = 0; l < d.n_structure_layer; ++l) {
+      const StructLayerW& w = c->st[l];
+      const TcStructW& t = s->st[l];
+      if ((rc = gemm_img(c, st, s->s_img, cs, t.Wqkv, IPA_QKV, w.bqkv, nullptr, 0, c->qkv, IPA_QKV, nullptr, false))) return rc;
+      if ((rc = simt_points_to_global(c, st))) return rc;
+      ipa_attention_tc_kernel<<<dim3((N + IA_G - 1) / IA_G, B), 256, IA_SMEM, st>>>(
+          c->qkv, s->pbias + (size_t)l * B * N * IPA_H * Np, s->z_img, c->rots_w, c->trans_w, w.hw, s->cat_img, N, Np, Rp);
+      GB_LAUNCH_CHECK(c, "ipa_attention_tc");
+      if ((rc = gemm_img(c, st, s->cat_img, IPA_CAT, t.Wout, cs, w.bout, c->s, cs, c->sA, cs, nullptr, false))) return rc;
+      ln_img_kernel<<<lnb, 256, 0, st>>>(c->sA, c->sB, nullptr, s->ln1_img, w.ln1_g, w.ln1_b, R, cs, Rp, 1);
+      GB_LAUNCH_CHECK(c, "ipa_layer_norm");
+      float* cur = c->sB;
+      float* other = c->sA;
+      for (int tl = 0; tl < d.n_structure_transition_layer; ++tl) {
+        if (tl > 0) {
+          ln_img_kernel<<<lnb, 256, 0, st>>>(cur, nullptr, nullptr, s->ln1_img, nullptr, nullptr, R, cs, Rp, 0);
+          GB_LAUNCH_CHECK(c, "to_img");
+        }
+        if ((rc = gemm_img(c, st, s->ln1_img, cs, t.W1[tl], cs, w.b1[tl], nullptr, 0, nullptr, 0, s->h1_img, true))) return rc;
+        if ((rc = gemm_img(c, st, s->h1_img, cs, t.W2[tl], cs, w.b2[tl], nullptr, 0, nullptr, 0, s->h2_img, true))) return rc;
+        if ((rc = gemm_img(c, st, s->h2_img, cs, t.W3[tl], cs, w.b3[tl], cur, cs, other, cs, nullptr, false))) return rc;
+        float* tmp = cur; cur = other; other = tmp;
+      }
+      float* st_out = states_out ? states_out + (size_t)state_idx * Rcs : nullptr;
+      ln_img_kernel<<<lnb, 256, 0, st>>>(cur, c->s, st_out, s->s_img, w.ln2_g, w.ln2_b, R, cs, Rp, 1);
+      GB_LAUNCH_CHECK(c, "transition_layer_norm");
+      ++state_idx;
+      if ((rc = simt_backbone_update(c, w, st))) return rc;
+    }
+  return GB_OK;
+}
