@@ -20,7 +20,7 @@ struct TriMulW {
   float *WzT, *bz;    // [128 k][128 n], [128]
   // tensor-core packings (K-major [n][k] rows, i.e. nn.Linear layout), filled by tc_pack
   void *tc_Wproj, *tc_Wz;
-  float *tc_bproj;
+  float *tc_bproj, *tc_uv;   // tc_uv: [128] u | [128] v of the LayerNorm-folded output projection
 };
 struct TransitionW {
   float *ln_g, *ln_b, *W1T, *b1, *W2T, *b2;

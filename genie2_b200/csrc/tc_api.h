@@ -9,7 +9,8 @@ void tc_destroy(gb_ctx* c);
 int tc_pack_trimul(gb_ctx* c, TriMulW& w, const std::vector<float>& ap, const std::vector<float>& ag,
                    const std::vector<float>& bp, const std::vector<float>& bg, const std::vector<float>& lg,
                    const std::vector<float>& lz, const std::vector<float>& apb, const std::vector<float>& agb,
-                   const std::vector<float>& bpb, const std::vector<float>& bgb, const std::vector<float>& lgb);
+                   const std::vector<float>& bpb, const std::vector<float>& bgb, const std::vector<float>& lgb,
+                   const std::vector<float>& lzb, const std::vector<float>& lno_g, const std::vector<float>& lno_b);
 int tc_pack_transition(gb_ctx* c, TransitionW& w, const std::vector<float>& w1, const std::vector<float>& w2);
 // workspace the tensor-core path needs for a (B,N) batch, carved by gb_set_features
 size_t tc_workspace_bytes(const gb_ctx* c, int B, int N);

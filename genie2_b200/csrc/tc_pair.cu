@@ -24,7 +24,7 @@ using namespace tc;
 // shared helpers
 // ---------------------------------------------------------------------------------------------
 // LayerNorm(128) of up to 128 pixel rows -> bf16 A operand image [2 kb][128 rows][64].
-// Warp w normalises rows 16w..16w+15, four at a time (four 512-byte coalesced loads in flight);
+// Warp w normalises rows 16w..16w+15, eight at a time (eight 512-byte coalesced loads in flight);
 // lane l holds channels 4l..4l+3.  src_row(m) returns the fp32 row pointer or nullptr (zero row).
 template <typename RowFn>
 __device__ __forceinline__ void ln_rows_to_image(uint8_t* A, RowFn src_row, const float* __restrict__ gamma,
@@ -33,16 +33,16 @@ __device__ __forceinline__ void ln_rows_to_image(uint8_t* A, RowFn src_row, cons
   const float4 g4 = ld4(gamma + lane * 4), b4 = ld4(beta + lane * 4);
   const uint32_t kb = lane >> 4, chunk = (lane & 15) >> 1, half = lane & 1;
 #pragma unroll
-  for (int it = 0; it < 4; ++it) {
-    float4 v[4];
+  for (int it = 0; it < 2; ++it) {
+    float4 v[8];
 #pragma unroll
-    for (int u = 0; u < 4; ++u) {
-      const float* r = src_row(warp * 16 + it * 4 + u);
+    for (int u = 0; u < 8; ++u) {
+      const float* r = src_row(warp * 16 + it * 8 + u);
       v[u] = r ? ld4(r + lane * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
     }
 #pragma unroll
-    for (int u = 0; u < 4; ++u) {
-      const uint32_t m = warp * 16 + it * 4 + u;
+    for (int u = 0; u < 8; ++u) {
+      const uint32_t m = warp * 16 + it * 8 + u;
       const float mean = warp_sum(v[u].x + v[u].y + v[u].z + v[u].w) * (1.f / 128.f);
       const float dx = v[u].x - mean, dy = v[u].y - mean, dz = v[u].z - mean, dw = v[u].w - mean;
       const float rstd = rsqrtf(warp_sum(dx * dx + dy * dy + dz * dz + dw * dw) * (1.f / 128.f) + 1e-5f);
@@ -188,19 +188,28 @@ __global__ void __launch_bounds__(256, 2) pair_transition_tc_kernel(
   tmem_to_stage(S, t_lane + 128 + h * 64 + 32, m, h * 64 + 32, b2);
   tc_fence_before();
   __syncthreads();
-  for (int r = warp; r < 128; r += 8) {
-    const uint32_t row = row0 + r;
-    if (row >= M) break;
-    const uint32_t cl = lane ^ (r & 31);
-    const float4 v = *reinterpret_cast<const float4*>(S + r * 512u + (lane << 4));
-    const float mk = rowmask[r];
-    float* dst = p + (size_t)row * 128 + cl * 4;
-    float4 pv = ld4(dst);
-    pv.x = (pv.x + v.x * mk) * mk;
-    pv.y = (pv.y + v.y * mk) * mk;
-    pv.z = (pv.z + v.z * mk) * mk;
-    pv.w = (pv.w + v.w * mk) * mk;
-    st4(dst, pv);
+  for (int r0 = warp * 16; r0 < warp * 16 + 16; r0 += 4) {     // 4 rows (2 KB of p) in flight per warp
+    float4 pv[4];
+    bool ok[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const uint32_t r = r0 + u, row = row0 + r;
+      ok[u] = row < M;
+      if (ok[u]) pv[u] = ld4(p + (size_t)row * 128 + ((lane ^ (r & 31)) << 2));
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const uint32_t r = r0 + u;
+      if (!ok[u]) continue;
+      const float4 v = *reinterpret_cast<const float4*>(S + r * 512u + (lane << 4));
+      const float mk = rowmask[r];
+      float4 o;
+      o.x = (pv[u].x + v.x * mk) * mk;
+      o.y = (pv[u].y + v.y * mk) * mk;
+      o.z = (pv[u].z + v.z * mk) * mk;
+      o.w = (pv[u].w + v.w * mk) * mk;
+      st4(p + (size_t)(row0 + r) * 128 + ((lane ^ (r & 31)) << 2), o);
+    }
   }
   if (warp == 1) tmem_dealloc(tmem, 256);
 }
@@ -218,23 +227,23 @@ __global__ void __launch_bounds__(256, 2) pair_transition_tc_kernel(
 //   Wimg: [a: 2 kb x 256 rows (a_p | a_g) x 64] 64K | [b: likewise] 64K | [g: 2 kb x 128 x 64] 32K
 //   bias: a_p | a_g | b_p | b_g | g   (5 x 128)
 //   a_out / b_out: [B][128 ch][Np/64 kb][Np rows][64] tile images (bf16);  g_out [B*N*N][128] bf16
-// Shared: A 32K | W 64K | barriers; 256 TMEM columns; 2 CTAs / SM.
+// The gated projections are computed TRANSPOSED, D[channel][pixel] = W . X^T (weights as the M-side
+// operand, the LayerNorm'ed pixel tile X as the N-side operand; both are the same K-major images):
+// a TMEM lane is then a channel, and the 64 pixel columns a thread drains are exactly one 128-byte
+// row of that channel's operand image -- eight 16-byte stores instead of 64 two-byte ones, biases
+// in two registers.  The output gate g stays pixel-major (D[pixel][channel]).
+// Shared: X 32K | W 64K | barriers, masks; 256 TMEM columns; 2 CTAs / SM.
 // ---------------------------------------------------------------------------------------------
-#define K4_SMEM (32768 + 65536 + 1024 + 64)
+#define K4_SMEM (32768 + 65536 + 1024 + 64 + 512)
 
-// gated, masked projection of this thread's pixel for 32 channels -> 2-byte stores into the image
-__device__ __forceinline__ void k4_store_gated(uint32_t t_proj, const float* __restrict__ bp, const float* __restrict__ bg,
-                                               float mk, bool valid, bf16* __restrict__ dst, size_t ch_stride) {
-  uint32_t vp[32], vg[32];
-  tmem_ld32(t_proj, vp);
-  tmem_ld32(t_proj + 128, vg);
-  tmem_ld_wait();
-  if (!valid) return;
+// D[128 ch][128 px] = Wrows . X^T for one 128-row block of a 256-row weight image pair
+__device__ __forceinline__ void k4_mma_T(uint32_t tmem_d, uint32_t w_rows, uint32_t x_base) {
+  const uint32_t idesc = umma_idesc(128, 128);
 #pragma unroll
-  for (int e = 0; e < 32; ++e) {
-    const float v = (__uint_as_float(vp[e]) + bp[e]) * sigmoidf_(__uint_as_float(vg[e]) + bg[e]) * mk;
-    dst[(size_t)e * ch_stride] = __float2bfloat16_rn(v);
-  }
+  for (int kb = 0; kb < 2; ++kb)
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+      umma(tmem_d, umma_desc(w_rows + kb * (256 * 128) + k * 32), umma_desc(x_base + kb * 16384 + k * 32), idesc, (kb | k) ? 1u : 0u);
 }
 
 __global__ void __launch_bounds__(256, 2) trimul_proj_tc_kernel(
@@ -243,11 +252,12 @@ __global__ void __launch_bounds__(256, 2) trimul_proj_tc_kernel(
     bf16* __restrict__ a_out, bf16* __restrict__ b_out, bf16* __restrict__ g_out, int incoming) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* sm = smem_base_1024(smem_raw);
-  uint8_t* A = sm;
+  uint8_t* X = sm;
   uint8_t* W = sm + 32768;
   uint64_t* bar_w = reinterpret_cast<uint64_t*>(sm + 98304);
   uint64_t* bar_mma = bar_w + 1;
   uint32_t* tslot = reinterpret_cast<uint32_t*>(bar_w + 2);
+  float* pmask = reinterpret_cast<float*>(sm + 98304 + 64);      // [128] pair mask of the tile's pixels
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const PixTile T = pix_tile(blockIdx.x, N, Np);
 
@@ -265,32 +275,29 @@ __global__ void __launch_bounds__(256, 2) trimul_proj_tc_kernel(
     ok = row < (uint32_t)N && col < (uint32_t)N;
     return sample + (incoming ? (size_t)col * N + row : (size_t)row * N + col);
   };
-  ln_rows_to_image(A, [&](int mm) -> const float* { bool ok; const size_t px = pixel_of(mm, ok); return ok ? p + px * 128 : nullptr; },
+  if (tid < 128) {
+    const uint32_t row = 2 * T.t2 + (tid >> 6), col = 64 * T.jb + (tid & 63);
+    pmask[tid] = (row < (uint32_t)N && col < (uint32_t)N) ? (float)(rmask[T.b * N + row] * rmask[T.b * N + col]) : 0.f;
+  }
+  ln_rows_to_image(X, [&](int mm) -> const float* { bool ok; const size_t px = pixel_of(mm, ok); return ok ? p + px * 128 : nullptr; },
                    ln_g, ln_b);
   fence_proxy_async();
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *tslot;
-  const uint32_t q = warp & 3, h = warp >> 2, m = q * 32 + lane;
+  const uint32_t q = warp & 3, h = warp >> 2;
   const uint32_t t_lane = tmem + ((q * 32u) << 16);
-  bool valid;
-  const size_t px = pixel_of(m, valid);
-  float mk = 0.f;
-  if (valid) {
-    const uint32_t row = 2 * T.t2 + (m >> 6), col = 64 * T.jb + (m & 63);
-    mk = (float)(rmask[T.b * N + row] * rmask[T.b * N + col]);
-  }
-  // destination of this pixel inside a channel plane of the operand image: row = 2 t2 + ii, k = col
-  const uint32_t orow = 2 * T.t2 + (m >> 6), jj = m & 63;
-  const size_t ch_stride = (size_t)(Np >> 6) * Np * 64;
-  const size_t img_off = ((size_t)T.b * 128 * (Np >> 6) + T.jb) * Np * 64 + (size_t)orow * 64 + (((jj >> 3) ^ (orow & 7)) << 3) + (jj & 7);
+  // transposed epilogue: this thread owns channel ch and the pixel columns [64 h, 64 h + 64) = image row orow
+  const uint32_t ch = q * 32 + lane, orow = 2 * T.t2 + h;
+  const size_t img_row = ((((size_t)T.b * 128 + ch) * (Np >> 6) + T.jb) * Np + orow) * 64;   // element offset of the 128-byte row
 
   for (int part = 0; part < 2; ++part) {     // part 0 -> a, part 1 -> b
     if (tid == 0) {
       mbar_wait(bar_w, part);
       tc_fence_after();
-      umma_tile(tmem, smem_u32(A), smem_u32(W), 256, 2, false);
+      k4_mma_T(tmem, smem_u32(W), smem_u32(X));                  // proj -> cols [0,128)
+      k4_mma_T(tmem + 128, smem_u32(W) + 16384, smem_u32(X));    // gate -> cols [128,256)
       umma_commit(bar_mma);
     }
     __syncwarp();
@@ -302,26 +309,46 @@ __global__ void __launch_bounds__(256, 2) trimul_proj_tc_kernel(
       bulk_g2s(W, Wimg + (size_t)(part + 1) * 32768, bytes, bar_w);
     }
     __syncwarp();
-    bf16* dst = (part == 0 ? a_out : b_out) + img_off;
-    const float* bp = bias + part * 256;
+    const float bp = bias[part * 256 + ch], bg = bias[part * 256 + 128 + ch];
+    uint8_t* dst = reinterpret_cast<uint8_t*>((part == 0 ? a_out : b_out) + img_row);
 #pragma unroll 1
     for (int cc = 0; cc < 2; ++cc) {
-      const int c0 = h * 64 + cc * 32;       // channels [c0, c0+32)
-      k4_store_gated(t_lane + c0, bp + c0, bp + 128 + c0, mk, valid, dst + (size_t)c0 * ch_stride, ch_stride);
+      uint32_t vp[32], vg[32];
+      tmem_ld32(t_lane + h * 64 + cc * 32, vp);
+      tmem_ld32(t_lane + 128 + h * 64 + cc * 32, vg);
+      tmem_ld_wait();
+      if (orow < (uint32_t)N) {
+        const float4* mk4 = reinterpret_cast<const float4*>(pmask + h * 64 + cc * 32);
+#pragma unroll
+        for (int c8 = 0; c8 < 4; ++c8) {
+          const float4 m0 = mk4[2 * c8], m1 = mk4[2 * c8 + 1];
+          const float mk[8] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
+          float o[8];
+#pragma unroll
+          for (int e = 0; e < 8; ++e)
+            o[e] = (__uint_as_float(vp[8 * c8 + e]) + bp) * fast_sigmoid(__uint_as_float(vg[8 * c8 + e]) + bg) * mk[e];
+          uint4 w;
+          w.x = pack_bf16(o[0], o[1]); w.y = pack_bf16(o[2], o[3]); w.z = pack_bf16(o[4], o[5]); w.w = pack_bf16(o[6], o[7]);
+          *reinterpret_cast<uint4*>(dst + ((((uint32_t)(cc * 4 + c8)) ^ (orow & 7u)) << 4)) = w;
+        }
+      }
     }
     tc_fence_before();
     __syncthreads();
   }
-  // output gate g = sigmoid(linear_g(LN z)), pixel-major bf16
+  // output gate g = sigmoid(linear_g(LN z)), pixel-major bf16: D[pixel][channel] = X . Wg^T
   if (tid == 0) {
     mbar_wait(bar_w, 0);
     tc_fence_after();
-    umma_tile(tmem, smem_u32(A), smem_u32(W), 128, 2, false);
+    umma_tile(tmem, smem_u32(X), smem_u32(W), 128, 2, false);
     umma_commit(bar_mma);
   }
   __syncwarp();
   mbar_wait(bar_mma, 0);
   tc_fence_after();
+  const uint32_t m = q * 32 + lane;
+  bool valid;
+  const size_t px = pixel_of(m, valid);
 #pragma unroll 1
   for (int cc = 0; cc < 2; ++cc) {
     const int c0 = h * 64 + cc * 32;
@@ -329,15 +356,16 @@ __global__ void __launch_bounds__(256, 2) trimul_proj_tc_kernel(
     tmem_ld32(t_lane + c0, v);
     tmem_ld_wait();
     if (valid) {
-      const float* bgp = bias + 512 + c0;
+      const float4* bg4 = reinterpret_cast<const float4*>(bias + 512 + c0);
       uint4* dst = reinterpret_cast<uint4*>(g_out + px * 128 + c0);
 #pragma unroll
       for (int k4 = 0; k4 < 4; ++k4) {
+        const float4 b0 = bg4[2 * k4], b1 = bg4[2 * k4 + 1];
         uint4 o;
-        o.x = pack_bf16(sigmoidf_(__uint_as_float(v[8 * k4 + 0]) + bgp[8 * k4 + 0]), sigmoidf_(__uint_as_float(v[8 * k4 + 1]) + bgp[8 * k4 + 1]));
-        o.y = pack_bf16(sigmoidf_(__uint_as_float(v[8 * k4 + 2]) + bgp[8 * k4 + 2]), sigmoidf_(__uint_as_float(v[8 * k4 + 3]) + bgp[8 * k4 + 3]));
-        o.z = pack_bf16(sigmoidf_(__uint_as_float(v[8 * k4 + 4]) + bgp[8 * k4 + 4]), sigmoidf_(__uint_as_float(v[8 * k4 + 5]) + bgp[8 * k4 + 5]));
-        o.w = pack_bf16(sigmoidf_(__uint_as_float(v[8 * k4 + 6]) + bgp[8 * k4 + 6]), sigmoidf_(__uint_as_float(v[8 * k4 + 7]) + bgp[8 * k4 + 7]));
+        o.x = pack_bf16(fast_sigmoid(__uint_as_float(v[8 * k4 + 0]) + b0.x), fast_sigmoid(__uint_as_float(v[8 * k4 + 1]) + b0.y));
+        o.y = pack_bf16(fast_sigmoid(__uint_as_float(v[8 * k4 + 2]) + b0.z), fast_sigmoid(__uint_as_float(v[8 * k4 + 3]) + b0.w));
+        o.z = pack_bf16(fast_sigmoid(__uint_as_float(v[8 * k4 + 4]) + b1.x), fast_sigmoid(__uint_as_float(v[8 * k4 + 5]) + b1.y));
+        o.w = pack_bf16(fast_sigmoid(__uint_as_float(v[8 * k4 + 6]) + b1.z), fast_sigmoid(__uint_as_float(v[8 * k4 + 7]) + b1.w));
         dst[k4] = o;
       }
     }
@@ -421,13 +449,17 @@ __global__ void __launch_bounds__(256, 2) trimul_contract_tc_kernel(const bf16* 
   // epilogue: thread = output row i (TMEM lane); warps 0-3 take even 32-column groups, 4-7 odd ones
   const uint32_t q = warp & 3, h = warp >> 2, i = ib * 128 + q * 32 + lane;
   const uint32_t t_lane = tmem + ((q * 32u) << 16);
-  bf16* xrow = x + ((size_t)blk * Np + i) * Np + (size_t)jb * NJ;
+  // x tile images: [b][t2 = i / 2][jb64][ii = i & 1][channel][64 j], 16-byte chunks swizzled by channel & 7:
+  // the 32 KB block of one (t2, jb64) pixel tile is exactly K6's MN-major A operand.
+  const uint32_t bb = blk >> 7, cch = blk & 127;
   for (uint32_t c0 = h * 32; c0 < nj; c0 += 64) {
     uint32_t v[32];
     tmem_ld32(t_lane + c0, v);
     tmem_ld_wait();
     if (i < (uint32_t)N) {
-      uint4* dst = reinterpret_cast<uint4*>(xrow + c0);
+      const uint32_t j = jb * NJ + c0, jb64 = j >> 6, q0 = (j & 63) >> 3;
+      uint8_t* dst = reinterpret_cast<uint8_t*>(x) +
+                     (((((size_t)bb * (Np >> 1) + (i >> 1)) * (Np >> 6) + jb64) * 2 + (i & 1)) * 128 + cch) * 128;
 #pragma unroll
       for (int k4 = 0; k4 < 4; ++k4) {
         uint4 o;
@@ -435,7 +467,7 @@ __global__ void __launch_bounds__(256, 2) trimul_contract_tc_kernel(const bf16* 
         o.y = pack_bf16(__uint_as_float(v[8 * k4 + 2]), __uint_as_float(v[8 * k4 + 3]));
         o.z = pack_bf16(__uint_as_float(v[8 * k4 + 4]), __uint_as_float(v[8 * k4 + 5]));
         o.w = pack_bf16(__uint_as_float(v[8 * k4 + 6]), __uint_as_float(v[8 * k4 + 7]));
-        dst[k4] = o;
+        *reinterpret_cast<uint4*>(dst + (((q0 + k4) ^ (cch & 7u)) << 4)) = o;
       }
     }
   }
@@ -447,68 +479,38 @@ __global__ void __launch_bounds__(256, 2) trimul_contract_tc_kernel(const bf16* 
 // ---------------------------------------------------------------------------------------------
 // K6 trimul_out_tc (triangular_multiplicative_update.py:105-108 + residual, pair_transform_net.py:111-112)
 //   p[pixel] += (W_z LN_out(x[:, pixel]) + b_z) * g[pixel]
-// x is channel-major bf16 [B][128][Np][Np]; thread t loads pixel t & 127, channels [64 (t>>7), +64).
-// Shared: A 32K | Wz 32K (reused as the 64K fp32 staging tile) ; 128 TMEM columns ; 3 CTAs / SM.
+// The LayerNorm over channels is applied AFTER the GEMM:  with W' = W_z * gamma (bf16),
+//   u[n] = sum_c W'[n][c],  v[n] = sum_c W_z[n][c] beta[c] + b_z[n]:
+//   W_z LN(x) + b_z = rstd * (W' x - mean * u) + v
+// so the raw bf16 x tile is the MMA operand as it lies in memory (one 32 KB cp.async.bulk, MN-major A:
+// pixels contiguous, channels along K) and no thread touches x except to take its per-pixel mean / rstd
+// from shared memory while the tensor core runs.  u is summed from the bf16-rounded W' so the mean
+// term cancels exactly.  Shared: X 32K | W' 32K (then the 64K fp32 staging tile); 128 TMEM columns.
 // ---------------------------------------------------------------------------------------------
-#define K6_SMEM (65536 + 1024 + 64 + 2048)
+#define K6_SMEM (65536 + 1024 + 64 + 3072)
 
-__global__ void __launch_bounds__(256, 2) trimul_out_tc_kernel(
+__global__ void __launch_bounds__(256, 3) trimul_out_tc_kernel(
     const bf16* __restrict__ x, const bf16* __restrict__ g, float* __restrict__ p, int N, int Np,
-    const float* __restrict__ ln_g, const float* __restrict__ ln_b, const bf16* __restrict__ Wzimg,
-    const float* __restrict__ bz) {
+    const bf16* __restrict__ Wzimg, const float* __restrict__ uvec, const float* __restrict__ vvec) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* sm = smem_base_1024(smem_raw);
-  uint8_t* A = sm;
+  uint8_t* X = sm;
   uint8_t* W = sm + 32768;
   uint64_t* bar_w = reinterpret_cast<uint64_t*>(sm + 65536);
   uint64_t* bar_mma = bar_w + 1;
   uint32_t* tslot = reinterpret_cast<uint32_t*>(bar_w + 2);
-  float* red = reinterpret_cast<float*>(sm + 65536 + 64);     // [2 halves][128] partial sums, [128] pixel index
+  float* red = reinterpret_cast<float*>(sm + 65536 + 64);     // [2][128] partials, then mean [128], rstd [128]
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const PixTile T = pix_tile(blockIdx.x, N, Np);
   if (tid == 0) {
     mbar_init(bar_w, 1);
     mbar_init(bar_mma, 1);
     fence_mbar_init();
-    mbar_expect_tx(bar_w, 32768);
+    mbar_expect_tx(bar_w, 65536);
+    bulk_g2s(X, x + (((size_t)T.b * (Np >> 1) + T.t2) * (Np >> 6) + T.jb) * 16384, 32768, bar_w);
     bulk_g2s(W, Wzimg, 32768, bar_w);
   }
   if (warp == 1) tmem_alloc(tslot, 128);
-  {
-    const uint32_t mm = tid & 127, hh = tid >> 7;
-    const uint32_t row = 2 * T.t2 + (mm >> 6), col = 64 * T.jb + (mm & 63);
-    const bool ok = row < (uint32_t)N && col < (uint32_t)N;
-    const bf16* src = x + (((size_t)T.b * 128 + hh * 64) * Np + row) * Np + col;
-    const size_t cs = (size_t)Np * Np;
-    float v[64];
-    float sum = 0.f;
-#pragma unroll
-    for (int c = 0; c < 64; ++c) {
-      v[c] = ok ? __bfloat162float(src[(size_t)c * cs]) : 0.f;
-      sum += v[c];
-    }
-    red[hh * 128 + mm] = sum;
-    __syncthreads();
-    const float mean = (red[mm] + red[128 + mm]) * (1.f / 128.f);
-    float d2 = 0.f;
-#pragma unroll
-    for (int c = 0; c < 64; ++c) { v[c] -= mean; d2 = fmaf(v[c], v[c], d2); }
-    red[256 + hh * 128 + mm] = d2;
-    __syncthreads();
-    const float rstd = rsqrtf((red[256 + mm] + red[384 + mm]) * (1.f / 128.f) + 1e-5f);
-    const float* gg = ln_g + hh * 64;
-    const float* bb = ln_b + hh * 64;
-#pragma unroll
-    for (int ch = 0; ch < 8; ++ch) {
-      uint4 o;
-      o.x = pack_bf16(v[8 * ch + 0] * rstd * gg[8 * ch + 0] + bb[8 * ch + 0], v[8 * ch + 1] * rstd * gg[8 * ch + 1] + bb[8 * ch + 1]);
-      o.y = pack_bf16(v[8 * ch + 2] * rstd * gg[8 * ch + 2] + bb[8 * ch + 2], v[8 * ch + 3] * rstd * gg[8 * ch + 3] + bb[8 * ch + 3]);
-      o.z = pack_bf16(v[8 * ch + 4] * rstd * gg[8 * ch + 4] + bb[8 * ch + 4], v[8 * ch + 5] * rstd * gg[8 * ch + 5] + bb[8 * ch + 5]);
-      o.w = pack_bf16(v[8 * ch + 6] * rstd * gg[8 * ch + 6] + bb[8 * ch + 6], v[8 * ch + 7] * rstd * gg[8 * ch + 7] + bb[8 * ch + 7]);
-      *reinterpret_cast<uint4*>(A + hh * 16384u + mm * 128u + (((uint32_t)ch ^ (mm & 7u)) << 4)) = o;
-    }
-  }
-  fence_proxy_async();
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -516,35 +518,97 @@ __global__ void __launch_bounds__(256, 2) trimul_out_tc_kernel(
   if (tid == 0) {
     mbar_wait(bar_w, 0);
     tc_fence_after();
-    umma_tile(tmem, smem_u32(A), smem_u32(W), 128, 2, false);
+    const uint32_t idesc = umma_idesc(128, 128) | (1u << 15);      // A (x tile) is MN-major
+#pragma unroll
+    for (int k = 0; k < 8; ++k)
+      umma(tmem, umma_desc_mn(smem_u32(X) + k * 2048, 16384), umma_desc(smem_u32(W) + (k >> 2) * 16384 + (k & 3) * 32), idesc, k ? 1u : 0u);
     umma_commit(bar_mma);
   }
   __syncwarp();
+  // per-pixel statistics over the 128 channels, from the same shared tile (two passes, fp32)
+  mbar_wait(bar_w, 0);
+  {
+    const uint32_t mm = tid & 127, hh = tid >> 7;                 // pixel, channel half
+    // element (pixel mm, channel c): block mm >> 6, row c, chunk ((mm & 63) >> 3) ^ (c & 7), lane mm & 7
+    const uint8_t* base = X + (mm >> 6) * 16384u + hh * 64u * 128u + ((mm & 7) << 1);
+    const uint32_t q8 = (mm & 63) >> 3;
+    float sum = 0.f;
+#pragma unroll 16
+    for (uint32_t c = 0; c < 64; ++c) sum += __bfloat162float(*reinterpret_cast<const bf16*>(base + c * 128u + ((q8 ^ (c & 7u)) << 4)));
+    red[hh * 128 + mm] = sum;
+    __syncthreads();
+    const float mean = (red[mm] + red[128 + mm]) * (1.f / 128.f);
+    float d2 = 0.f;
+#pragma unroll 16
+    for (uint32_t c = 0; c < 64; ++c) {
+      const float d = __bfloat162float(*reinterpret_cast<const bf16*>(base + c * 128u + ((q8 ^ (c & 7u)) << 4))) - mean;
+      d2 = fmaf(d, d, d2);
+    }
+    red[256 + hh * 128 + mm] = d2;
+    __syncthreads();
+    if (hh == 0) {
+      red[512 + mm] = mean;
+      red[640 + mm] = rsqrtf((red[256 + mm] + red[384 + mm]) * (1.f / 128.f) + 1e-5f);
+    }
+  }
   mbar_wait(bar_mma, 0);
   tc_fence_after();
+  __syncthreads();                                               // stats visible; X / W dead -> staging
   const uint32_t q = warp & 3, h = warp >> 2, m = q * 32 + lane;
   const uint32_t t_lane = tmem + ((q * 32u) << 16);
   uint8_t* S = sm;
-  tmem_to_stage(S, t_lane + h * 64, m, h * 64, bz);
-  tmem_to_stage(S, t_lane + h * 64 + 32, m, h * 64 + 32, bz);
+  {
+    const float mean = red[512 + m], rstd = red[640 + m];
+#pragma unroll 1
+    for (int cc = 0; cc < 2; ++cc) {
+      const uint32_t col0 = h * 64 + cc * 32;
+      uint32_t v[32];
+      tmem_ld32(t_lane + col0, v);
+      tmem_ld_wait();
+#pragma unroll
+      for (int k4 = 0; k4 < 8; ++k4) {
+        const float4 u4 = ld4(uvec + col0 + 4 * k4), v4 = ld4(vvec + col0 + 4 * k4);
+        float4 o;
+        o.x = rstd * (__uint_as_float(v[4 * k4 + 0]) - mean * u4.x) + v4.x;
+        o.y = rstd * (__uint_as_float(v[4 * k4 + 1]) - mean * u4.y) + v4.y;
+        o.z = rstd * (__uint_as_float(v[4 * k4 + 2]) - mean * u4.z) + v4.z;
+        o.w = rstd * (__uint_as_float(v[4 * k4 + 3]) - mean * u4.w) + v4.w;
+        *stage_ptr(S, m, (col0 >> 2) + k4) = o;
+      }
+    }
+  }
   tc_fence_before();
   __syncthreads();
-  for (int r = warp; r < 128; r += 8) {
-    const uint32_t row = 2 * T.t2 + (r >> 6), col = 64 * T.jb + (r & 63);
-    if (row >= (uint32_t)N || col >= (uint32_t)N) continue;
-    const size_t px = ((size_t)T.b * N + row) * N + col;
-    const uint32_t cl = lane ^ (r & 31);
-    const float4 v = *reinterpret_cast<const float4*>(S + r * 512u + (lane << 4));
-    const uint2 gv = *reinterpret_cast<const uint2*>(g + px * 128 + cl * 4);
-    const float2 g01 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&gv.x));
-    const float2 g23 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&gv.y));
-    float* dst = p + px * 128 + cl * 4;
-    float4 pv = ld4(dst);
-    pv.x += v.x * g01.x;
-    pv.y += v.y * g01.y;
-    pv.z += v.z * g23.x;
-    pv.w += v.w * g23.y;
-    st4(dst, pv);
+  for (int r0 = warp * 16; r0 < warp * 16 + 16; r0 += 4) {     // 4 pixels in flight per warp
+    float4 pv[4];
+    uint2 gv[4];
+    size_t px[4];
+    bool ok[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const uint32_t r = r0 + u, row = 2 * T.t2 + (r >> 6), col = 64 * T.jb + (r & 63);
+      ok[u] = row < (uint32_t)N && col < (uint32_t)N;
+      px[u] = ((size_t)T.b * N + row) * N + col;
+      if (ok[u]) {
+        const uint32_t cl = lane ^ (r & 31);
+        pv[u] = ld4(p + px[u] * 128 + cl * 4);
+        gv[u] = *reinterpret_cast<const uint2*>(g + px[u] * 128 + cl * 4);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const uint32_t r = r0 + u;
+      if (!ok[u]) continue;
+      const float4 v = *reinterpret_cast<const float4*>(S + r * 512u + (lane << 4));
+      const float2 g01 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&gv[u].x));
+      const float2 g23 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&gv[u].y));
+      float4 o = pv[u];
+      o.x += v.x * g01.x;
+      o.y += v.y * g01.y;
+      o.z += v.z * g23.x;
+      o.w += v.w * g23.y;
+      st4(p + px[u] * 128 + ((lane ^ (r & 31)) << 2), o);
+    }
   }
   if (warp == 1) tmem_dealloc(tmem, 128);
 }
@@ -571,19 +635,35 @@ void tc_destroy(gb_ctx* c) {
 int tc_pack_trimul(gb_ctx* c, TriMulW& w, const std::vector<float>& ap, const std::vector<float>& ag,
                    const std::vector<float>& bp, const std::vector<float>& bg, const std::vector<float>& lg,
                    const std::vector<float>& lz, const std::vector<float>& apb, const std::vector<float>& agb,
-                   const std::vector<float>& bpb, const std::vector<float>& bgb, const std::vector<float>& lgb) {
+                   const std::vector<float>& bpb, const std::vector<float>& bgb, const std::vector<float>& lgb,
+                   const std::vector<float>& lzb, const std::vector<float>& lno_g, const std::vector<float>& lno_b) {
   std::vector<uint16_t> img(5 * 128 * 128);
   pack_image(img.data(), 256, 128, [&](int r, int k) { return r < 128 ? ap[(size_t)r * 128 + k] : ag[(size_t)(r - 128) * 128 + k]; });
   pack_image(img.data() + 32768, 256, 128, [&](int r, int k) { return r < 128 ? bp[(size_t)r * 128 + k] : bg[(size_t)(r - 128) * 128 + k]; });
   pack_image(img.data() + 65536, 128, 128, [&](int r, int k) { return lg[(size_t)r * 128 + k]; });
   w.tc_Wproj = upload_bytes(c, img.data(), img.size() * 2);
+  // K6 folds LayerNorm_out into the GEMM: W' = W_z * gamma, u = row sums of bf16(W'), v = W_z beta + b_z
   std::vector<uint16_t> wz(128 * 128);
-  pack_image(wz.data(), 128, 128, [&](int r, int k) { return lz[(size_t)r * 128 + k]; });
+  pack_image(wz.data(), 128, 128, [&](int r, int k) { return lz[(size_t)r * 128 + k] * lno_g[k]; });
   w.tc_Wz = upload_bytes(c, wz.data(), wz.size() * 2);
+  std::vector<float> uv(256);
+  for (int n = 0; n < 128; ++n) {
+    double u = 0.0, v = lzb[n];
+    for (int k = 0; k < 128; ++k) {
+      const uint32_t bits = (uint32_t)f2bf(lz[(size_t)n * 128 + k] * lno_g[k]) << 16;
+      float wr;
+      memcpy(&wr, &bits, 4);
+      u += wr;
+      v += (double)lz[(size_t)n * 128 + k] * lno_b[k];
+    }
+    uv[n] = (float)u;
+    uv[128 + n] = (float)v;
+  }
+  w.tc_uv = (float*)upload_bytes(c, uv.data(), uv.size() * 4);
   std::vector<float> bias;
   for (const std::vector<float>* v : {&apb, &agb, &bpb, &bgb, &lgb}) bias.insert(bias.end(), v->begin(), v->end());
   w.tc_bproj = (float*)upload_bytes(c, bias.data(), bias.size() * 4);
-  if (!w.tc_Wproj || !w.tc_Wz || !w.tc_bproj) return gb_fail(c, GB_ERR_CUDA, "tc_pack_trimul: device allocation failed");
+  if (!w.tc_Wproj || !w.tc_Wz || !w.tc_bproj || !w.tc_uv) return gb_fail(c, GB_ERR_CUDA, "tc_pack_trimul: device allocation failed");
   return GB_OK;
 }
 
@@ -638,7 +718,7 @@ int tc_trimul(gb_ctx* c, const TriMulW& w, bool outgoing, float* p, cudaStream_t
   const unsigned cgrid = (unsigned)B * 128 * ((Np + 127) / 128) * ((Np + NJ - 1) / NJ);
   trimul_contract_tc_kernel<<<cgrid, 256, K5_SMEM, st>>>(s->a, s->b, s->x, N, Np, NJ);
   GB_LAUNCH_CHECK(c, "trimul_contract_tc");
-  trimul_out_tc_kernel<<<tiles, 256, K6_SMEM, st>>>(s->x, s->g, p, N, Np, w.ln_out_g, w.ln_out_b, (const bf16*)w.tc_Wz, w.bz);
+  trimul_out_tc_kernel<<<tiles, 256, K6_SMEM, st>>>(s->x, s->g, p, N, Np, (const bf16*)w.tc_Wz, w.tc_uv, w.tc_uv + 128);
   GB_LAUNCH_CHECK(c, "trimul_out_tc");
   return GB_OK;
 }

@@ -300,10 +300,6 @@ __global__ void __launch_bounds__(256, 2) ipa_prep_tc_kernel(const float* __rest
 #define IA_OFF_BAR (IA_OFF_FR + IA_G * 12 * 4)
 #define IA_SMEM (IA_OFF_BAR + 128 + 1024)
 
-// MN-major A descriptor: 64-channel blocks LBO bytes apart, 8-key groups 1024 B apart, SWIZZLE_128B
-__device__ __forceinline__ uint64_t umma_desc_mn(uint32_t saddr, uint32_t lbo_bytes) {
-  return (uint64_t)((saddr & 0x3FFFFu) >> 4) | ((uint64_t)(lbo_bytes >> 4) << 16) | (64ull << 32) | (1ull << 46) | (2ull << 61);
-}
 __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&v)[16]) {
   asm volatile(
       "tcgen05.ld.sync.aligned.32x32b.x16.b32 "

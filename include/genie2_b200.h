@@ -175,7 +175,7 @@ int gb_k_ipa(gb_ctx* ctx, int layer, const float* s, const float* p, const float
              const float* trans, float* out, void* stream);
 
 /* TEST ONLY: copy one bf16 intermediate of the last tensor-core triangle update into dst (device):
- * which = 0/1: a / b operand tile images [B][128][Np/64][Np][64]; 2: x [B][128][Np][Np];
+ * which = 0/1: a / b operand tile images [B][128][Np/64][Np][64]; 2: x tile images [B][Np/2][Np/64][2][128][64];
  * 3: g [B*N*N][128].  Returns the padded length Np (> 0) or a negative gb_status; dst may be NULL
  * to query Np only.  Lets unit tests check each tcgen05 kernel separately. */
 int gb_dbg_tc_copy(gb_ctx* ctx, int which, void* dst, int64_t bytes);

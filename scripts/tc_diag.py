@@ -30,6 +30,18 @@ def decode_image(buf, B, Np):
     return t.reshape(B, 128, Np // 64, Np, 64).permute(0, 1, 3, 2, 4).reshape(B, 128, Np, Np)
 
 
+def decode_x(buf, B, Np):
+    """x tile images [B][Np/2][Np/64][2][128 ch][64 j], chunks swizzled by ch & 7 -> [B,128,Np(i),Np(j)] float."""
+    import torch
+    t = buf.view(B, Np // 2, Np // 64, 2, 128, 8, 8).float()
+    c = torch.arange(128, device=buf.device)
+    q = torch.arange(8, device=buf.device)
+    pos = q[None, :] ^ (c[:, None] & 7)
+    idx = pos[None, None, None, None, :, :, None].expand(B, Np // 2, Np // 64, 2, 128, 8, 8)
+    t = torch.gather(t, 5, idx)
+    return t.permute(0, 4, 1, 3, 2, 5, 6).reshape(B, 128, Np, Np)
+
+
 def setup(B, N, seed=3):
     import torch
     from common import make_denoiser, feats_to
@@ -99,7 +111,7 @@ def run_case(case, B, N):
         return out
     ai = decode_image(grab(0, B * 128 * Np * Np), B, Np)[:, :, :N, :N]
     bi = decode_image(grab(1, B * 128 * Np * Np), B, Np)[:, :, :N, :N]
-    xi = grab(2, B * 128 * Np * Np).view(B, 128, Np, Np)[:, :, :N, :N].float()
+    xi = decode_x(grab(2, B * 128 * Np * Np), B, Np)[:, :, :N, :N]
     gi = grab(3, B * N * N * 128).view(B, N, N, 128).float()
     # operand orientation: outgoing A[row=i][k] = a[i,k]; incoming A[row=i][k] = a[k,i]
     a_ref = a.permute(0, 3, 1, 2) if outgoing else a.permute(0, 3, 2, 1)

@@ -64,7 +64,7 @@ def test_pair_transition_tc(B, N):
 @pytest.mark.parametrize('B,N', [(1, 64), (2, 100), (1, 200)])
 def test_trimul_tc_every_stage(B, N, outgoing):
     import genie2_b200._lib as L
-    from tc_diag import decode_image
+    from tc_diag import decode_image, decode_x
     lib = L.load()
     model, sd, ctx, p0, pm = _setup(B, N)
     model.set_precision('bf16')
@@ -96,7 +96,7 @@ def test_trimul_tc_every_stage(B, N, outgoing):
     assert rel(a_img[:, :, :N, :N], a.permute(*perm)) < TOL_OPERAND
     assert rel(b_img[:, :, :N, :N], b.permute(*perm)) < TOL_OPERAND
     assert rel(grab(3, B * N * N * 128).view(B, N, N, 128).float() * pm, gate * pm) < TOL_OPERAND
-    assert rel(grab(2, B * 128 * Np * Np).view(B, 128, Np, Np)[:, :, :N, :N].float(), x.permute(0, 3, 1, 2)) < TOL_X
+    assert rel(decode_x(grab(2, B * 128 * Np * Np), B, Np)[:, :, :N, :N], x.permute(0, 3, 1, 2)) < TOL_X
     assert rel(p - p0, upd) < TOL_UPDATE
 
 
