@@ -74,7 +74,7 @@ __global__ void single_combine_kernel(float* __restrict__ s, const float* __rest
 // m_ij = residue_mask_i * residue_mask_j, fst = fixed_structure_mask, fs = fixed_sequence_mask.
 // Weights arrive transposed [in][128] so the per-channel reads are coalesced.
 // ---------------------------------------------------------------------------------
-#define PE_TJ 32
+#define PE_TJ 128   // keys per tile = block size: every thread builds the features of one key
 #define PE_NBIN_MAX 40
 
 template <int NBIN>

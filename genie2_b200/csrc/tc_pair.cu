@@ -54,6 +54,32 @@ __device__ __forceinline__ void ln_rows_to_image(uint8_t* A, RowFn src_row, cons
   }
 }
 
+// Same for the eight rows m0 .. m0 + 7 of this warp only (the caller chooses the row range).
+template <typename RowFn>
+__device__ __forceinline__ void ln_rows8_to_image(uint8_t* A, uint32_t m0, RowFn src_row, const float* __restrict__ gamma,
+                                                  const float* __restrict__ beta) {
+  const int lane = threadIdx.x & 31;
+  const float4 g4 = ld4(gamma + lane * 4), b4 = ld4(beta + lane * 4);
+  const uint32_t kb = lane >> 4, chunk = (lane & 15) >> 1, half = lane & 1;
+  float4 v[8];
+#pragma unroll
+  for (int u = 0; u < 8; ++u) {
+    const float* r = src_row(m0 + u);
+    v[u] = r ? ld4(r + lane * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+#pragma unroll
+  for (int u = 0; u < 8; ++u) {
+    const uint32_t m = m0 + u;
+    const float mean = warp_sum(v[u].x + v[u].y + v[u].z + v[u].w) * (1.f / 128.f);
+    const float dx = v[u].x - mean, dy = v[u].y - mean, dz = v[u].z - mean, dw = v[u].w - mean;
+    const float rstd = rsqrtf(warp_sum(dx * dx + dy * dy + dz * dz + dw * dw) * (1.f / 128.f) + 1e-5f);
+    uint2 o;
+    o.x = pack_bf16(dx * rstd * g4.x + b4.x, dy * rstd * g4.y + b4.y);
+    o.y = pack_bf16(dz * rstd * g4.z + b4.z, dw * rstd * g4.w + b4.w);
+    *reinterpret_cast<uint2*>(A + kb * 16384u + m * 128u + ((chunk ^ (m & 7u)) << 4) + half * 8u) = o;
+  }
+}
+
 // fp32 staging tile [128 rows][128 cols] with 16-byte chunks XOR-swizzled by the row, so that a
 // thread-per-row writer (TMEM epilogue) and a warp-per-row reader are both bank-conflict free.
 __device__ __forceinline__ float4* stage_ptr(uint8_t* S, uint32_t m, uint32_t chunk) {
@@ -82,7 +108,7 @@ __device__ __forceinline__ void tmem_to_stage(uint8_t* S, uint32_t taddr, uint32
 // 256 threads, 2 CTAs / SM (97 KB shared, 256 TMEM columns each) so that one CTA's LayerNorm /
 // epilogue overlaps the other's MMAs.  Shared: A 32K | H 32K | W 32K | barriers.
 // ---------------------------------------------------------------------------------------------
-#define K7_SMEM (3 * 32768 + 1024 + 64 + 512)
+#define K7_SMEM (3 * 32768 + 1024 + 64 + 512)   // barriers (4 x 8 B) + TMEM slot live in the 64 B after the tiles
 
 __global__ void __launch_bounds__(256, 2) pair_transition_tc_kernel(
     float* __restrict__ p, uint32_t M, int N, const int* __restrict__ rmask, const float* __restrict__ ln_g,
@@ -100,12 +126,20 @@ __global__ void __launch_bounds__(256, 2) pair_transition_tc_kernel(
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const uint32_t row0 = blockIdx.x * 128u;
 
+  // The raw fp32 tile (128 rows x 512 B, contiguous in p) is fetched by the async proxy into the
+  // H | W buffers (rows 0..63 -> H, 64..127 -> W), so 64 KB per CTA are in flight from the first
+  // instruction.  The W half is normalised first; then the first weight image streams into W
+  // while the H half is normalised.
+  uint64_t* bar_raw = bar_w + 3;
+  const uint32_t nrows = min(128u, M - row0);
   if (tid == 0) {
     mbar_init(bar_w, 1);
     mbar_init(bar_mma, 1);
+    mbar_init(bar_raw, 1);
     fence_mbar_init();
-    mbar_expect_tx(bar_w, 32768);
-    bulk_g2s(W, W1img, 32768, bar_w);
+    mbar_expect_tx(bar_raw, nrows * 512u);
+    bulk_g2s(H, p + (size_t)row0 * 128, min(nrows, 64u) * 512u, bar_raw);
+    if (nrows > 64) bulk_g2s(W, p + (size_t)(row0 + 64) * 128, (nrows - 64) * 512u, bar_raw);
   }
   if (warp == 1) tmem_alloc(tslot, 256);
   if (tid < 128) {
@@ -117,7 +151,19 @@ __global__ void __launch_bounds__(256, 2) pair_transition_tc_kernel(
     }
     rowmask[tid] = mk;
   }
-  ln_rows_to_image(A, [&](int m) -> const float* { return (row0 + m < M) ? p + (size_t)(row0 + m) * 128 : nullptr; }, ln_g, ln_b);
+  __syncthreads();                       // barrier init visible
+  mbar_wait(bar_raw, 0);
+  ln_rows8_to_image(A, 64 + warp * 8, [&](uint32_t m) -> const float* { return (m < nrows) ? reinterpret_cast<const float*>(W + (m - 64) * 512u) : nullptr; },
+                    ln_g, ln_b);
+  fence_proxy_async();                   // generic reads of W ordered before the async-proxy overwrite below
+  __syncthreads();                       // every warp is done reading the raw rows in W
+  if (tid == 0) {
+    fence_proxy_async();                 // order the generic reads of W before the async overwrite
+    mbar_expect_tx(bar_w, 32768);
+    bulk_g2s(W, W1img, 32768, bar_w);
+  }
+  ln_rows8_to_image(A, warp * 8, [&](uint32_t m) -> const float* { return (m < nrows) ? reinterpret_cast<const float*>(H + m * 512u) : nullptr; },
+                    ln_g, ln_b);
   fence_proxy_async();
   tc_fence_before();
   __syncthreads();

@@ -296,7 +296,7 @@ __global__ void __launch_bounds__(256, 2) ipa_prep_tc_kernel(const float* __rest
 #define IA_OFF_P (IA_OFF_AIMG + IA_G * 8192)
 #define IA_OFF_QS (IA_OFF_P + 12 * 256 * 16)
 #define IA_OFF_RED (IA_OFF_QS + IA_G * 12 * 28 * 4)
-#define IA_OFF_FR (IA_OFF_RED + IA_G * 288 * 4)
+#define IA_OFF_FR (IA_OFF_RED + IA_G * 480 * 4)
 #define IA_OFF_BAR (IA_OFF_FR + IA_G * 12 * 4)
 #define IA_SMEM (IA_OFF_BAR + 128 + 1024)
 
@@ -325,7 +325,7 @@ __global__ void __launch_bounds__(256, 1) ipa_attention_tc_kernel(
   uint8_t* aimg = sm + IA_OFF_AIMG;
   float* P = reinterpret_cast<float*>(sm + IA_OFF_P);          // [12 h][Np j][IA_G]
   float* qs = reinterpret_cast<float*>(sm + IA_OFF_QS);        // [g][h][28]: q*sc (16) | q_pts c*4+p (12)
-  float* red = reinterpret_cast<float*>(sm + IA_OFF_RED);      // [g][288] o_pt, global frame
+  float* oacc = reinterpret_cast<float*>(sm + IA_OFF_RED);     // [g][h*40 + e]: o (e < 16) | o_pt global frame (16 + c*8 + p)
   float* fr = reinterpret_cast<float*>(sm + IA_OFF_FR);        // [g][12] R (9) t (3)
   uint64_t* full = reinterpret_cast<uint64_t*>(sm + IA_OFF_BAR);
   uint64_t* empty = full + IA_ZRING;
@@ -363,6 +363,7 @@ __global__ void __launch_bounds__(256, 1) ipa_attention_tc_kernel(
     qs[e] = v;
   }
   for (int e = tid; e < IA_G * 8192 / 16; e += 256) reinterpret_cast<uint4*>(aimg)[e] = make_uint4(0, 0, 0, 0);
+  for (int e = tid; e < IA_G * 480; e += 256) oacc[e] = 0.f;
   if (tid < IA_G * 12) {
     const int g = tid / 12, x = tid - g * 12;
     fr[tid] = g < ng ? (x < 9 ? rots[(rowb + i0 + g) * 9 + x] : trans[(rowb + i0 + g) * 3 + x - 9]) : 0.f;
@@ -474,30 +475,46 @@ __global__ void __launch_bounds__(256, 1) ipa_attention_tc_kernel(
     }
     __syncwarp();
   } else {
-    // o[h][16] and o_pt[h][8][3] (global frame): 480 outputs per query over 192 threads
-    for (int x = tid - 64; x < 480; x += 192) {
-      const int h = x / 40, e = x - h * 40;
-      const int off = e < 16 ? IPA_OFF_KV + h * 32 + 16 + e : IPA_OFF_KVP + ((e - 16) >> 3) * 144 + h * 12 + 4 + ((e - 16) & 7);
+    // o[h][16] and o_pt[h][8][3] (global frame): per query 120 float4 groups (10 per head) x 8 key
+    // segments = 960 tasks over 192 threads; partial sums meet in shared memory.
+    const int seg = (N + 7) >> 3;
+    for (int t = tid - 64; t < 960; t += 192) {
+      const int js = t / 120, grp = t - js * 120, h = grp / 10, e4 = grp - h * 10;
+      const int off = e4 < 4 ? IPA_OFF_KV + h * 32 + 16 + e4 * 4
+                             : IPA_OFF_KVP + (((e4 - 4) * 4) >> 3) * 144 + h * 12 + 4 + (((e4 - 4) * 4) & 7);
       const float* src = qkv + rowb * IPA_QKV + off;
-      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-      for (int j = 0; j < N; ++j) {
-        const float v = src[(size_t)j * IPA_QKV];
+      float acc[IA_G][4];
+#pragma unroll
+      for (int g = 0; g < IA_G; ++g) acc[g][0] = acc[g][1] = acc[g][2] = acc[g][3] = 0.f;
+      const int j1 = min(N, (js + 1) * seg);
+#pragma unroll 4
+      for (int j = js * seg; j < j1; ++j) {
+        const float4 v = ld4(src + (size_t)j * IPA_QKV);
         const float4 a = *reinterpret_cast<const float4*>(P + ((size_t)h * Np + j) * IA_G);
-        acc.x = fmaf(a.x, v, acc.x); acc.y = fmaf(a.y, v, acc.y); acc.z = fmaf(a.z, v, acc.z); acc.w = fmaf(a.w, v, acc.w);
+        const float av[4] = {a.x, a.y, a.z, a.w};
+#pragma unroll
+        for (int g = 0; g < IA_G; ++g) {
+          acc[g][0] = fmaf(av[g], v.x, acc[g][0]); acc[g][1] = fmaf(av[g], v.y, acc[g][1]);
+          acc[g][2] = fmaf(av[g], v.z, acc[g][2]); acc[g][3] = fmaf(av[g], v.w, acc[g][3]);
+        }
       }
-      const float o4[4] = {acc.x, acc.y, acc.z, acc.w};
-      for (int g = 0; g < ng; ++g) {
-        if (e < 16) img_store(cat_img, Rp, (uint32_t)(rowb + i0 + g), h * 16 + e, o4[g]);
-        else red[g * 288 + ((e - 16) >> 3) * 96 + h * 8 + ((e - 16) & 7)] = o4[g];
-      }
+#pragma unroll
+      for (int g = 0; g < IA_G; ++g)
+#pragma unroll
+        for (int e = 0; e < 4; ++e) atomicAdd(oacc + g * 480 + h * 40 + e4 * 4 + e, acc[g][e]);
     }
   }
   __syncthreads();
   // ---- 4. inverse frame + norm (invariant_point_attention.py:227-240)
+  for (int e = tid; e < ng * 192; e += 256) {
+    const int g = e / 192, x = e - g * 192;
+    img_store(cat_img, Rp, (uint32_t)(rowb + i0 + g), x, oacc[g * 480 + (x >> 4) * 40 + (x & 15)]);
+  }
   for (int e = tid; e < ng * 96; e += 256) {
     const int g = e / 96, pt = e - g * 96;
     const float* R = fr + g * 12;
-    const float x = red[g * 288 + pt] - R[9], y = red[g * 288 + 96 + pt] - R[10], zc = red[g * 288 + 192 + pt] - R[11];
+    const float* op = oacc + g * 480 + (pt >> 3) * 40 + 16 + (pt & 7);
+    const float x = op[0] - R[9], y = op[8] - R[10], zc = op[16] - R[11];
     const float lx = R[0] * x + R[3] * y + R[6] * zc, ly = R[1] * x + R[4] * y + R[7] * zc, lz = R[2] * x + R[5] * y + R[8] * zc;
     const uint32_t r = (uint32_t)(rowb + i0 + g);
     img_store(cat_img, Rp, r, 192 + pt, lx);
