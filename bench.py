@@ -196,25 +196,55 @@ def probe_forward(genie):
     torch.cuda.synchronize()
 
 
+def _time_launches(fn, reps):
+    import torch
+    for _ in range(3):
+        fn(0)
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(reps + 1)]
+    ev[0].record()
+    for i in range(reps):
+        fn(i)
+        ev[i + 1].record()
+    torch.cuda.synchronize()
+    return sorted(ev[i].elapsed_time(ev[i + 1]) for i in range(reps))[reps // 2]
+
+
 def dominant_kernel_roofline(genie, ctx, lib, prec, pk, reps=10):
-    """CUDA-event time of the kernel with the largest share of the step (profiles/): the fused
-    pair transition.  Algorithmic FLOPs per launch = B*N^2 * 262,144 (LN-free GEMM
-    terms 2*128*512*2 per pixel); the p tensor it streams (B*N^2*128*4 B = 134 MB) exceeds L2."""
+    """CUDA-event time, on the launching stream, of the kernel with the largest share of the step
+    (profiles/r01_launches_*.txt).  bf16 mode: K4 trimul_proj_tc, HBM-bound; algorithmic bytes per
+    launch = 10 S = B*N^2*128 * (4 read p fp32 + 3 * 2 write a, b, g bf16); its
+    inputs + outputs (335 MB) exceed the 126 MB L2, so every timed launch streams from HBM.  fp32 mode:
+    the fused pair transition, FLOP-bound on the CUDA cores, reported against the tensor peak."""
     import torch
     from genie2_b200 import _lib
     dev = genie.device
     M = B * L * L
     p = torch.randn(B, L, L, 128, device=dev)
     stream = torch.cuda.current_stream(dev).cuda_stream
-    for _ in range(3):
-        _lib.check(lib.gb_k_pair_transition(ctx, 0, p.data_ptr(), stream), ctx, 'gb_k_pair_transition')
-    ev = [torch.cuda.Event(enable_timing=True) for _ in range(reps + 1)]
-    ev[0].record()
-    for i in range(reps):
-        _lib.check(lib.gb_k_pair_transition(ctx, i % 5, p.data_ptr(), stream), ctx, 'gb_k_pair_transition')
-        ev[i + 1].record()
-    torch.cuda.synchronize()
-    ms = sorted(ev[i].elapsed_time(ev[i + 1]) for i in range(reps))[reps // 2]
+    others = {}
+    if prec == 'bf16':
+        S = M * 128
+        _lib.check(lib.gb_k_trimul(ctx, 0, 1, p.data_ptr(), stream), ctx, 'gb_k_trimul')
+        stage = lambda st: (lambda i: _lib.check(lib.gb_k_trimul_stage(ctx, i % 5, i & 1, st, p.data_ptr(), stream), ctx, 'stage'))
+        ms = _time_launches(stage(1), reps)
+        ms5, ms6 = _time_launches(stage(2), reps), _time_launches(stage(3), reps)
+        ms7 = _time_launches(lambda i: _lib.check(lib.gb_k_pair_transition(ctx, i % 5, p.data_ptr(), stream), ctx, 'k7'), reps)
+        others = {
+            'trimul_contract_tc': {'ms': ms5, 'tflops': 2.0 * B * 128 * L ** 3 / (ms5 * 1e-3) / 1e12, 'hbm_gbs': 6.0 * S / (ms5 * 1e-3) / 1e9},
+            'trimul_out_tc': {'ms': ms6, 'hbm_gbs': 12.0 * S / (ms6 * 1e-3) / 1e9},
+            'pair_transition_tc': {'ms': ms7, 'tflops': M * 262144.0 / (ms7 * 1e-3) / 1e12, 'hbm_gbs': 8.0 * S / (ms7 * 1e-3) / 1e9},
+        }
+        nbytes = 10.0 * S
+        achieved = nbytes / (ms * 1e-3) / 1e9
+        traffic = None
+        prof = os.path.join(ROOT, 'profiles', 'r01_ncu_summary.json')
+        if os.path.exists(prof):
+            traffic = json.load(open(prof)).get('trimul_proj_tc_kernel', {}).get('dram_bytes_per_launch')
+        return {'kernel': 'trimul_proj_tc_kernel (K4: LayerNorm + gated projections, bf16 tcgen05)', 'bound': 'hbm', 'achieved': achieved,
+                'peak': pk['hbm'], 'unit': 'GB/s', 'frac': achieved / pk['hbm'], 'traffic': traffic, 'ms_per_launch': ms,
+                'algorithmic_bytes_per_launch': nbytes, 'peak_source': pk['src'] + ' HBM copy',
+                'tensor_tflops': 2.0 * 128 * 640 * M / (ms * 1e-3) / 1e12, 'other_kernels': others}
+    ms = _time_launches(lambda i: _lib.check(lib.gb_k_pair_transition(ctx, i % 5, p.data_ptr(), stream), ctx, 'k7'), reps)
     flops = M * 262144.0
     achieved = flops / (ms * 1e-3) / 1e12
     peak = pk['tensor_burst']

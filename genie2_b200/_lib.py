@@ -65,6 +65,7 @@ SYMBOLS = {
     'gb_workspace_bytes': (C.c_int64, [_P]),
     'gb_k_frenet': (C.c_int, [_P, _P, _P, C.c_int, C.c_int, _P, _P]),
     'gb_k_trimul': (C.c_int, [_P, C.c_int, C.c_int, _P, _P]),
+    'gb_k_trimul_stage': (C.c_int, [_P, C.c_int, C.c_int, C.c_int, _P, _P]),
     'gb_k_pair_transition': (C.c_int, [_P, C.c_int, _P, _P]),
     'gb_k_tri_attention': (C.c_int, [_P, C.c_int, C.c_int, _P, _P]),
     'gb_k_ipa': (C.c_int, [_P, C.c_int, _P, _P, _P, _P, _P, _P]),

@@ -750,6 +750,15 @@ extern "C" int gb_k_trimul(gb_ctx* c, int layer, int outgoing, float* p, void* s
   return run_trimul(c, outgoing ? c->pair[layer].mul_out : c->pair[layer].mul_in, outgoing != 0, p, (cudaStream_t)stream);
 }
 
+extern "C" int gb_k_trimul_stage(gb_ctx* c, int layer, int outgoing, int stage, float* p, void* stream) {
+  int rc = check_ready(c, "gb_k_trimul_stage");
+  if (rc) return rc;
+  if (!p || layer < 0 || layer >= c->d.n_pair_transform_layer || !c->d.include_mul_update || stage < 1 || stage > 3)
+    return gb_fail(c, GB_ERR_INVALID, "gb_k_trimul_stage: bad arguments");
+  if (c->precision != GB_PREC_BF16) return gb_fail(c, GB_ERR_UNSUPPORTED, "gb_k_trimul_stage: tensor-core (bf16) mode only");
+  return tc_trimul_stage(c, outgoing ? c->pair[layer].mul_out : c->pair[layer].mul_in, outgoing != 0, stage, p, (cudaStream_t)stream);
+}
+
 extern "C" int gb_k_pair_transition(gb_ctx* c, int layer, float* p, void* stream) {
   int rc = check_ready(c, "gb_k_pair_transition");
   if (rc) return rc;

@@ -752,25 +752,33 @@ int tc_bind_workspace(gb_ctx* c, void* base, size_t bytes, int B, int N) {
   return tc_struct_bind(c, q + used, bytes - used, B, N);
 }
 
-int tc_trimul(gb_ctx* c, const TriMulW& w, bool outgoing, float* p, cudaStream_t st) {
-  if (c->precision != GB_PREC_BF16) return gb_fail(c, GB_ERR_UNSUPPORTED, "tensor-core path: only bf16 precision is built in this revision");
+int tc_trimul_stage(gb_ctx* c, const TriMulW& w, bool outgoing, int stage, float* p, cudaStream_t st) {
+  if (c->precision != GB_PREC_BF16) return gb_fail(c, GB_ERR_UNSUPPORTED, "tensor-core path: tf32 kernels are not built in this revision (use bf16 or fp32)");
   TcState* s = static_cast<TcState*>(c->tc_state);
   const int B = c->B, N = c->N, Np = s->Np;
   const unsigned tiles = (unsigned)B * ((N + 1) / 2) * (Np / 64);
-  trimul_proj_tc_kernel<<<tiles, 256, K4_SMEM, st>>>(p, N, Np, c->mask, w.ln_in_g, w.ln_in_b, (const bf16*)w.tc_Wproj, w.tc_bproj,
-                                                     s->a, s->b, s->g, outgoing ? 0 : 1);
-  GB_LAUNCH_CHECK(c, "trimul_proj_tc");
-  const int NJ = 256;
-  const unsigned cgrid = (unsigned)B * 128 * ((Np + 127) / 128) * ((Np + NJ - 1) / NJ);
-  trimul_contract_tc_kernel<<<cgrid, 256, K5_SMEM, st>>>(s->a, s->b, s->x, N, Np, NJ);
-  GB_LAUNCH_CHECK(c, "trimul_contract_tc");
-  trimul_out_tc_kernel<<<tiles, 256, K6_SMEM, st>>>(s->x, s->g, p, N, Np, (const bf16*)w.tc_Wz, w.tc_uv, w.tc_uv + 128);
-  GB_LAUNCH_CHECK(c, "trimul_out_tc");
+  if (stage == 0 || stage == 1) {
+    trimul_proj_tc_kernel<<<tiles, 256, K4_SMEM, st>>>(p, N, Np, c->mask, w.ln_in_g, w.ln_in_b, (const bf16*)w.tc_Wproj, w.tc_bproj,
+                                                       s->a, s->b, s->g, outgoing ? 0 : 1);
+    GB_LAUNCH_CHECK(c, "trimul_proj_tc");
+  }
+  if (stage == 0 || stage == 2) {
+    const int NJ = 256;
+    const unsigned cgrid = (unsigned)B * 128 * ((Np + 127) / 128) * ((Np + NJ - 1) / NJ);
+    trimul_contract_tc_kernel<<<cgrid, 256, K5_SMEM, st>>>(s->a, s->b, s->x, N, Np, NJ);
+    GB_LAUNCH_CHECK(c, "trimul_contract_tc");
+  }
+  if (stage == 0 || stage == 3) {
+    trimul_out_tc_kernel<<<tiles, 256, K6_SMEM, st>>>(s->x, s->g, p, N, Np, (const bf16*)w.tc_Wz, w.tc_uv, w.tc_uv + 128);
+    GB_LAUNCH_CHECK(c, "trimul_out_tc");
+  }
   return GB_OK;
 }
 
+int tc_trimul(gb_ctx* c, const TriMulW& w, bool outgoing, float* p, cudaStream_t st) { return tc_trimul_stage(c, w, outgoing, 0, p, st); }
+
 int tc_pair_transition(gb_ctx* c, const TransitionW& w, float* p, cudaStream_t st) {
-  if (c->precision != GB_PREC_BF16) return gb_fail(c, GB_ERR_UNSUPPORTED, "tensor-core path: only bf16 precision is built in this revision");
+  if (c->precision != GB_PREC_BF16) return gb_fail(c, GB_ERR_UNSUPPORTED, "tensor-core path: tf32 kernels are not built in this revision (use bf16 or fp32)");
   const size_t M = (size_t)c->B * c->N * c->N;
   if (M >= (1ull << 31)) return gb_fail(c, GB_ERR_UNSUPPORTED, "pair map too large");
   pair_transition_tc_kernel<<<(unsigned)((M + 127) / 128), 256, K7_SMEM, st>>>(p, (uint32_t)M, c->N, c->mask, w.ln_g, w.ln_b,

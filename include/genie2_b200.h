@@ -162,6 +162,12 @@ int gb_k_frenet(const float* trans, const int32_t* chain_index, const int32_t* r
  * (p += update), i.e. including the residual add at pair_transform_net.py:111-112. */
 int gb_k_trimul(gb_ctx* ctx, int layer, int outgoing, float* p, void* stream);
 
+/* One kernel of the tensor-core (bf16) triangle update, for per-kernel timing and tests: stage 1 = LayerNorm +
+ * gated projections (triangular_multiplicative_update.py:97-103,107), 2 = the per-channel contraction
+ * (:57-82), 3 = LayerNorm_out + linear_z + gate + residual (:105-108).  Stages 2, 3 consume what the
+ * previous stage of the same context left in the workspace. */
+int gb_k_trimul_stage(gb_ctx* ctx, int layer, int outgoing, int stage, float* p, void* stream);
+
 /* PairTransition.forward + residual + the layer-final mask (pair_transition.py:48-87,
  * pair_transform_net.py:116-117): p = (p + transition(p)) * mask, in place. */
 int gb_k_pair_transition(gb_ctx* ctx, int layer, float* p, void* stream);

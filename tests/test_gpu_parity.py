@@ -202,3 +202,21 @@ def test_sample_loop_equals_stepwise():
     torch.cuda.synchronize()
     got = np.stack([f['atom_positions'] for f in a])
     assert np.array_equal(got.astype(np.float32), ts.trans.cpu().numpy())
+
+
+def test_cli_unconditional_end_to_end(tmp_path):
+    """The reference's CLI surface (genie/sample_unconditional.py flags) through the runner, random-init
+    weights, 4 diffusion steps: one PDB per (length, sample), C-alpha records only."""
+    from genie2_b200 import sample_unconditional as S
+    root = tmp_path / 'results' / 'tiny'
+    root.mkdir(parents=True)
+    (root / 'configuration').write_text('name tiny\nnumTimesteps 4\nnumPairTransformLayers 1\nnumStructureLayers 2\n')
+    out = tmp_path / 'out'
+    args = S.build_parser().parse_args([
+        '--name', 'tiny', '--epoch', '1', '--rootdir', str(tmp_path / 'results'), '--scale', '0.6', '--outdir', str(out),
+        '--num_samples', '3', '--batch_size', '2', '--min_length', '20', '--max_length', '22', '--random_init', '0'])
+    S.main(args)
+    files = sorted(os.listdir(out / 'pdbs'))
+    assert files == ['%d_%d.pdb' % (l, i) for l in (20, 21, 22) for i in range(3)]
+    lines = [l for l in open(out / 'pdbs' / '22_2.pdb') if l.startswith('ATOM')]
+    assert len(lines) == 22 and all(' CA ' in l for l in lines)
