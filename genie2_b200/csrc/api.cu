@@ -66,9 +66,9 @@ extern "C" int gb_create(gb_ctx** out, const gb_dims* d, int device) {
   cudaFuncSetAttribute(trimul_out_simt_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemPair);
   cudaFuncSetAttribute(pair_transition_simt_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemTrans);
   cudaFuncSetAttribute(ipa_attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+  triatt_set_attributes();
   cudaFuncSetAttribute(frenet_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
   cudaFuncSetAttribute(ddpm_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-  triatt_set_attributes();
   if (cudaGetLastError() != cudaSuccess) { delete c; return gb_fail(nullptr, GB_ERR_CUDA, "cudaFuncSetAttribute failed"); }
   int rc = tc_init(c);
   if (rc != GB_OK) { g_create_err = c->err; delete c; return rc; }
@@ -211,6 +211,9 @@ static int pack_triatt(gb_ctx* c, Getter& G, const std::string& pre, TriAttW& w)
   if (!G.ok) return GB_ERR_MISSING;
   w.ln_g = upload(c, lg); w.ln_b = upload(c, lb); w.Wbias = upload(c, wl);
   w.Wqkvg = upload(c, concat({&wq, &wk, &wv, &wg})); w.bg = upload(c, bg);
+  std::vector<float> bq(4 * hc, 0.f);   // q, k, v have no bias (primitives.py:243-251)
+  std::copy(bg.begin(), bg.end(), bq.begin() + 3 * hc);
+  w.bqkvg = upload(c, bq);
   w.Wo = upload(c, wo); w.bo = upload(c, bo);
   return GB_OK;
 }
@@ -422,6 +425,10 @@ static void carve_workspace(gb_ctx* c, Carver& k, int B, int N) {
   c->b = k.take<float>(M * 128);
   c->x = k.take<float>(M * 128);
   c->g = k.take<float>(M * 128);
+  if (c->d.include_tri_att) {   // a..g double as the [M][512] q|k|v|g buffer of K8
+    c->ta_x = k.take<float>(M * 128);
+    c->ta_bias = k.take<float>(M * TA_H);
+  }
 }
 
 extern "C" int gb_set_features(gb_ctx* c, const gb_features* f) {
@@ -540,6 +547,26 @@ static int run_trimul(gb_ctx* c, const TriMulW& w, bool outgoing, float* p, cuda
   return GB_OK;
 }
 
+// K8: p += TriangleAttention(p) (pair_transform_net.py:109-119); fp32 CUDA cores in every precision mode.
+static int run_triatt(gb_ctx* c, const TriAttW& w, bool starting, float* p, cudaStream_t st) {
+  const int B = c->B, N = c->N;
+  const size_t M = (size_t)B * N * N;
+  if (M > (size_t)INT32_MAX) return gb_fail(c, GB_ERR_UNSUPPORTED, "triangle attention: B*N*N too large");
+  if (triatt_smem_bytes(N) > 200 * 1024) return gb_fail(c, GB_ERR_UNSUPPORTED, "triangle attention: N = %d too large", N);
+  float* qkvg = c->a;   // a | b | x | g are contiguous: [M][512]
+  layernorm_rows_kernel<<<(unsigned)((M * 32 + 255) / 256), 256, 0, st>>>(p, c->ta_x, nullptr, w.ln_g, w.ln_b, (int)M, 128);
+  GB_LAUNCH_CHECK(c, "triatt_layer_norm");
+  sgemm_nt(st, c->ta_x, 128, w.Wqkvg, 128, w.bqkvg, nullptr, 0, qkvg, 512, (int)M, 512, 128, false);
+  GB_LAUNCH_CHECK(c, "triatt_qkvg");
+  sgemm_nt(st, c->ta_x, 128, w.Wbias, 128, nullptr, nullptr, 0, c->ta_bias, TA_H, (int)M, TA_H, 128, false);
+  GB_LAUNCH_CHECK(c, "triatt_bias");
+  triatt_core_kernel<<<dim3(N, B), 256, triatt_smem_bytes(N), st>>>(qkvg, c->ta_bias, c->mask, c->ta_x, N, starting ? 1 : 0);
+  GB_LAUNCH_CHECK(c, "triatt_core");
+  sgemm_nt(st, c->ta_x, 128, w.Wo, 128, w.bo, p, 128, p, 128, (int)M, 128, 128, false);
+  GB_LAUNCH_CHECK(c, "triatt_out");
+  return GB_OK;
+}
+
 static int run_transition(gb_ctx* c, const TransitionW& w, float* p, cudaStream_t st) {
   if (c->precision != GB_PREC_FP32) return tc_pair_transition(c, w, p, st);
   const size_t M = (size_t)c->B * c->N * c->N;
@@ -607,7 +634,6 @@ extern "C" int gb_denoise(gb_ctx* c, const float* rots, const float* trans, cons
   int rc = check_ready(c, "gb_denoise");
   if (rc) return rc;
   if (!rots || !trans || !timesteps || !z_out) return gb_fail(c, GB_ERR_INVALID, "gb_denoise: NULL pointer");
-  if (c->d.include_tri_att) return gb_fail(c, GB_ERR_UNSUPPORTED, "gb_denoise: triangle attention kernels not built in this revision");
   cudaStream_t st = (cudaStream_t)stream;
   const gb_dims& d = c->d;
   const int B = c->B, N = c->N, R = B * N, cs = d.c_s;
@@ -632,6 +658,10 @@ extern "C" int gb_denoise(gb_ctx* c, const float* rots, const float* trans, cons
     if (d.include_mul_update) {
       if ((rc = run_trimul(c, c->pair[l].mul_out, true, c->p, st))) return rc;
       if ((rc = run_trimul(c, c->pair[l].mul_in, false, c->p, st))) return rc;
+    }
+    if (d.include_tri_att) {
+      if ((rc = run_triatt(c, c->pair[l].att_start, true, c->p, st))) return rc;
+      if ((rc = run_triatt(c, c->pair[l].att_end, false, c->p, st))) return rc;
     }
     if ((rc = run_transition(c, c->pair[l].tr, c->p, st))) return rc;
   }
@@ -767,8 +797,11 @@ extern "C" int gb_k_pair_transition(gb_ctx* c, int layer, float* p, void* stream
 }
 
 extern "C" int gb_k_tri_attention(gb_ctx* c, int layer, int starting, float* p, void* stream) {
-  (void)layer; (void)starting; (void)p; (void)stream;
-  return gb_fail(c, GB_ERR_UNSUPPORTED, "gb_k_tri_attention: not built in this revision");
+  int rc = check_ready(c, "gb_k_tri_attention");
+  if (rc) return rc;
+  if (!c->d.include_tri_att) return gb_fail(c, GB_ERR_INVALID, "gb_k_tri_attention: include_tri_att is off in this context");
+  if (!p || layer < 0 || layer >= c->d.n_pair_transform_layer) return gb_fail(c, GB_ERR_INVALID, "gb_k_tri_attention: bad arguments");
+  return run_triatt(c, starting ? c->pair[layer].att_start : c->pair[layer].att_end, starting != 0, p, (cudaStream_t)stream);
 }
 
 extern "C" int gb_k_ipa(gb_ctx* c, int layer, const float* s, const float* p, const float* rots, const float* trans,

@@ -27,7 +27,7 @@ struct TransitionW {
   void *tc_W1, *tc_W2;
 };
 struct TriAttW {
-  float *ln_g, *ln_b, *Wbias /*[H][128]*/, *Wqkvg /*[4*H*C][128]: q|k|v|g*/, *bg, *Wo /*[128][H*C]*/, *bo;
+  float *ln_g, *ln_b, *Wbias /*[H][128]*/, *Wqkvg /*[4*H*C][128]: q|k|v|g*/, *bg, *Wo /*[128][H*C]*/, *bo, *bqkvg /*[4*H*C]: 0|0|0|bg*/;
 };
 struct PairLayerW {
   TriMulW mul_out, mul_in;
@@ -78,6 +78,7 @@ struct gb_ctx {
   size_t ws_bytes = 0;
   float *s = nullptr, *sA = nullptr, *sB = nullptr, *h1 = nullptr, *h2 = nullptr, *pipj = nullptr;
   float *p = nullptr, *a = nullptr, *b = nullptr, *x = nullptr, *g = nullptr;
+  float *ta_x = nullptr, *ta_bias = nullptr;   // triangle attention: LN(p) / gated o [M][128], bias [M][4]
   float *qkv = nullptr, *cat = nullptr, *rots_w = nullptr, *trans_w = nullptr, *z = nullptr;
   float *trans_io = nullptr, *rots_io = nullptr;   // gb_sample_host state
   int* t_dev = nullptr;                            // [B] timesteps

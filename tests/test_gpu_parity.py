@@ -43,7 +43,7 @@ def test_frenet_golden_and_random():
         assert float((out.cpu() - ref).abs().max()) < 2e-5, (B, N)
 
 
-@pytest.mark.parametrize('name', ['uncond_base_ragged', 'uncond_stock', 'motif_base', 'multichain'])
+@pytest.mark.parametrize('name', ['uncond_base_ragged', 'uncond_stock', 'motif_base', 'multichain', 'triatt'])
 def test_forward_matches_reference_fixture(name):
     """CUDA forward vs the unmodified reference's recorded outputs (quaternion sign replayed)."""
     cfg, sd, feats, t = load_forward_case(name)
@@ -220,3 +220,30 @@ def test_cli_unconditional_end_to_end(tmp_path):
     assert files == ['%d_%d.pdb' % (l, i) for l in (20, 21, 22) for i in range(3)]
     lines = [l for l in open(out / 'pdbs' / '22_2.pdb') if l.startswith('ATOM')]
     assert len(lines) == 22 and all(' CA ' in l for l in lines)
+
+
+@pytest.mark.parametrize('starting', [1, 0])
+@pytest.mark.parametrize('B,N', [(2, 21), (1, 70), (1, 280)])
+def test_triangle_attention_kernel(B, N, starting):
+    """K8 on its own (gb_k_tri_attention) vs the oracle's restatement of
+    modules/triangular_attention.py:67-130: starting and ending node, ragged masks, N above one
+    thread block of queries."""
+    import genie2_b200._lib as L
+    lib = L.load()
+    cfg = O.OracleConfig(include_tri_att=True, n_pair_transform_layer=1, n_structure_layer=1)
+    sd = W.make_state_dict(cfg, 21, 'activated')
+    model = make_denoiser(cfg, sd)
+    lens = [[N]] + [[max(3, N - 6 - 2 * i)] for i in range(B - 1)]
+    feats = feats_to(O.make_features(lens), DEV)
+    ctx = model.bind_features(feats, torch.device(DEV))
+    g = torch.Generator().manual_seed(N)
+    p0 = torch.randn(B, N, N, 128, generator=g) * 1.2 + 0.2
+    rm = feats['residue_mask'].cpu()
+    pm = rm.unsqueeze(1) * rm.unsqueeze(2)
+    pre = 'pair_transform_net.net.0.tri_att_%s' % ('start' if starting else 'end')
+    with torch.no_grad():
+        ref = O.triangle_attention(sd, cfg, pre, p0, pm, bool(starting))
+    p = p0.to(DEV).contiguous()
+    L.check(lib.gb_k_tri_attention(ctx, 0, starting, p.data_ptr(), None), ctx, 'gb_k_tri_attention')
+    torch.cuda.synchronize()
+    assert rel(p.cpu() - p0, ref) < TOL

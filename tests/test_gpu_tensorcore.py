@@ -124,3 +124,13 @@ def test_forward_bf16_vs_oracle_and_fp32_path():
     model.set_precision('fp32')
     o32, _ = run_cuda_forward(model, rots, trans, ts, feats, None)
     assert rel(o32['z'], ref['z']) < 1e-4
+
+
+def test_forward_bf16_with_triangle_attention_fixture():
+    """include_tri_att configuration in bf16 mode (K8 itself stays fp32) against the reference fixture."""
+    from common import load_forward_case
+    cfg, sd, feats, t = load_forward_case('triatt')
+    model = make_denoiser(cfg, sd, precision='bf16')
+    o, _ = run_cuda_forward(model, t['rots'], t['trans'], t['timesteps'], feats, t['quat'])
+    assert rel(o['p'], t['p']) < 2e-2
+    assert rel(o['z'], t['z']) < TOL_Z_BF16
