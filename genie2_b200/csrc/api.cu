@@ -172,7 +172,7 @@ static int pack_trimul(gb_ctx* c, Getter& G, const std::string& pre, TriMulW& w)
   w.WzT = upload(c, transpose(lz, 128, 128)); w.bz = upload(c, lzb);
   w.ln_in_g = upload(c, lig); w.ln_in_b = upload(c, lib);
   w.ln_out_g = upload(c, log_); w.ln_out_b = upload(c, lob);
-  return tc_pack_trimul(c, w, ap, ag, bp, bg, lg, lz, apb, agb, bpb, bgb, lgb, lzb, log_, lob);
+  return tc_pack_trimul(c, w, ap, ag, bp, bg, lg, lz, apb, agb, bpb, bgb, lgb, lzb, lig, lib, log_, lob);
 }
 
 static int pack_transition(gb_ctx* c, Getter& G, const std::string& pre, TransitionW& w) {

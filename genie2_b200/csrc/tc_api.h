@@ -10,7 +10,13 @@ int tc_pack_trimul(gb_ctx* c, TriMulW& w, const std::vector<float>& ap, const st
                    const std::vector<float>& bp, const std::vector<float>& bg, const std::vector<float>& lg,
                    const std::vector<float>& lz, const std::vector<float>& apb, const std::vector<float>& agb,
                    const std::vector<float>& bpb, const std::vector<float>& bgb, const std::vector<float>& lgb,
-                   const std::vector<float>& lzb, const std::vector<float>& lno_g, const std::vector<float>& lno_b);
+                   const std::vector<float>& lzb, const std::vector<float>& lni_g, const std::vector<float>& lni_b,
+                   const std::vector<float>& lno_g, const std::vector<float>& lno_b);
+// K4 (tc_proj.cu): folded / scaled weight images, SM count, launch
+int tc_proj_init(gb_ctx* c);
+int tc_pack_trimul_proj(gb_ctx* c, TriMulW& w, const std::vector<float>* Wm[5], const std::vector<float>* bm[5],
+                        const std::vector<float>& ln_g, const std::vector<float>& ln_b);
+int tc_launch_trimul_proj(gb_ctx* c, const TriMulW& w, bool outgoing, const float* p, cudaStream_t st);
 int tc_pack_transition(gb_ctx* c, TransitionW& w, const std::vector<float>& w1, const std::vector<float>& w2);
 // workspace the tensor-core path needs for a (B,N) batch, carved by gb_set_features
 size_t tc_workspace_bytes(const gb_ctx* c, int B, int N);

@@ -268,159 +268,7 @@ __global__ void __launch_bounds__(256, 2) pair_transition_tc_kernel(
 // that in both cases it emits A[row][k = col] (and B likewise) K-major and K5 is a plain A . B^T:
 //   outgoing x_ij = sum_k a_ik b_jk ;  incoming x_ij = sum_k a_ki b_kj = sum_k aT_ik bT_jk.
 // ---------------------------------------------------------------------------------------------
-// ---------------------------------------------------------------------------------------------
-// K4 trimul_proj_tc (triangular_multiplicative_update.py:97-103,107)
-//   Wimg: [a: 2 kb x 256 rows (a_p | a_g) x 64] 64K | [b: likewise] 64K | [g: 2 kb x 128 x 64] 32K
-//   bias: a_p | a_g | b_p | b_g | g   (5 x 128)
-//   a_out / b_out: [B][128 ch][Np/64 kb][Np rows][64] tile images (bf16);  g_out [B*N*N][128] bf16
-// The gated projections are computed TRANSPOSED, D[channel][pixel] = W . X^T (weights as the M-side
-// operand, the LayerNorm'ed pixel tile X as the N-side operand; both are the same K-major images):
-// a TMEM lane is then a channel, and the 64 pixel columns a thread drains are exactly one 128-byte
-// row of that channel's operand image -- eight 16-byte stores instead of 64 two-byte ones, biases
-// in two registers.  The output gate g stays pixel-major (D[pixel][channel]).
-// Shared: X 32K | W 64K | barriers, masks; 256 TMEM columns; 2 CTAs / SM.
-// ---------------------------------------------------------------------------------------------
-#define K4_SMEM (32768 + 65536 + 1024 + 64 + 512)
-
-// D[128 ch][128 px] = Wrows . X^T for one 128-row block of a 256-row weight image pair
-__device__ __forceinline__ void k4_mma_T(uint32_t tmem_d, uint32_t w_rows, uint32_t x_base) {
-  const uint32_t idesc = umma_idesc(128, 128);
-#pragma unroll
-  for (int kb = 0; kb < 2; ++kb)
-#pragma unroll
-    for (int k = 0; k < 4; ++k)
-      umma(tmem_d, umma_desc(w_rows + kb * (256 * 128) + k * 32), umma_desc(x_base + kb * 16384 + k * 32), idesc, (kb | k) ? 1u : 0u);
-}
-
-__global__ void __launch_bounds__(256, 2) trimul_proj_tc_kernel(
-    const float* __restrict__ p, int N, int Np, const int* __restrict__ rmask, const float* __restrict__ ln_g,
-    const float* __restrict__ ln_b, const bf16* __restrict__ Wimg, const float* __restrict__ bias,
-    bf16* __restrict__ a_out, bf16* __restrict__ b_out, bf16* __restrict__ g_out, int incoming) {
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* sm = smem_base_1024(smem_raw);
-  uint8_t* X = sm;
-  uint8_t* W = sm + 32768;
-  uint64_t* bar_w = reinterpret_cast<uint64_t*>(sm + 98304);
-  uint64_t* bar_mma = bar_w + 1;
-  uint32_t* tslot = reinterpret_cast<uint32_t*>(bar_w + 2);
-  float* pmask = reinterpret_cast<float*>(sm + 98304 + 64);      // [128] pair mask of the tile's pixels
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const PixTile T = pix_tile(blockIdx.x, N, Np);
-
-  if (tid == 0) {
-    mbar_init(bar_w, 1);
-    mbar_init(bar_mma, 1);
-    fence_mbar_init();
-    mbar_expect_tx(bar_w, 65536);
-    bulk_g2s(W, Wimg, 65536, bar_w);
-  }
-  if (warp == 1) tmem_alloc(tslot, 256);
-  const size_t sample = (size_t)T.b * N * N;
-  auto pixel_of = [&](uint32_t mm, bool& ok) -> size_t {   // source pixel (flat index into [B*N*N])
-    const uint32_t row = 2 * T.t2 + (mm >> 6), col = 64 * T.jb + (mm & 63);
-    ok = row < (uint32_t)N && col < (uint32_t)N;
-    return sample + (incoming ? (size_t)col * N + row : (size_t)row * N + col);
-  };
-  if (tid < 128) {
-    const uint32_t row = 2 * T.t2 + (tid >> 6), col = 64 * T.jb + (tid & 63);
-    pmask[tid] = (row < (uint32_t)N && col < (uint32_t)N) ? (float)(rmask[T.b * N + row] * rmask[T.b * N + col]) : 0.f;
-  }
-  ln_rows_to_image(X, [&](int mm) -> const float* { bool ok; const size_t px = pixel_of(mm, ok); return ok ? p + px * 128 : nullptr; },
-                   ln_g, ln_b);
-  fence_proxy_async();
-  tc_fence_before();
-  __syncthreads();
-  tc_fence_after();
-  const uint32_t tmem = *tslot;
-  const uint32_t q = warp & 3, h = warp >> 2;
-  const uint32_t t_lane = tmem + ((q * 32u) << 16);
-  // transposed epilogue: this thread owns channel ch and the pixel columns [64 h, 64 h + 64) = image row orow
-  const uint32_t ch = q * 32 + lane, orow = 2 * T.t2 + h;
-  const size_t img_row = ((((size_t)T.b * 128 + ch) * (Np >> 6) + T.jb) * Np + orow) * 64;   // element offset of the 128-byte row
-
-  for (int part = 0; part < 2; ++part) {     // part 0 -> a, part 1 -> b
-    if (tid == 0) {
-      mbar_wait(bar_w, part);
-      tc_fence_after();
-      k4_mma_T(tmem, smem_u32(W), smem_u32(X));                  // proj -> cols [0,128)
-      k4_mma_T(tmem + 128, smem_u32(W) + 16384, smem_u32(X));    // gate -> cols [128,256)
-      umma_commit(bar_mma);
-    }
-    __syncwarp();
-    mbar_wait(bar_mma, part);
-    tc_fence_after();
-    if (tid == 0) {
-      const uint32_t bytes = part == 0 ? 65536u : 32768u;
-      mbar_expect_tx(bar_w, bytes);
-      bulk_g2s(W, Wimg + (size_t)(part + 1) * 32768, bytes, bar_w);
-    }
-    __syncwarp();
-    const float bp = bias[part * 256 + ch], bg = bias[part * 256 + 128 + ch];
-    uint8_t* dst = reinterpret_cast<uint8_t*>((part == 0 ? a_out : b_out) + img_row);
-#pragma unroll 1
-    for (int cc = 0; cc < 2; ++cc) {
-      uint32_t vp[32], vg[32];
-      tmem_ld32(t_lane + h * 64 + cc * 32, vp);
-      tmem_ld32(t_lane + 128 + h * 64 + cc * 32, vg);
-      tmem_ld_wait();
-      if (orow < (uint32_t)N) {
-        const float4* mk4 = reinterpret_cast<const float4*>(pmask + h * 64 + cc * 32);
-#pragma unroll
-        for (int c8 = 0; c8 < 4; ++c8) {
-          const float4 m0 = mk4[2 * c8], m1 = mk4[2 * c8 + 1];
-          const float mk[8] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
-          float o[8];
-#pragma unroll
-          for (int e = 0; e < 8; ++e)
-            o[e] = (__uint_as_float(vp[8 * c8 + e]) + bp) * fast_sigmoid(__uint_as_float(vg[8 * c8 + e]) + bg) * mk[e];
-          uint4 w;
-          w.x = pack_bf16(o[0], o[1]); w.y = pack_bf16(o[2], o[3]); w.z = pack_bf16(o[4], o[5]); w.w = pack_bf16(o[6], o[7]);
-          *reinterpret_cast<uint4*>(dst + ((((uint32_t)(cc * 4 + c8)) ^ (orow & 7u)) << 4)) = w;
-        }
-      }
-    }
-    tc_fence_before();
-    __syncthreads();
-  }
-  // output gate g = sigmoid(linear_g(LN z)), pixel-major bf16: D[pixel][channel] = X . Wg^T
-  if (tid == 0) {
-    mbar_wait(bar_w, 0);
-    tc_fence_after();
-    umma_tile(tmem, smem_u32(X), smem_u32(W), 128, 2, false);
-    umma_commit(bar_mma);
-  }
-  __syncwarp();
-  mbar_wait(bar_mma, 0);
-  tc_fence_after();
-  const uint32_t m = q * 32 + lane;
-  bool valid;
-  const size_t px = pixel_of(m, valid);
-#pragma unroll 1
-  for (int cc = 0; cc < 2; ++cc) {
-    const int c0 = h * 64 + cc * 32;
-    uint32_t v[32];
-    tmem_ld32(t_lane + c0, v);
-    tmem_ld_wait();
-    if (valid) {
-      const float4* bg4 = reinterpret_cast<const float4*>(bias + 512 + c0);
-      uint4* dst = reinterpret_cast<uint4*>(g_out + px * 128 + c0);
-#pragma unroll
-      for (int k4 = 0; k4 < 4; ++k4) {
-        const float4 b0 = bg4[2 * k4], b1 = bg4[2 * k4 + 1];
-        uint4 o;
-        o.x = pack_bf16(fast_sigmoid(__uint_as_float(v[8 * k4 + 0]) + b0.x), fast_sigmoid(__uint_as_float(v[8 * k4 + 1]) + b0.y));
-        o.y = pack_bf16(fast_sigmoid(__uint_as_float(v[8 * k4 + 2]) + b0.z), fast_sigmoid(__uint_as_float(v[8 * k4 + 3]) + b0.w));
-        o.z = pack_bf16(fast_sigmoid(__uint_as_float(v[8 * k4 + 4]) + b1.x), fast_sigmoid(__uint_as_float(v[8 * k4 + 5]) + b1.y));
-        o.w = pack_bf16(fast_sigmoid(__uint_as_float(v[8 * k4 + 6]) + b1.z), fast_sigmoid(__uint_as_float(v[8 * k4 + 7]) + b1.w));
-        dst[k4] = o;
-      }
-    }
-  }
-  tc_fence_before();
-  __syncthreads();
-  if (warp == 1) tmem_dealloc(tmem, 256);
-}
-
+// K4 (gated projections) lives in tc_proj.cu.
 // ---------------------------------------------------------------------------------------------
 // K5 trimul_contract_tc (triangular_multiplicative_update.py:57-82 with the operand orientation
 // fixed by K4): per (sample b, channel c): X[i][j] = sum_k A[i][k] B[j][k].
@@ -665,12 +513,12 @@ __global__ void __launch_bounds__(256, 3) trimul_out_tc_kernel(
 int tc_init(gb_ctx* c) {
   cudaError_t e;
   if ((e = cudaFuncSetAttribute(pair_transition_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, K7_SMEM)) != cudaSuccess ||
-      (e = cudaFuncSetAttribute(trimul_proj_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, K4_SMEM)) != cudaSuccess ||
       (e = cudaFuncSetAttribute(trimul_contract_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, K5_SMEM)) != cudaSuccess ||
       (e = cudaFuncSetAttribute(trimul_out_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, K6_SMEM)) != cudaSuccess)
     return gb_fail(c, GB_ERR_CUDA, "tc_init: cudaFuncSetAttribute failed: %s", cudaGetErrorString(e));
   c->tc_state = new TcState();
-  return tc_struct_init(c);
+  int rc = tc_proj_init(c);
+  return rc != GB_OK ? rc : tc_struct_init(c);
 }
 
 void tc_destroy(gb_ctx* c) {
@@ -682,12 +530,14 @@ int tc_pack_trimul(gb_ctx* c, TriMulW& w, const std::vector<float>& ap, const st
                    const std::vector<float>& bp, const std::vector<float>& bg, const std::vector<float>& lg,
                    const std::vector<float>& lz, const std::vector<float>& apb, const std::vector<float>& agb,
                    const std::vector<float>& bpb, const std::vector<float>& bgb, const std::vector<float>& lgb,
-                   const std::vector<float>& lzb, const std::vector<float>& lno_g, const std::vector<float>& lno_b) {
-  std::vector<uint16_t> img(5 * 128 * 128);
-  pack_image(img.data(), 256, 128, [&](int r, int k) { return r < 128 ? ap[(size_t)r * 128 + k] : ag[(size_t)(r - 128) * 128 + k]; });
-  pack_image(img.data() + 32768, 256, 128, [&](int r, int k) { return r < 128 ? bp[(size_t)r * 128 + k] : bg[(size_t)(r - 128) * 128 + k]; });
-  pack_image(img.data() + 65536, 128, 128, [&](int r, int k) { return lg[(size_t)r * 128 + k]; });
-  w.tc_Wproj = upload_bytes(c, img.data(), img.size() * 2);
+                   const std::vector<float>& lzb, const std::vector<float>& lni_g, const std::vector<float>& lni_b,
+                   const std::vector<float>& lno_g, const std::vector<float>& lno_b) {
+  {
+    const std::vector<float>* Wm[5] = {&ap, &ag, &bp, &bg, &lg};
+    const std::vector<float>* bm[5] = {&apb, &agb, &bpb, &bgb, &lgb};
+    const int rc = tc_pack_trimul_proj(c, w, Wm, bm, lni_g, lni_b);
+    if (rc != GB_OK) return rc;
+  }
   // K6 folds LayerNorm_out into the GEMM: W' = W_z * gamma, u = row sums of bf16(W'), v = W_z beta + b_z
   std::vector<uint16_t> wz(128 * 128);
   pack_image(wz.data(), 128, 128, [&](int r, int k) { return lz[(size_t)r * 128 + k] * lno_g[k]; });
@@ -706,10 +556,7 @@ int tc_pack_trimul(gb_ctx* c, TriMulW& w, const std::vector<float>& ap, const st
     uv[128 + n] = (float)v;
   }
   w.tc_uv = (float*)upload_bytes(c, uv.data(), uv.size() * 4);
-  std::vector<float> bias;
-  for (const std::vector<float>* v : {&apb, &agb, &bpb, &bgb, &lgb}) bias.insert(bias.end(), v->begin(), v->end());
-  w.tc_bproj = (float*)upload_bytes(c, bias.data(), bias.size() * 4);
-  if (!w.tc_Wproj || !w.tc_Wz || !w.tc_bproj || !w.tc_uv) return gb_fail(c, GB_ERR_CUDA, "tc_pack_trimul: device allocation failed");
+  if (!w.tc_Wz || !w.tc_uv) return gb_fail(c, GB_ERR_CUDA, "tc_pack_trimul: device allocation failed");
   return GB_OK;
 }
 
@@ -758,9 +605,8 @@ int tc_trimul_stage(gb_ctx* c, const TriMulW& w, bool outgoing, int stage, float
   const int B = c->B, N = c->N, Np = s->Np;
   const unsigned tiles = (unsigned)B * ((N + 1) / 2) * (Np / 64);
   if (stage == 0 || stage == 1) {
-    trimul_proj_tc_kernel<<<tiles, 256, K4_SMEM, st>>>(p, N, Np, c->mask, w.ln_in_g, w.ln_in_b, (const bf16*)w.tc_Wproj, w.tc_bproj,
-                                                       s->a, s->b, s->g, outgoing ? 0 : 1);
-    GB_LAUNCH_CHECK(c, "trimul_proj_tc");
+    const int rc = tc_launch_trimul_proj(c, w, outgoing, p, st);
+    if (rc != GB_OK) return rc;
   }
   if (stage == 0 || stage == 2) {
     const int NJ = 256;

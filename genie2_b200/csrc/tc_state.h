@@ -17,6 +17,7 @@ struct TcState {
   bf16 *x = nullptr;                 // [B][128][Np][Np]
   bf16 *g = nullptr;                 // [B*N*N][128]
   size_t ab_bytes = 0;
+  int num_sms = 0;
   // structure net
   int Rp = 0;                        // B*N rounded up to a multiple of 128
   bf16 *s_img = nullptr, *cat_img = nullptr, *ln1_img = nullptr, *h1_img = nullptr, *h2_img = nullptr;

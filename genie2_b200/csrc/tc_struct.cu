@@ -300,15 +300,6 @@ __global__ void __launch_bounds__(256, 2) ipa_prep_tc_kernel(const float* __rest
 #define IA_OFF_BAR (IA_OFF_FR + IA_G * 12 * 4)
 #define IA_SMEM (IA_OFF_BAR + 128 + 1024)
 
-__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&v)[16]) {
-  asm volatile(
-      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
-      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
-      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
-        "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
-      : "r"(taddr)
-      : "memory");
-}
 // 2-byte store of element k of row r of a [.][Rp][64] operand image
 __device__ __forceinline__ void img_store(bf16* img, int Rp, uint32_t r, uint32_t k, float v) {
   uint8_t* base = reinterpret_cast<uint8_t*>(img + ((size_t)(k >> 6) * Rp + r) * 64);
