@@ -322,20 +322,20 @@ __global__ void __launch_bounds__(256, 2) trimul_contract_tc_kernel(const bf16* 
     }
     __syncwarp();
   } else if (warp == 1) {
-    if (lane == 0) {
-      const uint32_t idesc = umma_idesc(128, nj);
-      for (int kb = 0; kb < nkb; ++kb) {
-        const int s = kb % K5_STAGES;
-        mbar_wait(full + s, (kb / K5_STAGES) & 1);
-        tc_fence_after();
-        const uint32_t sa = smem_u32(sm + s * K5_STAGE_BYTES), sb = sa + 16384;
+    const uint32_t idesc = umma_idesc(128, nj), tm = warp_uniform(tmem);
+    for (int kb = 0; kb < nkb; ++kb) {
+      const int s = kb % K5_STAGES;
+      mbar_wait(full + s, (kb / K5_STAGES) & 1);
+      tc_fence_after();
+      const uint32_t sa = smem_u32(sm + s * K5_STAGE_BYTES), sb = sa + 16384;
+      if (elect_one()) {
 #pragma unroll
-        for (int k = 0; k < 4; ++k) umma(tmem, umma_desc(sa + k * 32), umma_desc(sb + k * 32), idesc, (kb | k) ? 1u : 0u);
+        for (int k = 0; k < 4; ++k) umma(tm, umma_desc(sa + k * 32), umma_desc(sb + k * 32), idesc, (kb | k) ? 1u : 0u);
         umma_commit(empty + s);
+        if (kb == nkb - 1) umma_commit(done);
       }
-      umma_commit(done);
+      __syncwarp();
     }
-    __syncwarp();
   }
   mbar_wait(done, 0);
   tc_fence_after();
@@ -354,14 +354,20 @@ __global__ void __launch_bounds__(256, 2) trimul_contract_tc_kernel(const bf16* 
       const uint32_t j = jb * NJ + c0, jb64 = j >> 6, q0 = (j & 63) >> 3;
       uint8_t* dst = reinterpret_cast<uint8_t*>(x) +
                      (((((size_t)bb * (Np >> 1) + (i >> 1)) * (Np >> 6) + jb64) * 2 + (i & 1)) * 128 + cch) * 128;
+      const uint32_t sw = cch & 7u;
 #pragma unroll
-      for (int k4 = 0; k4 < 4; ++k4) {
-        uint4 o;
-        o.x = pack_bf16(__uint_as_float(v[8 * k4 + 0]), __uint_as_float(v[8 * k4 + 1]));
-        o.y = pack_bf16(__uint_as_float(v[8 * k4 + 2]), __uint_as_float(v[8 * k4 + 3]));
-        o.z = pack_bf16(__uint_as_float(v[8 * k4 + 4]), __uint_as_float(v[8 * k4 + 5]));
-        o.w = pack_bf16(__uint_as_float(v[8 * k4 + 6]), __uint_as_float(v[8 * k4 + 7]));
-        *reinterpret_cast<uint4*>(dst + (((q0 + k4) ^ (cch & 7u)) << 4)) = o;
+      for (int kp = 0; kp < 2; ++kp) {     // two 16-byte chunks = one 32-byte sector per store
+        uint4 o[2];
+#pragma unroll
+        for (int k4 = 0; k4 < 2; ++k4) {
+          const uint32_t* vv = v + 16 * kp + 8 * k4;
+          o[k4].x = pack_bf16(__uint_as_float(vv[0]), __uint_as_float(vv[1]));
+          o[k4].y = pack_bf16(__uint_as_float(vv[2]), __uint_as_float(vv[3]));
+          o[k4].z = pack_bf16(__uint_as_float(vv[4]), __uint_as_float(vv[5]));
+          o[k4].w = pack_bf16(__uint_as_float(vv[6]), __uint_as_float(vv[7]));
+        }
+        const bool swap = sw & 1u;
+        st_global_32B(dst + (((q0 + 2 * kp) ^ (sw & 6u)) << 4), swap ? o[1] : o[0], swap ? o[0] : o[1]);
       }
     }
   }

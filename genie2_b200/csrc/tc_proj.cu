@@ -33,9 +33,9 @@
 using namespace tc;
 
 #define K4_THREADS 544
-#define K4_OFF_X 163840u
-#define K4_OFF_BAR 229376u
-#define K4_SMEM (229376 + 128 + 1408 + 1024)   // barriers | masks 800 B + g bias 512 B (+ pad) | alignment slack
+#define K4_OFF_X 32768u
+#define K4_OFF_BAR 98304u
+#define K4_SMEM (98304 + 128 + 1408 + 1024)   // barriers | masks 800 B + g bias 512 B (+ pad) | alignment slack
 
 __device__ __forceinline__ float tanh_approx(float x) {
   float t;
@@ -59,7 +59,7 @@ __global__ void __launch_bounds__(K4_THREADS, 1) trimul_proj_tc_kernel(
 #define TR(idx) do { if (trace && blockIdx.x == 0 && lane == 0 && it < 8) trace[(it) * 64 + (idx)] = clock64(); } while (0)
   extern __shared__ uint8_t smem_raw[];
   uint8_t* sm = smem_base_1024(smem_raw);
-  uint8_t* W = sm;                       // a 64K | b 64K | g 32K
+  uint8_t* W = sm;                       // g weight image 32K (a / b weights live in tensor memory)
   uint8_t* X = sm + K4_OFF_X;            // 2 x 32K
   uint64_t* full_x = reinterpret_cast<uint64_t*>(sm + K4_OFF_BAR);
   uint64_t* empty_x = full_x + 2;
@@ -75,7 +75,7 @@ __global__ void __launch_bounds__(K4_THREADS, 1) trimul_proj_tc_kernel(
 
   if (tid == 0) {
     for (int i = 0; i < 2; ++i) { mbar_init(full_x + i, 8); mbar_init(empty_x + i, 1); }
-    for (int i = 0; i < 4; ++i) { mbar_init(slot_full + i, 1); mbar_init(slot_free + i, 8); }
+    for (int i = 0; i < 2; ++i) { mbar_init(slot_full + i, 1); mbar_init(slot_free + i, 8); }
     mbar_init(bar_w, 1);
     fence_mbar_init();
   }
@@ -85,13 +85,36 @@ __global__ void __launch_bounds__(K4_THREADS, 1) trimul_proj_tc_kernel(
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *tslot;
+  if (warp < 8) {
+    // a_p | a_g | b_p | b_g rows -> TMEM columns [0,256): lane = output channel, 64 columns = K 128 bf16 in pairs
+    const uint32_t q = warp & 3;
+#pragma unroll 1
+    for (int bi = 0; bi < 2; ++bi) {
+      const int blk = (warp >> 2) * 2 + bi;
+      const uint4* src = reinterpret_cast<const uint4*>(Wimg + 16384 + ((size_t)blk * 128 + q * 32 + lane) * 128);
+#pragma unroll
+      for (int hf = 0; hf < 2; ++hf) {
+        uint32_t v[32];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const uint4 t = src[hf * 8 + i];
+          v[4 * i] = t.x; v[4 * i + 1] = t.y; v[4 * i + 2] = t.z; v[4 * i + 3] = t.w;
+        }
+        tmem_st32(tmem + ((q * 32u) << 16) + blk * 64 + hf * 32, v);
+      }
+    }
+    tmem_st_wait();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
   const int my_tiles = (ntiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
 
   if (warp == 16) {
     // ------------------------------------------------------------------ weights + MMA issue (converged warp)
     if (lane == 0) {
-      mbar_expect_tx(bar_w, 163840u);
-      for (int i = 0; i < 5; ++i) bulk_g2s(W + i * 32768, reinterpret_cast<const uint8_t*>(Wimg) + i * 32768, 32768u, bar_w);
+      mbar_expect_tx(bar_w, 32768u);
+      bulk_g2s(W, Wimg, 32768u, bar_w);
     }
     __syncwarp();
     mbar_wait(bar_w, 0);
@@ -104,18 +127,22 @@ __global__ void __launch_bounds__(K4_THREADS, 1) trimul_proj_tc_kernel(
       TR(8);
 #pragma unroll 1
       for (uint32_t u = 0; u < 5; ++u, ++U) {
-        const uint32_t slot = U & 3u, d = tm + slot * 128u;
-        mbar_wait(slot_free + slot, ((U >> 2) & 1u) ^ 1u);
+        const uint32_t slot = U & 1u, d = tm + 256u + slot * 128u;
+        mbar_wait(slot_free + slot, ((U >> 1) & 1u) ^ 1u);
         tc_fence_after();
         TR(10 + u);
         if (elect_one()) {
           if (dbg & 8) {
           } else if (u < 4) {
-            const uint32_t wpart = wb + (u >> 1) * 65536u, xr = xb + (u & 1u) * 8192u;
-            k4_mma_T64(d, wpart, xr);
-            k4_mma_T64(d + 64, wpart + 16384u, xr);
+            const uint32_t wt = tm + (u >> 1) * 128u, xr = xb + (u & 1u) * 8192u;
+#pragma unroll
+            for (uint32_t ks = 0; ks < 8; ++ks) {
+              const uint64_t bd = umma_desc(xr + (ks >> 2) * 16384u + (ks & 3u) * 32u);
+              umma_ts(d, wt + ks * 8u, bd, umma_idesc(128, 64), ks);
+              umma_ts(d + 64u, wt + 64u + ks * 8u, bd, umma_idesc(128, 64), ks);
+            }
           } else {
-            umma_tile(d, xb, wb + 131072u, 128, 2, false);
+            umma_tile(d, xb, wb, 128, 2, false);
           }
           umma_commit(slot_full + slot);
           if (u == 4) umma_commit(empty_x + buf);
@@ -211,18 +238,18 @@ __global__ void __launch_bounds__(K4_THREADS, 1) trimul_proj_tc_kernel(
       const float rm0 = rowm[(it % 3) * 2], rm1 = rowm[(it % 3) * 2 + 1];
 #pragma unroll
       for (uint32_t u = 0; u < 4; ++u, ++U) {
-        const uint32_t slot = U & 3u, hh = u & 1u, orow = 2 * T.t2 + hh;
+        const uint32_t slot = U & 1u, hh = u & 1u, orow = 2 * T.t2 + hh;
         const float2 bp = (u < 2) ? b_ap : b_bp, bg = (u < 2) ? b_ag : b_bg;
         uint8_t* dst = ((u < 2) ? dst_a : dst_b) + hh * 128;
         const bool row_in = orow < (uint32_t)N, row_on = (hh ? rm1 : rm0) != 0.f;
-        mbar_wait(slot_full + slot, (U >> 2) & 1u);
+        mbar_wait(slot_full + slot, (U >> 1) & 1u);
         tc_fence_after();
         if (warp == 0) TR(20 + u * 2);
 #pragma unroll
         for (int hf = 0; hf < 2; ++hf) {
           uint32_t vp[16], vg[16];
-          tmem_ld16(t_lane + slot * 128u + c2 * 32u + hf * 16u, vp);
-          tmem_ld16(t_lane + slot * 128u + 64u + c2 * 32u + hf * 16u, vg);
+          tmem_ld16(t_lane + 256u + slot * 128u + c2 * 32u + hf * 16u, vp);
+          tmem_ld16(t_lane + 256u + slot * 128u + 64u + c2 * 32u + hf * 16u, vg);
           tmem_ld_wait();
           if (hf == 1) {
             tc_fence_before();
@@ -249,19 +276,19 @@ __global__ void __launch_bounds__(K4_THREADS, 1) trimul_proj_tc_kernel(
         if (warp == 0) TR(21 + u * 2);
       }
       {   // unit g: this thread = pixel m, channels [64 c2, 64 c2 + 64)
-        const uint32_t slot = U & 3u;
+        const uint32_t slot = U & 1u;
         const uint32_t m = q * 32 + lane;
         const uint32_t row = 2 * T.t2 + (m >> 6), col = 64 * T.jb + (m & 63);
         const bool valid = row < (uint32_t)N && col < (uint32_t)N;
         const size_t px = (size_t)T.b * N * N + (incoming ? (size_t)col * N + row : (size_t)row * N + col);
         uint4* dst = reinterpret_cast<uint4*>(g_out + px * 128 + c2 * 64);
-        mbar_wait(slot_full + slot, (U >> 2) & 1u);
+        mbar_wait(slot_full + slot, (U >> 1) & 1u);
         tc_fence_after();
         if (warp == 0) TR(28);
 #pragma unroll
         for (int hf = 0; hf < 2; ++hf) {
           uint32_t v[32];
-          tmem_ld32(t_lane + slot * 128u + c2 * 64u + hf * 32u, v);
+          tmem_ld32(t_lane + 256u + slot * 128u + c2 * 64u + hf * 32u, v);
           tmem_ld_wait();
           if (hf == 1) {
             tc_fence_before();
@@ -314,11 +341,13 @@ int tc_proj_init(gb_ctx* c) {
 //   W' = W * gamma / 2 ;  bias' = (b + W beta) / 2       order: a_p | a_g | b_p | b_g | g
 int tc_pack_trimul_proj(gb_ctx* c, TriMulW& w, const std::vector<float>* Wm[5], const std::vector<float>* bm[5],
                         const std::vector<float>& ln_g, const std::vector<float>& ln_b) {
+  // [g: K-major operand image 32 KB][a_p | a_g | b_p | b_g: row-major bf16 [128][128], loaded into tensor memory]
   std::vector<uint16_t> img(5 * 128 * 128);
   auto wv = [&](int t, int r, int k) { return 0.5f * (*Wm[t])[(size_t)r * 128 + k] * ln_g[k]; };
-  pack_image(img.data(), 256, 128, [&](int r, int k) { return r < 128 ? wv(0, r, k) : wv(1, r - 128, k); });
-  pack_image(img.data() + 32768, 256, 128, [&](int r, int k) { return r < 128 ? wv(2, r, k) : wv(3, r - 128, k); });
-  pack_image(img.data() + 65536, 128, 128, [&](int r, int k) { return wv(4, r, k); });
+  pack_image(img.data(), 128, 128, [&](int r, int k) { return wv(4, r, k); });
+  for (int t = 0; t < 4; ++t)
+    for (int r = 0; r < 128; ++r)
+      for (int k = 0; k < 128; ++k) img[16384 + ((size_t)t * 128 + r) * 128 + k] = f2bf(wv(t, r, k));
   w.tc_Wproj = upload_bytes(c, img.data(), img.size() * 2);
   std::vector<float> bias(5 * 128);
   for (int t = 0; t < 5; ++t)

@@ -40,6 +40,8 @@ def main():
         torch.cuda.synchronize()
         print('%-18s %8.1f us' % (name, 1e3 * min(e[i].elapsed_time(e[i + 1]) for i in range(reps))), flush=True)
 
+    for st, nm in ((1, 'K4 proj'), (2, 'K5 contract'), (3, 'K6 out')):
+        timed(nm, lambda st=st: L.check(lib.gb_k_trimul_stage(ctx, 0, 1, st, p.data_ptr(), None), ctx, 'k'))
     timed('trimul_out', lambda: L.check(lib.gb_k_trimul(ctx, 0, 1, p.data_ptr(), None), ctx, 'k'))
     timed('trimul_in', lambda: L.check(lib.gb_k_trimul(ctx, 0, 0, p.data_ptr(), None), ctx, 'k'))
     timed('pair_transition', lambda: L.check(lib.gb_k_pair_transition(ctx, 0, p.data_ptr(), None), ctx, 'k'))
