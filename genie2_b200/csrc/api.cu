@@ -193,7 +193,7 @@ static int pack_transition(gb_ctx* c, Getter& G, const std::string& pre, Transit
       }
   w.W1T = upload(c, W1T); w.b1 = upload(c, b1); w.W2T = upload(c, W2T); w.b2 = upload(c, b2);
   w.ln_g = upload(c, lg); w.ln_b = upload(c, lb);
-  return tc_pack_transition(c, w, w1, w2);
+  return tc_pack_transition(c, w, w1, b1, w2, lg, lb);
 }
 
 static int pack_triatt(gb_ctx* c, Getter& G, const std::string& pre, TriAttW& w) {

@@ -24,7 +24,8 @@ struct TriMulW {
 };
 struct TransitionW {
   float *ln_g, *ln_b, *W1T, *b1, *W2T, *b2;
-  void *tc_W1, *tc_W2;
+  void *tc_W1, *tc_W2;   // bf16 chunk images; W1 carries the LayerNorm gamma
+  float* tc_b1;          // b1 + W1 beta
 };
 struct TriAttW {
   float *ln_g, *ln_b, *Wbias /*[H][128]*/, *Wqkvg /*[4*H*C][128]: q|k|v|g*/, *bg, *Wo /*[128][H*C]*/, *bo, *bqkvg /*[4*H*C]: 0|0|0|bg*/;

@@ -17,7 +17,9 @@ int tc_proj_init(gb_ctx* c);
 int tc_pack_trimul_proj(gb_ctx* c, TriMulW& w, const std::vector<float>* Wm[5], const std::vector<float>* bm[5],
                         const std::vector<float>& ln_g, const std::vector<float>& ln_b);
 int tc_launch_trimul_proj(gb_ctx* c, const TriMulW& w, bool outgoing, const float* p, cudaStream_t st);
-int tc_pack_transition(gb_ctx* c, TransitionW& w, const std::vector<float>& w1, const std::vector<float>& w2);
+int tc_transition_init(gb_ctx* c);
+int tc_pack_transition(gb_ctx* c, TransitionW& w, const std::vector<float>& w1, const std::vector<float>& b1,
+                       const std::vector<float>& w2, const std::vector<float>& ln_g, const std::vector<float>& ln_b);
 // workspace the tensor-core path needs for a (B,N) batch, carved by gb_set_features
 size_t tc_workspace_bytes(const gb_ctx* c, int B, int N);
 int tc_bind_workspace(gb_ctx* c, void* base, size_t bytes, int B, int N);

@@ -102,164 +102,7 @@ __device__ __forceinline__ void tmem_to_stage(uint8_t* S, uint32_t taddr, uint32
   }
 }
 
-// ---------------------------------------------------------------------------------------------
-// K7 pair_transition_tc:  p = (p + (W2 relu(W1 LN(p) + b1) + b2) * mask) * mask
-//   W1img [nchunk][2 kb][128 hidden rows][64]   W2img [nchunk][2 kb][128 out rows][64 hidden]
-// 256 threads, 2 CTAs / SM (97 KB shared, 256 TMEM columns each) so that one CTA's LayerNorm /
-// epilogue overlaps the other's MMAs.  Shared: A 32K | H 32K | W 32K | barriers.
-// ---------------------------------------------------------------------------------------------
-#define K7_SMEM (3 * 32768 + 1024 + 64 + 512)   // barriers (4 x 8 B) + TMEM slot live in the 64 B after the tiles
-
-__global__ void __launch_bounds__(256, 2) pair_transition_tc_kernel(
-    float* __restrict__ p, uint32_t M, int N, const int* __restrict__ rmask, const float* __restrict__ ln_g,
-    const float* __restrict__ ln_b, const bf16* __restrict__ W1img, const float* __restrict__ b1,
-    const bf16* __restrict__ W2img, const float* __restrict__ b2, int nchunk) {
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* sm = smem_base_1024(smem_raw);
-  uint8_t* A = sm;
-  uint8_t* H = sm + 32768;
-  uint8_t* W = sm + 65536;
-  uint64_t* bar_w = reinterpret_cast<uint64_t*>(sm + 98304);
-  uint64_t* bar_mma = bar_w + 1;
-  uint32_t* tslot = reinterpret_cast<uint32_t*>(bar_w + 2);
-  float* rowmask = reinterpret_cast<float*>(sm + 98304 + 64);
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const uint32_t row0 = blockIdx.x * 128u;
-
-  // The raw fp32 tile (128 rows x 512 B, contiguous in p) is fetched by the async proxy into the
-  // H | W buffers (rows 0..63 -> H, 64..127 -> W), so 64 KB per CTA are in flight from the first
-  // instruction.  The W half is normalised first; then the first weight image streams into W
-  // while the H half is normalised.
-  uint64_t* bar_raw = bar_w + 3;
-  const uint32_t nrows = min(128u, M - row0);
-  if (tid == 0) {
-    mbar_init(bar_w, 1);
-    mbar_init(bar_mma, 1);
-    mbar_init(bar_raw, 1);
-    fence_mbar_init();
-    mbar_expect_tx(bar_raw, nrows * 512u);
-    bulk_g2s(H, p + (size_t)row0 * 128, min(nrows, 64u) * 512u, bar_raw);
-    if (nrows > 64) bulk_g2s(W, p + (size_t)(row0 + 64) * 128, (nrows - 64) * 512u, bar_raw);
-  }
-  if (warp == 1) tmem_alloc(tslot, 256);
-  if (tid < 128) {
-    const uint32_t row = row0 + tid;
-    float mk = 0.f;
-    if (row < M) {
-      const uint32_t NN = (uint32_t)N * N, b = row / NN, rem = row - b * NN, i = rem / N, j = rem - i * N;
-      mk = (float)(rmask[b * N + i] * rmask[b * N + j]);
-    }
-    rowmask[tid] = mk;
-  }
-  __syncthreads();                       // barrier init visible
-  mbar_wait(bar_raw, 0);
-  ln_rows8_to_image(A, 64 + warp * 8, [&](uint32_t m) -> const float* { return (m < nrows) ? reinterpret_cast<const float*>(W + (m - 64) * 512u) : nullptr; },
-                    ln_g, ln_b);
-  fence_proxy_async();                   // generic reads of W ordered before the async-proxy overwrite below
-  __syncthreads();                       // every warp is done reading the raw rows in W
-  if (tid == 0) {
-    fence_proxy_async();                 // order the generic reads of W before the async overwrite
-    mbar_expect_tx(bar_w, 32768);
-    bulk_g2s(W, W1img, 32768, bar_w);
-  }
-  ln_rows8_to_image(A, warp * 8, [&](uint32_t m) -> const float* { return (m < nrows) ? reinterpret_cast<const float*>(H + m * 512u) : nullptr; },
-                    ln_g, ln_b);
-  fence_proxy_async();
-  tc_fence_before();
-  __syncthreads();
-  tc_fence_after();
-  const uint32_t tmem = *tslot;
-  const uint32_t q = warp & 3, h = warp >> 2, m = q * 32 + lane;
-  const uint32_t t_lane = tmem + ((q * 32u) << 16);
-  uint32_t wph = 0, mph = 0;
-
-  for (int c = 0; c < nchunk; ++c) {
-    if (tid == 0) {                         // hidden chunk c = A . W1[c]^T -> TMEM cols [0,128)
-      mbar_wait(bar_w, wph);
-      tc_fence_after();
-      umma_tile(tmem, smem_u32(A), smem_u32(W), 128, 2, false);
-      umma_commit(bar_mma);
-    }
-    wph ^= 1;
-    __syncwarp();
-    mbar_wait(bar_mma, mph);
-    mph ^= 1;
-    tc_fence_after();
-    if (tid == 0) {                         // W is free again: fetch W2[c] behind the epilogue
-      mbar_expect_tx(bar_w, 32768);
-      bulk_g2s(W, W2img + (size_t)c * 16384, 32768, bar_w);
-    }
-    __syncwarp();
-    // relu(hidden + b1) -> bf16 H image; this warp: rows 32q.., hidden columns [64h, 64h+64) = k-block h
-#pragma unroll
-    for (int cc = 0; cc < 2; ++cc) {
-      uint32_t v[32];
-      tmem_ld32(t_lane + h * 64 + cc * 32, v);
-      tmem_ld_wait();
-      const float* bb = b1 + c * 128 + h * 64 + cc * 32;
-#pragma unroll
-      for (int ch = 0; ch < 4; ++ch) {
-        uint4 o;
-        o.x = pack_bf16(fmaxf(__uint_as_float(v[8 * ch + 0]) + bb[8 * ch + 0], 0.f), fmaxf(__uint_as_float(v[8 * ch + 1]) + bb[8 * ch + 1], 0.f));
-        o.y = pack_bf16(fmaxf(__uint_as_float(v[8 * ch + 2]) + bb[8 * ch + 2], 0.f), fmaxf(__uint_as_float(v[8 * ch + 3]) + bb[8 * ch + 3], 0.f));
-        o.z = pack_bf16(fmaxf(__uint_as_float(v[8 * ch + 4]) + bb[8 * ch + 4], 0.f), fmaxf(__uint_as_float(v[8 * ch + 5]) + bb[8 * ch + 5], 0.f));
-        o.w = pack_bf16(fmaxf(__uint_as_float(v[8 * ch + 6]) + bb[8 * ch + 6], 0.f), fmaxf(__uint_as_float(v[8 * ch + 7]) + bb[8 * ch + 7], 0.f));
-        const uint32_t chunk = cc * 4 + ch;
-        *reinterpret_cast<uint4*>(H + h * 16384u + m * 128u + ((chunk ^ (m & 7u)) << 4)) = o;
-      }
-    }
-    fence_proxy_async();
-    tc_fence_before();
-    __syncthreads();
-    if (tid == 0) {                         // out += H . W2[c]^T -> TMEM cols [128,256)
-      mbar_wait(bar_w, wph);
-      tc_fence_after();
-      umma_tile(tmem + 128, smem_u32(H), smem_u32(W), 128, 2, c > 0);
-      umma_commit(bar_mma);
-    }
-    wph ^= 1;
-    __syncwarp();
-    mbar_wait(bar_mma, mph);
-    mph ^= 1;
-    tc_fence_after();
-    if (tid == 0 && c + 1 < nchunk) {
-      mbar_expect_tx(bar_w, 32768);
-      bulk_g2s(W, W1img + (size_t)(c + 1) * 16384, 32768, bar_w);
-    }
-    __syncwarp();
-  }
-  // epilogue: out (+ b2) -> fp32 staging over A|H (both dead), then coalesced residual update of p
-  uint8_t* S = sm;
-  tmem_to_stage(S, t_lane + 128 + h * 64, m, h * 64, b2);
-  tmem_to_stage(S, t_lane + 128 + h * 64 + 32, m, h * 64 + 32, b2);
-  tc_fence_before();
-  __syncthreads();
-  for (int r0 = warp * 16; r0 < warp * 16 + 16; r0 += 4) {     // 4 rows (2 KB of p) in flight per warp
-    float4 pv[4];
-    bool ok[4];
-#pragma unroll
-    for (int u = 0; u < 4; ++u) {
-      const uint32_t r = r0 + u, row = row0 + r;
-      ok[u] = row < M;
-      if (ok[u]) pv[u] = ld4(p + (size_t)row * 128 + ((lane ^ (r & 31)) << 2));
-    }
-#pragma unroll
-    for (int u = 0; u < 4; ++u) {
-      const uint32_t r = r0 + u;
-      if (!ok[u]) continue;
-      const float4 v = *reinterpret_cast<const float4*>(S + r * 512u + (lane << 4));
-      const float mk = rowmask[r];
-      float4 o;
-      o.x = (pv[u].x + v.x * mk) * mk;
-      o.y = (pv[u].y + v.y * mk) * mk;
-      o.z = (pv[u].z + v.z * mk) * mk;
-      o.w = (pv[u].w + v.w * mk) * mk;
-      st4(p + (size_t)(row0 + r) * 128 + ((lane ^ (r & 31)) << 2), o);
-    }
-  }
-  if (warp == 1) tmem_dealloc(tmem, 256);
-}
-
+// K7 (pair transition) lives in tc_transition.cu.
 // ---------------------------------------------------------------------------------------------
 // Pixel tiles of the triangle kernels: a CTA owns 128 pixels = 2 consecutive rows x 64 consecutive
 // columns of one sample's N x N pair map; tile-local pixel m = 64 * ii + jj.
@@ -518,12 +361,12 @@ __global__ void __launch_bounds__(256, 3) trimul_out_tc_kernel(
 // ---------------------------------------------------------------------------------------------
 int tc_init(gb_ctx* c) {
   cudaError_t e;
-  if ((e = cudaFuncSetAttribute(pair_transition_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, K7_SMEM)) != cudaSuccess ||
-      (e = cudaFuncSetAttribute(trimul_contract_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, K5_SMEM)) != cudaSuccess ||
+  if ((e = cudaFuncSetAttribute(trimul_contract_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, K5_SMEM)) != cudaSuccess ||
       (e = cudaFuncSetAttribute(trimul_out_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, K6_SMEM)) != cudaSuccess)
     return gb_fail(c, GB_ERR_CUDA, "tc_init: cudaFuncSetAttribute failed: %s", cudaGetErrorString(e));
   c->tc_state = new TcState();
   int rc = tc_proj_init(c);
+  if (rc == GB_OK) rc = tc_transition_init(c);
   return rc != GB_OK ? rc : tc_struct_init(c);
 }
 
@@ -563,19 +406,6 @@ int tc_pack_trimul(gb_ctx* c, TriMulW& w, const std::vector<float>& ap, const st
   }
   w.tc_uv = (float*)upload_bytes(c, uv.data(), uv.size() * 4);
   if (!w.tc_Wz || !w.tc_uv) return gb_fail(c, GB_ERR_CUDA, "tc_pack_trimul: device allocation failed");
-  return GB_OK;
-}
-
-int tc_pack_transition(gb_ctx* c, TransitionW& w, const std::vector<float>& w1, const std::vector<float>& w2) {
-  const int nh = c->d.pair_transition_n, HID = 128 * nh;
-  std::vector<uint16_t> i1((size_t)nh * 128 * 128), i2((size_t)nh * 128 * 128);
-  for (int t = 0; t < nh; ++t) {
-    pack_image(i1.data() + (size_t)t * 16384, 128, 128, [&](int r, int k) { return w1[(size_t)(t * 128 + r) * 128 + k]; });
-    pack_image(i2.data() + (size_t)t * 16384, 128, 128, [&](int r, int k) { return w2[(size_t)r * HID + t * 128 + k]; });
-  }
-  w.tc_W1 = upload_bytes(c, i1.data(), i1.size() * 2);
-  w.tc_W2 = upload_bytes(c, i2.data(), i2.size() * 2);
-  if (!w.tc_W1 || !w.tc_W2) return gb_fail(c, GB_ERR_CUDA, "tc_pack_transition: device allocation failed");
   return GB_OK;
 }
 
@@ -628,17 +458,6 @@ int tc_trimul_stage(gb_ctx* c, const TriMulW& w, bool outgoing, int stage, float
 }
 
 int tc_trimul(gb_ctx* c, const TriMulW& w, bool outgoing, float* p, cudaStream_t st) { return tc_trimul_stage(c, w, outgoing, 0, p, st); }
-
-int tc_pair_transition(gb_ctx* c, const TransitionW& w, float* p, cudaStream_t st) {
-  if (c->precision != GB_PREC_BF16) return gb_fail(c, GB_ERR_UNSUPPORTED, "tensor-core path: tf32 kernels are not built in this revision (use bf16 or fp32)");
-  const size_t M = (size_t)c->B * c->N * c->N;
-  if (M >= (1ull << 31)) return gb_fail(c, GB_ERR_UNSUPPORTED, "pair map too large");
-  pair_transition_tc_kernel<<<(unsigned)((M + 127) / 128), 256, K7_SMEM, st>>>(p, (uint32_t)M, c->N, c->mask, w.ln_g, w.ln_b,
-                                                                              (const bf16*)w.tc_W1, w.b1, (const bf16*)w.tc_W2, w.b2,
-                                                                              c->d.pair_transition_n);
-  GB_LAUNCH_CHECK(c, "pair_transition_tc");
-  return GB_OK;
-}
 
 extern "C" int gb_dbg_tc_copy(gb_ctx* c, int which, void* dst, int64_t bytes) {
   if (!c || !c->tc_state || !c->features_set) return GB_ERR_INVALID;
