@@ -78,7 +78,7 @@ __global__ void single_combine_kernel(float* __restrict__ s, const float* __rest
 #define PE_NBIN_MAX 40
 
 template <int NBIN>
-__device__ __forceinline__ void soft_bins(float d, float dmin, float dstep, float* out /*smem*/, float scale) {
+__device__ __forceinline__ void soft_bins(float d, float dmin, float dstep, float* out /*smem, stride PE_TJ*/, float scale) {
   constexpr int nbin = NBIN;
   // softmax_k( -4 |d - (dmin + k dstep)| ), pair_feature_net.py:246-263
   float mx = -1e30f;
@@ -86,11 +86,11 @@ __device__ __forceinline__ void soft_bins(float d, float dmin, float dstep, floa
   float sum = 0.f;
   for (int k = 0; k < nbin; ++k) {
     const float e = expf(-4.f * fabsf(d - (dmin + (float)k * dstep)) - mx);
-    out[k] = e;
+    out[k * PE_TJ] = e;
     sum += e;
   }
   const float inv = scale / sum;
-  for (int k = 0; k < nbin; ++k) out[k] *= inv;
+  for (int k = 0; k < nbin; ++k) out[k * PE_TJ] *= inv;
 }
 
 template <int NBIN>
@@ -103,8 +103,9 @@ __global__ void __launch_bounds__(128) pair_embed_kernel(
     const float* __restrict__ quat_follow, int N, int relpos_k, float dmin, float dstep,
     int has_motif) {
   constexpr int nbin = NBIN;
-  __shared__ float feat[PE_TJ][PE_NBIN_MAX + 9];   // bins | quat(4) | fst | relidx | samechain | pm
-  __shared__ float mfeat[PE_TJ][PE_NBIN_MAX + 1];      // motif bins (already masked)
+  // feature-major tiles: the per-channel dot products read four keys per 16-byte broadcast load
+  __shared__ __align__(16) float feat[NBIN + 8][PE_TJ];   // bins | quat(4) | fst | relidx | samechain | pm
+  __shared__ __align__(16) float mfeat[NBIN][PE_TJ];      // motif bins (already masked)
   __shared__ float Ri[9], xi[3], mi3[3];
   const int b = blockIdx.y, i = blockIdx.x, c = threadIdx.x;
   const size_t row_i = (size_t)b * N + i;
@@ -123,13 +124,13 @@ __global__ void __launch_bounds__(128) pair_embed_kernel(
   __syncthreads();
 
   for (int j0 = 0; j0 < N; j0 += PE_TJ) {
-    if (c < PE_TJ && j0 + c < N) {
+    if (j0 + c < N) {
       const int j = j0 + c;
       const size_t row_j = (size_t)b * N + j;
       const float pm = (float)(mi * mask[row_j]);
       const float dx = xi[0] - trans[row_j * 3 + 0], dy = xi[1] - trans[row_j * 3 + 1], dz = xi[2] - trans[row_j * 3 + 2];
       const float d = sqrtf(1e-10f + dx * dx + dy * dy + dz * dz);
-      soft_bins<NBIN>(d, dmin, dstep, feat[c], pm);
+      soft_bins<NBIN>(d, dmin, dstep, &feat[0][c], pm);
       float Rj[9], R[9], q[4];
 #pragma unroll
       for (int e = 0; e < 9; ++e) Rj[e] = rots[row_j * 9 + e];
@@ -140,43 +141,57 @@ __global__ void __launch_bounds__(128) pair_embed_kernel(
         if (q[0] * qf[0] + q[1] * qf[1] + q[2] * qf[2] + q[3] * qf[3] < 0.f) { q[0] = -q[0]; q[1] = -q[1]; q[2] = -q[2]; q[3] = -q[3]; }
       }
 #pragma unroll
-      for (int e = 0; e < 4; ++e) feat[c][nbin + e] = q[e] * pm;
+      for (int e = 0; e < 4; ++e) feat[nbin + e][c] = q[e] * pm;
       const int fs = fst[row_i * N + j];
-      feat[c][nbin + 4] = (float)fs;
+      feat[nbin + 4][c] = (float)fs;
       const int same = (chain_index[row_j] == ci);
       int dr = ri - residue_index[row_j] + relpos_k;
       dr = dr < 0 ? 0 : (dr > 2 * relpos_k ? 2 * relpos_k : dr);
-      feat[c][nbin + 5] = __int_as_float(same ? dr : 2 * relpos_k + 1);
-      feat[c][nbin + 6] = (float)same;
-      feat[c][nbin + 7] = pm;
+      feat[nbin + 5][c] = __int_as_float(same ? dr : 2 * relpos_k + 1);
+      feat[nbin + 6][c] = (float)same;
+      feat[nbin + 7][c] = pm;
       if (has_motif) {
         if (fs) {
           const float ex = mi3[0] - motif_pos[row_j * 3 + 0], ey = mi3[1] - motif_pos[row_j * 3 + 1], ez = mi3[2] - motif_pos[row_j * 3 + 2];
           const float dm = sqrtf(1e-10f + ex * ex + ey * ey + ez * ez);
-          soft_bins<NBIN>(dm, dmin, dstep, mfeat[c], (float)(fsi * (int)fsm[row_j]));
+          soft_bins<NBIN>(dm, dmin, dstep, &mfeat[0][c], (float)(fsi * (int)fsm[row_j]));
         }
       }
+    } else {
+#pragma unroll
+      for (int k = 0; k < nbin + 8; ++k) feat[k][c] = 0.f;   // keys past the end: relidx 0, fst 0, never stored
     }
     __syncthreads();
     const int jn = min(PE_TJ, N - j0);
-    for (int jj = 0; jj < jn; ++jj) {
-      const size_t row_j = (size_t)b * N + j0 + jj;
-      const float* f = feat[jj];
-      float acc = pi_c + PiPj[row_j * 256 + 128 + c];
-      acc += WrelT[__float_as_int(f[nbin + 5]) * 128 + c];
-      acc = fmaf(f[nbin + 6], w_same, acc);
-      float t = 0.f;
+    for (int jj = 0; jj < jn; jj += 4) {
+      float t[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-      for (int k = 0; k < nbin + 4; ++k) t = fmaf(wt[k], f[k], t);
-      acc += t;
-      const float fs = f[nbin + 4];
-      acc = fmaf(fs, wt_fst, acc);
-      if (has_motif && fs != 0.f) {
-        float m = 0.f;
-        for (int k = 0; k < nbin; ++k) m = fmaf(WmT[k * 128 + c], mfeat[jj][k], m);
-        acc += m + wm_fst;
+      for (int k = 0; k < nbin + 4; ++k) {
+        const float4 f = *reinterpret_cast<const float4*>(&feat[k][jj]);
+        t[0] = fmaf(wt[k], f.x, t[0]); t[1] = fmaf(wt[k], f.y, t[1]); t[2] = fmaf(wt[k], f.z, t[2]); t[3] = fmaf(wt[k], f.w, t[3]);
       }
-      p[(row_i * N + j0 + jj) * 128 + c] = acc * f[nbin + 7];
+      const float4 fs4 = *reinterpret_cast<const float4*>(&feat[nbin + 4][jj]);
+      const float4 rel4 = *reinterpret_cast<const float4*>(&feat[nbin + 5][jj]);
+      const float4 same4 = *reinterpret_cast<const float4*>(&feat[nbin + 6][jj]);
+      const float4 pm4 = *reinterpret_cast<const float4*>(&feat[nbin + 7][jj]);
+      const float fsv[4] = {fs4.x, fs4.y, fs4.z, fs4.w}, relv[4] = {rel4.x, rel4.y, rel4.z, rel4.w};
+      const float samev[4] = {same4.x, same4.y, same4.z, same4.w}, pmv[4] = {pm4.x, pm4.y, pm4.z, pm4.w};
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        if (jj + u >= jn) break;
+        const size_t row_j = (size_t)b * N + j0 + jj + u;
+        float acc = pi_c + PiPj[row_j * 256 + 128 + c];
+        acc += WrelT[__float_as_int(relv[u]) * 128 + c];
+        acc = fmaf(samev[u], w_same, acc);
+        acc += t[u];
+        acc = fmaf(fsv[u], wt_fst, acc);
+        if (has_motif && fsv[u] != 0.f) {
+          float m = 0.f;
+          for (int k = 0; k < nbin; ++k) m = fmaf(WmT[k * 128 + c], mfeat[k][jj + u], m);
+          acc += m + wm_fst;
+        }
+        p[(row_i * N + j0 + jj + u) * 128 + c] = acc * pmv[u];
+      }
     }
     __syncthreads();
   }

@@ -1,10 +1,11 @@
 // tcgen05 / TMEM implementation of the pair stack (GB_PREC_BF16): bf16 operands, fp32
 // accumulation in tensor memory, fp32 LayerNorm statistics, fp32 residual stream p.
-//   K4 trimul_proj_tc      LN_in -> [a_p|a_g], [b_p|b_g], g GEMMs -> gated/masked a, b (bf16 tile
-//                          images, the operand format of K5) and the output gate g (bf16)
+//   K4 trimul_proj_tc      (tc_proj.cu) LN_in -> gated / masked a, b (bf16 tile images, the operand
+//                          format of K5) and the output gate g (bf16)
 //   K5 trimul_contract_tc  per (sample, channel): X = A . B^T, operands streamed with cp.async.bulk
 //   K6 trimul_out_tc       LN_out over channels -> linear_z -> * g -> p +=
-//   K7 pair_transition_tc  LN -> 128->512 -> ReLU -> 512->128, hidden never leaves the SM
+//   K7 pair_transition_tc  (tc_transition.cu) LN -> 128->512 -> ReLU -> 512->128, hidden never leaves the SM
+// This file: shared helpers, K5, K6, workspace and dispatch.
 // Reference: modules/triangular_multiplicative_update.py:57-110, modules/pair_transition.py:48-87.
 #include <string.h>
 

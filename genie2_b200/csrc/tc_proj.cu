@@ -7,21 +7,21 @@
 //   warps 8..15  producers: 64 KB of p rows in flight per SM in registers, LayerNorm statistics with
 //                 8 lanes per row, normalised rows (gamma / beta are folded into the weights on the
 //                 host) written as the bf16 K-major operand image X[buf] (two buffers)
-//   warp 16      one thread: all five weight images stay in shared memory for the whole kernel
-//                 (160 KB, one bulk load per CTA); issues tcgen05.mma for the five "units" of a tile
-//                 into a ring of four 128-column TMEM slots
+//   warp 16      MMA issue (converged warp, elected lane, descriptors in uniform registers).  The a / b
+//                 weights are the A operand and live in TENSOR MEMORY for the whole kernel (columns
+//                 0..255, loaded once per CTA): TS-mode tcgen05.mma reads only the 64 pixel rows of X
+//                 from shared memory per instruction (measured 46 cycles per 128x64x16 MMA against 72 in
+//                 SS mode, scripts/micro/mma_rate.cu).  Five "units" per tile go through a ring of two
+//                 128-column accumulator slots (columns 256..511):
 //                   a0 a1 b0 b1 : D[channel][64 pixels of tile row 0/1], proj in columns 0..63, gate 64..127
-//                   g           : D[pixel][channel]
-//   warps 0..7   epilogue: drain a slot, release it at once (the MMA warp runs up to three units
-//                 ahead), gate, mask, and store: a thread owns one channel and 32 pixels = 64
-//                 contiguous bytes of that channel's operand image row
-// Weights are scaled by 1/2 on the host so that sigmoid(y) = (tanh(y/2) + 1)/2 costs one MUFU and
-// one FMA:  a = u * t + u  with u = (W_ap z + b_ap)/2,  t = tanh((W_ag z + b_ag)/2).
-// Output formats (unchanged): a / b [B][128 ch][Np/64 kb][Np rows][64] tile images (incoming
-// update: transposed pixels, see tc_pair.cu), g [B*N*N][128] bf16.
-#include <stdio.h>
-#include <stdlib.h>
-
+//                   g           : D[pixel][channel], SS mode, W_g image in shared memory
+//   warps 0..7   epilogue: drain a slot, release it at once, gate, mask, store: a thread owns one channel
+//                 and 32 pixels = 64 contiguous bytes of that channel's operand image row, written as two
+//                 32-byte (full sector) stores
+// Weights are scaled by 1/2 on the host so that sigmoid(y) = (tanh(y/2) + 1)/2 costs one MUFU and one
+// packed FMA:  a = u * t + u  with u = (W_ap z + b_ap)/2,  t = tanh((W_ag z + b_ag)/2).
+// Output formats: a / b [B][128 ch][Np/64 kb][Np rows][64] tile images (incoming update: transposed
+// pixels, see tc_pair.cu), g [B*N*N][128] bf16.
 #include <vector>
 
 #include "common.cuh"
@@ -55,8 +55,7 @@ __device__ __forceinline__ void k4_mma_T64(uint32_t tmem_d, uint32_t w_rows, uin
 
 __global__ void __launch_bounds__(K4_THREADS, 1) trimul_proj_tc_kernel(
     const float* __restrict__ p, int N, int Np, int ntiles, const int* __restrict__ rmask, const bf16* __restrict__ Wimg,
-    const float* __restrict__ bias, bf16* __restrict__ a_out, bf16* __restrict__ b_out, bf16* __restrict__ g_out, int incoming, int dbg, long long* __restrict__ trace) {
-#define TR(idx) do { if (trace && blockIdx.x == 0 && lane == 0 && it < 8) trace[(it) * 64 + (idx)] = clock64(); } while (0)
+    const float* __restrict__ bias, bf16* __restrict__ a_out, bf16* __restrict__ b_out, bf16* __restrict__ g_out, int incoming) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* sm = smem_base_1024(smem_raw);
   uint8_t* W = sm;                       // g weight image 32K (a / b weights live in tensor memory)
@@ -124,16 +123,13 @@ __global__ void __launch_bounds__(K4_THREADS, 1) trimul_proj_tc_kernel(
       const uint32_t buf = it & 1, xb = smem_u32(X) + buf * 32768u;
       mbar_wait(full_x + buf, (it >> 1) & 1);
       tc_fence_after();
-      TR(8);
 #pragma unroll 1
       for (uint32_t u = 0; u < 5; ++u, ++U) {
         const uint32_t slot = U & 1u, d = tm + 256u + slot * 128u;
         mbar_wait(slot_free + slot, ((U >> 1) & 1u) ^ 1u);
         tc_fence_after();
-        TR(10 + u);
         if (elect_one()) {
-          if (dbg & 8) {
-          } else if (u < 4) {
+          if (u < 4) {
             const uint32_t wt = tm + (u >> 1) * 128u, xr = xb + (u & 1u) * 8192u;
 #pragma unroll
             for (uint32_t ks = 0; ks < 8; ++ks) {
@@ -163,26 +159,23 @@ __global__ void __launch_bounds__(K4_THREADS, 1) trimul_proj_tc_kernel(
       for (int gi = 0; gi < 4; ++gi) {
         const uint32_t m = 16 * pw + gi + 4 * rsub;
         const uint32_t row = 2 * T.t2 + (m >> 6), col = 64 * T.jb + (m & 63);
-        const bool ok = row < (uint32_t)N && col < (uint32_t)N && !(dbg & 2);
+        const bool ok = row < (uint32_t)N && col < (uint32_t)N;
         const float* src = p + (sample + (incoming ? (size_t)col * N + row : (size_t)row * N + col)) * 128 + l8 * 4;
 #pragma unroll
         for (int k = 0; k < 4; ++k) v[gi][k] = ok ? ld4(src + k * 32) : make_float4(0.f, 0.f, 0.f, 0.f);
       }
-      if (pw == 0) TR(0);
       float mk = 0.f;
       if (ptid < 66) {          // 64 column masks, then the 2 row masks
         const uint32_t r = ptid < 64 ? 64 * T.jb + ptid : 2 * T.t2 + (ptid - 64);
         if (r < (uint32_t)N) mk = (float)rmask[T.b * N + r];
       }
       mbar_wait(empty_x + buf, ((it >> 1) & 1) ^ 1);
-      if (pw == 0) TR(1);
       if (ptid < 64) {
         cmask[(it % 3) * 64 + ptid] = mk;
         const unsigned on = __ballot_sync(0xffffffffu, mk != 0.f);
         if (lane == 0) cfull[(it % 3) * 2 + pw] = on == 0xffffffffu ? 1.f : 0.f;
       } else if (ptid < 66) rowm[(it % 3) * 2 + (ptid - 64)] = mk;
       uint8_t* Xb = X + buf * 32768u;
-      if (!(dbg & 4))
 #pragma unroll
       for (int gi = 0; gi < 4; ++gi) {
         const uint32_t m = 16 * pw + gi + 4 * rsub;
@@ -216,7 +209,6 @@ __global__ void __launch_bounds__(K4_THREADS, 1) trimul_proj_tc_kernel(
       fence_proxy_async();
       __syncwarp();
       if (lane == 0) mbar_arrive(full_x + buf);
-      if (pw == 0) TR(2);
     }
   } else {
     // ------------------------------------------------------------------ epilogue
@@ -244,7 +236,6 @@ __global__ void __launch_bounds__(K4_THREADS, 1) trimul_proj_tc_kernel(
         const bool row_in = orow < (uint32_t)N, row_on = (hh ? rm1 : rm0) != 0.f;
         mbar_wait(slot_full + slot, (U >> 1) & 1u);
         tc_fence_after();
-        if (warp == 0) TR(20 + u * 2);
 #pragma unroll
         for (int hf = 0; hf < 2; ++hf) {
           uint32_t vp[16], vg[16];
@@ -273,7 +264,6 @@ __global__ void __launch_bounds__(K4_THREADS, 1) trimul_proj_tc_kernel(
           const uint4 w0 = make_uint4(w[0], w[1], w[2], w[3]), w1 = make_uint4(w[4], w[5], w[6], w[7]);
           st_global_32B(dst + ((((uint32_t)(c2 * 4 + hf * 2)) ^ (orow & 6u)) << 4), swap ? w1 : w0, swap ? w0 : w1);
         }
-        if (warp == 0) TR(21 + u * 2);
       }
       {   // unit g: this thread = pixel m, channels [64 c2, 64 c2 + 64)
         const uint32_t slot = U & 1u;
@@ -284,7 +274,6 @@ __global__ void __launch_bounds__(K4_THREADS, 1) trimul_proj_tc_kernel(
         uint4* dst = reinterpret_cast<uint4*>(g_out + px * 128 + c2 * 64);
         mbar_wait(slot_full + slot, (U >> 1) & 1u);
         tc_fence_after();
-        if (warp == 0) TR(28);
 #pragma unroll
         for (int hf = 0; hf < 2; ++hf) {
           uint32_t v[32];
@@ -312,7 +301,6 @@ __global__ void __launch_bounds__(K4_THREADS, 1) trimul_proj_tc_kernel(
             st_global_32B(dst + hf * 4 + k8 * 2, o[0], o[1]);
           }
         }
-        if (warp == 0) TR(29);
         ++U;
       }
     }
@@ -361,29 +349,13 @@ int tc_pack_trimul_proj(gb_ctx* c, TriMulW& w, const std::vector<float>* Wm[5], 
   return GB_OK;
 }
 
-static long long* g_trace = nullptr;
 int tc_launch_trimul_proj(gb_ctx* c, const TriMulW& w, bool outgoing, const float* p, cudaStream_t st) {
   TcState* s = static_cast<TcState*>(c->tc_state);
   const int B = c->B, N = c->N, Np = s->Np;
   const int tiles = B * ((N + 1) / 2) * (Np / 64);
   const int grid = tiles < s->num_sms ? tiles : s->num_sms;
-  if (getenv("GB_K4_TRACE") && !g_trace) { cudaMalloc(&g_trace, 4096); cudaMemset(g_trace, 0, 4096); }
   trimul_proj_tc_kernel<<<grid, K4_THREADS, K4_SMEM, st>>>(p, N, Np, tiles, c->mask, (const bf16*)w.tc_Wproj, w.tc_bproj, s->a, s->b,
-                                                           s->g, outgoing ? 0 : 1, getenv("GB_K4_DBG") ? atoi(getenv("GB_K4_DBG")) : 0, g_trace);
+                                                           s->g, outgoing ? 0 : 1);
   GB_LAUNCH_CHECK(c, "trimul_proj_tc");
-  if (g_trace) {
-    static int shots = 0;
-    cudaDeviceSynchronize();
-    long long h[512];
-    cudaMemcpy(h, g_trace, sizeof(h), cudaMemcpyDeviceToHost);
-    if (++shots == 3) {
-      const long long t0 = h[0];
-      for (int it = 0; it < 8; ++it) {
-        printf("tile %d:", it);
-        for (int k : {0, 1, 2, 8, 10, 11, 12, 13, 14, 20, 21, 22, 23, 24, 25, 26, 27, 28, 29}) printf(" [%d]%lld", k, h[it * 64 + k] - t0);
-        printf("\n");
-      }
-    }
-  }
   return GB_OK;
 }

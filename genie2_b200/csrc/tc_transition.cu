@@ -12,9 +12,6 @@
 // while the epilogue warps turn D1 into H.  LayerNorm's gamma / beta are folded into W1 / b1 on the host.
 //   warps 0..7   E1 / E2        warps 8..15  LayerNorm producers (registers -> bf16 operand image ring)
 //   warp 16      MMA issue      warp 17      weight-block loader (cp.async.bulk ring of three 32 KB slots)
-#include <stdio.h>
-#include <stdlib.h>
-
 #include <vector>
 
 #include "common.cuh"
@@ -42,8 +39,7 @@ __device__ __forceinline__ uint32_t relu_pack_bf16(float lo, float hi) {
 
 __global__ void __launch_bounds__(K7_THREADS, 1) pair_transition_tc_kernel(
     float* __restrict__ p, uint32_t M, int N, uint32_t npairs, const int* __restrict__ rmask, const bf16* __restrict__ W1img,
-    const float* __restrict__ b1, const bf16* __restrict__ W2img, const float* __restrict__ b2, uint32_t C, long long* __restrict__ trace, int dbg) {
-#define TR7(itv, idx) do { if (trace && blockIdx.x == 0 && lane == 0 && (itv) < 4) trace[(itv) * 64 + (idx)] = clock64(); } while (0)
+    const float* __restrict__ b1, const bf16* __restrict__ W2img, const float* __restrict__ b2, uint32_t C) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* sm = smem_base_1024(smem_raw);
   uint8_t* XR = sm;                      // 3 x 32 KB operand images of LayerNorm'ed pixel tiles
@@ -106,7 +102,6 @@ __global__ void __launch_bounds__(K7_THREADS, 1) pair_transition_tc_kernel(
         if (t == 0) mbar_wait(w_full + ws, (J / 3u) & 1u);
         mbar_wait(d1_free, (n1 & 1u) ^ 1u);
         tc_fence_after();
-        TR7(it, c * 2 + t);
         if (elect_one()) {
           umma_tile(tm + T_D1, xr + xs * 32768u, wr + ws * 32768u, 128, 2, false);
           umma_commit(d1_full);
@@ -122,7 +117,6 @@ __global__ void __launch_bounds__(K7_THREADS, 1) pair_transition_tc_kernel(
         if (c == 0) mbar_wait(d2_free + t, (it & 1u) ^ 1u);
         mbar_wait(h_full + t, k & 1u);
         tc_fence_after();
-        TR7(it, 8 + c * 2 + t);
         if (elect_one()) {
           const uint32_t wb = wr + ws * 32768u;
 #pragma unroll
@@ -215,12 +209,11 @@ __global__ void __launch_bounds__(K7_THREADS, 1) pair_transition_tc_kernel(
       const uint32_t r4 = lane >> 3, ch = lane & 7;      // phase 2: row within a group of four, 16-byte chunk
       mbar_wait(d2_full + t, it & 1u);
       tc_fence_after();
-      if (pw == 0) TR7(it, 32 + t);
       auto load_res = [&](uint32_t slab, float4 (&pv)[4]) {
 #pragma unroll
         for (int g = 0; g < 4; ++g) {
           const uint32_t row = row0 + pw * 16 + g * 4 + r4;
-          pv[g] = (row < M && !(dbg & 1)) ? ld4(p + (size_t)row * 128 + slab * 32 + ch * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
+          pv[g] = row < M ? ld4(p + (size_t)row * 128 + slab * 32 + ch * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
         }
       };
       float4 pva[4], pvb[4];
@@ -250,7 +243,7 @@ __global__ void __launch_bounds__(K7_THREADS, 1) pair_transition_tc_kernel(
           o.y = (pv[g].y + (a.y + bv.y) * mk) * mk;
           o.z = (pv[g].z + (a.z + bv.z) * mk) * mk;
           o.w = (pv[g].w + (a.w + bv.w) * mk) * mk;
-          if (row < M && !(dbg & 2)) st4(p + (size_t)row * 128 + slab * 32 + ch * 4, o);
+          if (row < M) st4(p + (size_t)row * 128 + slab * 32 + ch * 4, o);
         }
         asm volatile("bar.sync 1, 256;" ::: "memory");
       };
@@ -258,7 +251,6 @@ __global__ void __launch_bounds__(K7_THREADS, 1) pair_transition_tc_kernel(
       do_slab(1, pvb, pva);
       do_slab(2, pva, pvb);
       do_slab(3, pvb, pva);
-      if (pw == 0) TR7(it, 34 + t);
     };
     if (iters > 0) { produce(0); produce(1); }
     for (uint32_t it = 0; it < iters; ++it) {
@@ -281,7 +273,6 @@ __global__ void __launch_bounds__(K7_THREADS, 1) pair_transition_tc_kernel(
           const uint32_t k = it * C + c;
           mbar_wait(d1_full, n1 & 1u);
           tc_fence_after();
-          if (warp == 0) TR7(it, 16 + c * 2 + t);
 #pragma unroll
           for (int hf = 0; hf < 2; ++hf) {
             uint32_t v[32], hp[16];
@@ -308,7 +299,6 @@ __global__ void __launch_bounds__(K7_THREADS, 1) pair_transition_tc_kernel(
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive(h_full + t);
-          if (warp == 0) TR7(it, 24 + c * 2 + t);
         }
     }
   }
@@ -351,9 +341,7 @@ int tc_pack_transition(gb_ctx* c, TransitionW& w, const std::vector<float>& w1, 
   return GB_OK;
 }
 
-static long long* g_trace7 = nullptr;
 int tc_pair_transition(gb_ctx* c, const TransitionW& w, float* p, cudaStream_t st) {
-  if (getenv("GB_K7_TRACE") && !g_trace7) { cudaMalloc(&g_trace7, 2048); cudaMemset(g_trace7, 0, 2048); }
   if (c->precision != GB_PREC_BF16) return gb_fail(c, GB_ERR_UNSUPPORTED, "tensor-core path: tf32 kernels are not built in this revision (use bf16 or fp32)");
   const size_t M = (size_t)c->B * c->N * c->N;
   if (M >= (1ull << 31)) return gb_fail(c, GB_ERR_UNSUPPORTED, "pair map too large");
@@ -361,33 +349,7 @@ int tc_pair_transition(gb_ctx* c, const TransitionW& w, float* p, cudaStream_t s
   const uint32_t npairs = (uint32_t)((M + 255) / 256);
   const uint32_t grid = npairs < (uint32_t)s->num_sms ? npairs : (uint32_t)s->num_sms;
   pair_transition_tc_kernel<<<grid, K7_THREADS, K7_SMEM, st>>>(p, (uint32_t)M, c->N, npairs, c->mask, (const bf16*)w.tc_W1, w.tc_b1,
-                                                               (const bf16*)w.tc_W2, w.b2, (uint32_t)c->d.pair_transition_n, g_trace7, getenv("GB_K7_DBG") ? atoi(getenv("GB_K7_DBG")) : 0);
+                                                               (const bf16*)w.tc_W2, w.b2, (uint32_t)c->d.pair_transition_n);
   GB_LAUNCH_CHECK(c, "pair_transition_tc");
-  if (g_trace7) {
-    static int shots = 0;
-    cudaDeviceSynchronize();
-    long long h[256];
-    cudaMemcpy(h, g_trace7, sizeof(h), cudaMemcpyDeviceToHost);
-    if (++shots == 3) {
-      long long t0 = h[40];
-      for (int it = 0; it < 4; ++it) {
-        printf("it %d G1:", it);
-        for (int k = 0; k < 8; ++k) printf(" %lld", h[it * 64 + k] - t0);
-        printf(" | G2:");
-        for (int k = 8; k < 16; ++k) printf(" %lld", h[it * 64 + k] - t0);
-        printf("\n     E1s:");
-        for (int k = 16; k < 24; ++k) printf(" %lld", h[it * 64 + k] - t0);
-        printf(" | E1e:");
-        for (int k = 24; k < 32; ++k) printf(" %lld", h[it * 64 + k] - t0);
-        printf("\n     E2:");
-        for (int k = 32; k < 36; ++k) printf(" %lld", h[it * 64 + k] - t0);
-        printf(" | prod:");
-        for (int k = 40; k < 46; ++k) printf(" %lld", h[it * 64 + k] - t0);
-        printf("\n     E2A detail:");
-        for (int k = 46; k < 56; ++k) printf(" %lld", h[it * 64 + k] - t0);
-        printf("\n");
-      }
-    }
-  }
   return GB_OK;
 }
