@@ -340,7 +340,7 @@ extern "C" int gb_load_weights(gb_ctx* c, const gb_tensor* tensors, int n) {
       w.W3.push_back(upload(c, a3)); w.b3.push_back(upload(c, c3));
       w123.push_back(&a1); w123.push_back(&a2); w123.push_back(&a3);
     }
-    int rc = tc_pack_struct_layer(c, l, concat({&wq, &wkv, &wqp, &wkvp}), wo, w123);
+    int rc = tc_pack_struct_layer(c, l, concat({&wq, &wkv, &wqp, &wkvp}), concat({&bq, &bkv, &bqp, &bkvp}), wo, w123);
     if (rc != GB_OK) return rc;
   }
   {

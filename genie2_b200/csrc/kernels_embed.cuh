@@ -94,7 +94,7 @@ __device__ __forceinline__ void soft_bins(float d, float dmin, float dstep, floa
 }
 
 template <int NBIN>
-__global__ void __launch_bounds__(128) pair_embed_kernel(
+__global__ void __launch_bounds__(128, 5) pair_embed_kernel(
     float* __restrict__ p, const float* __restrict__ PiPj /*[B*N, 256]: Pi | Pj*/, const float* __restrict__ rots,
     const float* __restrict__ trans, const int* __restrict__ residue_index, const int* __restrict__ chain_index,
     const int* __restrict__ mask, const uint8_t* __restrict__ fsm, const uint8_t* __restrict__ fst,
@@ -164,6 +164,16 @@ __global__ void __launch_bounds__(128) pair_embed_kernel(
     __syncthreads();
     const int jn = min(PE_TJ, N - j0);
     for (int jj = 0; jj < jn; jj += 4) {
+      // global operands of the four pixels first: their latency hides behind the 41 x 4 FMAs below
+      const float4 rel4 = *reinterpret_cast<const float4*>(&feat[nbin + 5][jj]);
+      const float relv[4] = {rel4.x, rel4.y, rel4.z, rel4.w};
+      float pj[4], wr[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int jc = min(j0 + jj + u, N - 1);
+        pj[u] = PiPj[((size_t)b * N + jc) * 256 + 128 + c];
+        wr[u] = WrelT[__float_as_int(relv[u]) * 128 + c];
+      }
       float t[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
       for (int k = 0; k < nbin + 4; ++k) {
@@ -171,17 +181,15 @@ __global__ void __launch_bounds__(128) pair_embed_kernel(
         t[0] = fmaf(wt[k], f.x, t[0]); t[1] = fmaf(wt[k], f.y, t[1]); t[2] = fmaf(wt[k], f.z, t[2]); t[3] = fmaf(wt[k], f.w, t[3]);
       }
       const float4 fs4 = *reinterpret_cast<const float4*>(&feat[nbin + 4][jj]);
-      const float4 rel4 = *reinterpret_cast<const float4*>(&feat[nbin + 5][jj]);
       const float4 same4 = *reinterpret_cast<const float4*>(&feat[nbin + 6][jj]);
       const float4 pm4 = *reinterpret_cast<const float4*>(&feat[nbin + 7][jj]);
-      const float fsv[4] = {fs4.x, fs4.y, fs4.z, fs4.w}, relv[4] = {rel4.x, rel4.y, rel4.z, rel4.w};
+      const float fsv[4] = {fs4.x, fs4.y, fs4.z, fs4.w};
       const float samev[4] = {same4.x, same4.y, same4.z, same4.w}, pmv[4] = {pm4.x, pm4.y, pm4.z, pm4.w};
 #pragma unroll
       for (int u = 0; u < 4; ++u) {
         if (jj + u >= jn) break;
-        const size_t row_j = (size_t)b * N + j0 + jj + u;
-        float acc = pi_c + PiPj[row_j * 256 + 128 + c];
-        acc += WrelT[__float_as_int(relv[u]) * 128 + c];
+        float acc = pi_c + pj[u];
+        acc += wr[u];
         acc = fmaf(samev[u], w_same, acc);
         acc += t[u];
         acc = fmaf(fsv[u], wt_fst, acc);

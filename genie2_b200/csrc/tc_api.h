@@ -35,7 +35,7 @@ int tc_struct_init(gb_ctx* c);
 bool tc_struct_supported(const gb_ctx* c, int N);
 size_t tc_struct_workspace_bytes(const gb_ctx* c, int B, int N);
 int tc_struct_bind(gb_ctx* c, void* base, size_t bytes, int B, int N);
-int tc_pack_struct_layer(gb_ctx* c, int l, const std::vector<float>& wqkv, const std::vector<float>& wout,
+int tc_pack_struct_layer(gb_ctx* c, int l, const std::vector<float>& wqkv, const std::vector<float>& bqkv, const std::vector<float>& wout,
                          const std::vector<const std::vector<float>*>& w123);
 int tc_pack_ipa_bias(gb_ctx* c, const std::vector<const std::vector<float>*>& wb, const std::vector<const std::vector<float>*>& bb);
 // StructureNet.forward on c->s / c->p / c->rots_w / c->trans_w (bf16 mode); states_out may be NULL

@@ -7,7 +7,8 @@
 typedef __nv_bfloat16 bf16;
 
 struct TcStructW {                 // per structure layer, bf16 operand images [K/64][N][64]
-  bf16 *Wqkv = nullptr, *Wout = nullptr;
+  bf16 *Wqkv = nullptr, *Wout = nullptr;   // Wqkv rows (and bqkv) in the plane order of ipa_dims.h
+  float* bqkv = nullptr;
   std::vector<bf16*> W1, W2, W3;
 };
 

@@ -36,6 +36,8 @@ struct GemmImgArgs {
   float* C;           // fp32 out [R][ldc] or null
   bf16* O;            // bf16 image out [Nw/64][Rp][64] or null
   int Rp, Nw, nkb, R, ldc, ldr, relu;
+  int kvsplit;        // > 0: IPA projection scatter, value = N (keys per sample): columns < IPA_QW go to rows [R][IPA_QW],
+                      // the rest to key-major planes [B][IPA_NPLANE][N][4] behind them (see ipa_dims.h)
 };
 
 __global__ void __launch_bounds__(256, 1) gemm_img_tc_kernel(const GemmImgArgs g) {
@@ -70,20 +72,20 @@ __global__ void __launch_bounds__(256, 1) gemm_img_tc_kernel(const GemmImgArgs g
     }
     __syncwarp();
   } else if (warp == 1) {
-    if (lane == 0) {
-      const uint32_t idesc = umma_idesc(128, 64);
-      for (int kb = 0; kb < g.nkb; ++kb) {
-        const int s = kb % GI_STAGES;
-        mbar_wait(full + s, (kb / GI_STAGES) & 1);
-        tc_fence_after();
-        const uint32_t sa = smem_u32(sm + s * GI_STAGE_BYTES), sb = sa + 16384;
+    const uint32_t idesc = umma_idesc(128, 64), tm = warp_uniform(tmem);
+    for (int kb = 0; kb < g.nkb; ++kb) {
+      const int s = kb % GI_STAGES;
+      mbar_wait(full + s, (kb / GI_STAGES) & 1);
+      tc_fence_after();
+      const uint32_t sa = smem_u32(sm + s * GI_STAGE_BYTES), sb = sa + 16384;
+      if (elect_one()) {
 #pragma unroll
-        for (int k = 0; k < 4; ++k) umma(tmem, umma_desc(sa + k * 32), umma_desc(sb + k * 32), idesc, (kb | k) ? 1u : 0u);
+        for (int k = 0; k < 4; ++k) umma(tm, umma_desc(sa + k * 32), umma_desc(sb + k * 32), idesc, (kb | k) ? 1u : 0u);
         umma_commit(empty + s);
+        if (kb == g.nkb - 1) umma_commit(done);
       }
-      umma_commit(done);
+      __syncwarp();
     }
-    __syncwarp();
   }
   mbar_wait(done, 0);
   tc_fence_after();
@@ -105,7 +107,17 @@ __global__ void __launch_bounds__(256, 1) gemm_img_tc_kernel(const GemmImgArgs g
 #pragma unroll
       for (int e = 0; e < 8; ++e) { const float4 r = r4[e]; o[4 * e] += r.x; o[4 * e + 1] += r.y; o[4 * e + 2] += r.z; o[4 * e + 3] += r.w; }
     }
-    if (g.C) {
+    if (g.C && g.kvsplit) {
+      const uint32_t bb = m / (uint32_t)g.kvsplit, jj = m - bb * (uint32_t)g.kvsplit;
+      float* planes = g.C + (size_t)g.R * IPA_QW;
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        const uint32_t col = c0 + 4 * e;
+        float* dst = col < IPA_QW ? g.C + (size_t)m * IPA_QW + col
+                                  : planes + (((size_t)bb * IPA_NPLANE + ((col - IPA_QW) >> 2)) * g.kvsplit + jj) * 4;
+        *reinterpret_cast<float4*>(dst) = make_float4(o[4 * e], o[4 * e + 1], o[4 * e + 2], o[4 * e + 3]);
+      }
+    } else if (g.C) {
       float4* c4 = reinterpret_cast<float4*>(g.C + (size_t)m * g.ldc + c0);
 #pragma unroll
       for (int e = 0; e < 8; ++e) c4[e] = make_float4(o[4 * e], o[4 * e + 1], o[4 * e + 2], o[4 * e + 3]);
@@ -278,6 +290,48 @@ __global__ void __launch_bounds__(256, 2) ipa_prep_tc_kernel(const float* __rest
 }
 
 // ---------------------------------------------------------------------------------------------
+// ipa_points_planes_kernel: T.apply on the projected points (invariant_point_attention.py:149,162) in the
+// Q-row / key-plane layout of ipa_dims.h.  One thread per (row, head): 4 q points, 4 k points, 8 v points.
+// ---------------------------------------------------------------------------------------------
+__global__ void ipa_points_planes_kernel(float* __restrict__ qkv, const float* __restrict__ rots, const float* __restrict__ trans,
+                                         int R, int N) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= R * IPA_H) return;
+  const int row = idx / IPA_H, h = idx - row * IPA_H, b = row / N, j = row - b * N;
+  const float* Rm = rots + (size_t)row * 9;
+  const float* T = trans + (size_t)row * 3;
+  const float r0 = Rm[0], r1 = Rm[1], r2 = Rm[2], r3 = Rm[3], r4 = Rm[4], r5 = Rm[5], r6 = Rm[6], r7 = Rm[7], r8 = Rm[8];
+  const float t0 = T[0], t1 = T[1], t2 = T[2];
+  auto apply4 = [&](float4& x, float4& y, float4& z) {
+    const float4 a = x, bq = y, cz = z;
+    x = make_float4(r0 * a.x + r1 * bq.x + r2 * cz.x + t0, r0 * a.y + r1 * bq.y + r2 * cz.y + t0, r0 * a.z + r1 * bq.z + r2 * cz.z + t0,
+                    r0 * a.w + r1 * bq.w + r2 * cz.w + t0);
+    y = make_float4(r3 * a.x + r4 * bq.x + r5 * cz.x + t1, r3 * a.y + r4 * bq.y + r5 * cz.y + t1, r3 * a.z + r4 * bq.z + r5 * cz.z + t1,
+                    r3 * a.w + r4 * bq.w + r5 * cz.w + t1);
+    z = make_float4(r6 * a.x + r7 * bq.x + r8 * cz.x + t2, r6 * a.y + r7 * bq.y + r8 * cz.y + t2, r6 * a.z + r7 * bq.z + r8 * cz.z + t2,
+                    r6 * a.w + r7 * bq.w + r8 * cz.w + t2);
+  };
+  {   // q points: Q row, 192 + c*48 + h*4 + p
+    float4* q = reinterpret_cast<float4*>(qkv + (size_t)row * IPA_QW + 192 + h * 4);
+    float4 x = q[0], y = q[12], z = q[24];
+    apply4(x, y, z);
+    q[0] = x; q[12] = y; q[24] = z;
+  }
+  float4* pl = reinterpret_cast<float4*>(qkv + (size_t)R * IPA_QW) + ((size_t)b * IPA_NPLANE + h * IPA_PLANES_PER_HEAD) * N + j;
+  {   // k points: planes e = 4, 5, 6
+    float4 x = pl[(size_t)4 * N], y = pl[(size_t)5 * N], z = pl[(size_t)6 * N];
+    apply4(x, y, z);
+    pl[(size_t)4 * N] = x; pl[(size_t)5 * N] = y; pl[(size_t)6 * N] = z;
+  }
+#pragma unroll
+  for (int pg = 0; pg < 2; ++pg) {   // v points: x planes 11, 12; y 13, 14; z 15, 16
+    float4 x = pl[(size_t)(11 + pg) * N], y = pl[(size_t)(13 + pg) * N], z = pl[(size_t)(15 + pg) * N];
+    apply4(x, y, z);
+    pl[(size_t)(11 + pg) * N] = x; pl[(size_t)(13 + pg) * N] = y; pl[(size_t)(15 + pg) * N] = z;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
 // ipa_attention_tc_kernel (invariant_point_attention.py:181-259), Np <= 256.
 // One CTA = IA_G consecutive query rows i0.. of sample b (256 threads):
 //   1. logits: thread j owns key j; per head it loads k / k_pts of its key once (registers) and scores
@@ -290,11 +344,12 @@ __global__ void __launch_bounds__(256, 2) ipa_prep_tc_kernel(const float* __rest
 //   4. epilogue: inverse frame + norms for o_pt; everything is written as bf16 straight into the
 //      operand image of the output projection (cat_img, K = 2112: o | o_pt.x | .y | .z | |o_pt| | o_pair).
 // ---------------------------------------------------------------------------------------------
-#define IA_G 4
-#define IA_ZRING 4
-#define IA_OFF_AIMG 65536
+#define IA_G 8          // queries per CTA: every CTA streams the whole K / V of its sample, so the L2 traffic per query is 1/IA_G
+#define IA_ZRING 2
+#define IA_THREADS 512   // the CUDA-core phases run at ~0.2 IPC per warp (dependent FMA chains): occupancy, not bandwidth, bounds them
+#define IA_OFF_AIMG (IA_ZRING * 16384)
 #define IA_OFF_P (IA_OFF_AIMG + IA_G * 8192)
-#define IA_OFF_QS (IA_OFF_P + 12 * 256 * 16)
+#define IA_OFF_QS (IA_OFF_P + 12 * 256 * IA_G * 4)
 #define IA_OFF_RED (IA_OFF_QS + IA_G * 12 * 28 * 4)
 #define IA_OFF_FR (IA_OFF_RED + IA_G * 480 * 4)
 #define IA_OFF_BAR (IA_OFF_FR + IA_G * 12 * 4)
@@ -306,7 +361,7 @@ __device__ __forceinline__ void img_store(bf16* img, int Rp, uint32_t r, uint32_
   *reinterpret_cast<bf16*>(base + ((((k & 63) >> 3) ^ (r & 7u)) << 4) + ((k & 7) << 1)) = __float2bfloat16_rn(v);
 }
 
-__global__ void __launch_bounds__(256, 1) ipa_attention_tc_kernel(
+__global__ void __launch_bounds__(IA_THREADS, 1) ipa_attention_tc_kernel(
     const float* __restrict__ qkv, const float* __restrict__ pbias, const bf16* __restrict__ z_img,
     const float* __restrict__ rots, const float* __restrict__ trans, const float* __restrict__ hw,
     bf16* __restrict__ cat_img, int N, int Np, int Rp) {
@@ -341,20 +396,20 @@ __global__ void __launch_bounds__(256, 1) ipa_attention_tc_kernel(
       bulk_g2s(zring + it * 16384 + 8192, src + (size_t)Np * 128, 8192, full + it);
     }
   }
-  if (warp == 2) tmem_alloc(tslot, 64);
+  if (warp == 2) tmem_alloc(tslot, IA_G * 16);
   // q, q_pts of the IA_G queries; a_img cleared (rows 12..15 and padded keys must read as zero)
   const float sc_qk = sqrtf(1.f / (3.f * IPA_C));
-  for (int e = tid; e < IA_G * 12 * 28; e += 256) {
+  for (int e = tid; e < IA_G * 12 * 28; e += IA_THREADS) {
     const int g = e / 336, r = e - g * 336, h = r / 28, x = r - h * 28;
     float v = 0.f;
     if (g < ng) {
-      const float* row = qkv + (rowb + i0 + g) * IPA_QKV;
-      v = x < 16 ? row[h * 16 + x] * sc_qk : row[IPA_OFF_QP + ((x - 16) >> 2) * 48 + h * 4 + ((x - 16) & 3)];
+      const float* row = qkv + (rowb + i0 + g) * IPA_QW;
+      v = x < 16 ? row[h * 16 + x] * sc_qk : row[192 + ((x - 16) >> 2) * 48 + h * 4 + ((x - 16) & 3)];
     }
     qs[e] = v;
   }
-  for (int e = tid; e < IA_G * 8192 / 16; e += 256) reinterpret_cast<uint4*>(aimg)[e] = make_uint4(0, 0, 0, 0);
-  for (int e = tid; e < IA_G * 480; e += 256) oacc[e] = 0.f;
+  for (int e = tid; e < IA_G * 8192 / 16; e += IA_THREADS) reinterpret_cast<uint4*>(aimg)[e] = make_uint4(0, 0, 0, 0);
+  for (int e = tid; e < IA_G * 480; e += IA_THREADS) oacc[e] = 0.f;
   if (tid < IA_G * 12) {
     const int g = tid / 12, x = tid - g * 12;
     fr[tid] = g < ng ? (x < 9 ? rots[(rowb + i0 + g) * 9 + x] : trans[(rowb + i0 + g) * 3 + x - 9]) : 0.f;
@@ -366,19 +421,23 @@ __global__ void __launch_bounds__(256, 1) ipa_attention_tc_kernel(
 
   // ---- 1. logits
   {
-    const int j = tid;
+    const int j = tid & 255, hg = tid >> 8;      // two thread groups of 256 keys, six heads each
     const bool kv = j < N;
-    const float* krow = qkv + (rowb + (kv ? j : 0)) * IPA_QKV;
-    for (int h = 0; h < 12; ++h) {
-      float4 lg = make_float4(-3.0e38f, -3.0e38f, -3.0e38f, -3.0e38f);
+    const float4* kpl = reinterpret_cast<const float4*>(qkv + (size_t)gridDim.y * N * IPA_QW) + (size_t)b * IPA_NPLANE * N + (kv ? j : 0);
+#pragma unroll
+    for (int hh = 0; hh < 12 / (IA_THREADS / 256); ++hh) {       // unrolled: the K planes and pair-bias words of later heads are in flight early
+      const int h = hg * (12 / (IA_THREADS / 256)) + hh;
+      float out[IA_G];
+#pragma unroll
+      for (int g = 0; g < IA_G; ++g) out[g] = -3.0e38f;
       if (kv) {
         float k[28];
 #pragma unroll
-        for (int e = 0; e < 4; ++e) { const float4 t = ld4(krow + IPA_OFF_KV + h * 32 + e * 4); k[4 * e] = t.x; k[4 * e + 1] = t.y; k[4 * e + 2] = t.z; k[4 * e + 3] = t.w; }
-#pragma unroll
-        for (int c = 0; c < 3; ++c) { const float4 t = ld4(krow + IPA_OFF_KVP + c * 144 + h * 12); k[16 + 4 * c] = t.x; k[17 + 4 * c] = t.y; k[18 + 4 * c] = t.z; k[19 + 4 * c] = t.w; }
+        for (int e = 0; e < 7; ++e) {       // planes 0..3 = k, 4..6 = k_pts x / y / z: consecutive keys, consecutive 16-byte words
+          const float4 t = kpl[(size_t)(h * IPA_PLANES_PER_HEAD + e) * N];
+          k[4 * e] = t.x; k[4 * e + 1] = t.y; k[4 * e + 2] = t.z; k[4 * e + 3] = t.w;
+        }
         const float gam = -0.5f * hw[h];
-        float out[IA_G];
 #pragma unroll
         for (int g = 0; g < IA_G; ++g) {
           const float4* q4 = reinterpret_cast<const float4*>(qs + (g * 12 + h) * 28);
@@ -395,39 +454,56 @@ __global__ void __launch_bounds__(256, 1) ipa_attention_tc_kernel(
           if (g < ng) pb = pbias[((rowb + i0 + g) * 12 + h) * Np + j];
           out[g] = qk + pb + gam * d2;
         }
-        lg = make_float4(out[0], out[1], out[2], out[3]);
       }
-      if (j < Np) *reinterpret_cast<float4*>(P + ((size_t)h * Np + j) * IA_G) = lg;
+      if (j < Np) {
+#pragma unroll
+        for (int g4 = 0; g4 < IA_G / 4; ++g4)
+          *reinterpret_cast<float4*>(P + ((size_t)h * Np + j) * IA_G + 4 * g4) = make_float4(out[4 * g4], out[4 * g4 + 1], out[4 * g4 + 2], out[4 * g4 + 3]);
+      }
     }
   }
   __syncthreads();
   // ---- 2. softmax over j; warp w owns heads w, w+8
-  for (int h = warp; h < 12; h += 8) {
-    float4 mx = make_float4(-3.0e38f, -3.0e38f, -3.0e38f, -3.0e38f);
+  for (int h = warp; h < 12; h += IA_THREADS / 32) {
+    float mx[IA_G], sum[IA_G];
+#pragma unroll
+    for (int g = 0; g < IA_G; ++g) { mx[g] = -3.0e38f; sum[g] = 0.f; }
     for (int j = lane; j < Np; j += 32) {
-      const float4 t = *reinterpret_cast<const float4*>(P + ((size_t)h * Np + j) * IA_G);
-      mx.x = fmaxf(mx.x, t.x); mx.y = fmaxf(mx.y, t.y); mx.z = fmaxf(mx.z, t.z); mx.w = fmaxf(mx.w, t.w);
+      const float* pp = P + ((size_t)h * Np + j) * IA_G;
+#pragma unroll
+      for (int g4 = 0; g4 < IA_G / 4; ++g4) {
+        const float4 t = *reinterpret_cast<const float4*>(pp + 4 * g4);
+        mx[4 * g4] = fmaxf(mx[4 * g4], t.x); mx[4 * g4 + 1] = fmaxf(mx[4 * g4 + 1], t.y);
+        mx[4 * g4 + 2] = fmaxf(mx[4 * g4 + 2], t.z); mx[4 * g4 + 3] = fmaxf(mx[4 * g4 + 3], t.w);
+      }
     }
-    mx.x = warp_max(mx.x); mx.y = warp_max(mx.y); mx.z = warp_max(mx.z); mx.w = warp_max(mx.w);
-    float4 sum = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+    for (int g = 0; g < IA_G; ++g) mx[g] = warp_max(mx[g]);
     for (int j = lane; j < Np; j += 32) {
-      float4* pp = reinterpret_cast<float4*>(P + ((size_t)h * Np + j) * IA_G);
-      float4 t = *pp;
-      t.x = __expf(t.x - mx.x); t.y = __expf(t.y - mx.y); t.z = __expf(t.z - mx.z); t.w = __expf(t.w - mx.w);
-      sum.x += t.x; sum.y += t.y; sum.z += t.z; sum.w += t.w;
-      *pp = t;
+      float* pp = P + ((size_t)h * Np + j) * IA_G;
+#pragma unroll
+      for (int g4 = 0; g4 < IA_G / 4; ++g4) {
+        float4 t = *reinterpret_cast<float4*>(pp + 4 * g4);
+        t.x = __expf(t.x - mx[4 * g4]); t.y = __expf(t.y - mx[4 * g4 + 1]); t.z = __expf(t.z - mx[4 * g4 + 2]); t.w = __expf(t.w - mx[4 * g4 + 3]);
+        sum[4 * g4] += t.x; sum[4 * g4 + 1] += t.y; sum[4 * g4 + 2] += t.z; sum[4 * g4 + 3] += t.w;
+        *reinterpret_cast<float4*>(pp + 4 * g4) = t;
+      }
     }
-    const float ix = 1.f / warp_sum(sum.x), iy = 1.f / warp_sum(sum.y), iz = 1.f / warp_sum(sum.z), iw = 1.f / warp_sum(sum.w);
+#pragma unroll
+    for (int g = 0; g < IA_G; ++g) sum[g] = 1.f / warp_sum(sum[g]);
     for (int j = lane; j < Np; j += 32) {
-      float4* pp = reinterpret_cast<float4*>(P + ((size_t)h * Np + j) * IA_G);
-      float4 t = *pp;
-      t.x *= ix; t.y *= iy; t.z *= iz; t.w *= iw;
-      *pp = t;
+      float* pp = P + ((size_t)h * Np + j) * IA_G;
       const uint32_t off = (j >> 6) * 2048u + h * 128u + (((((uint32_t)j & 63) >> 3) ^ ((uint32_t)h & 7u)) << 4) + ((j & 7) << 1);
-      *reinterpret_cast<bf16*>(aimg + off) = __float2bfloat16_rn(t.x);
-      *reinterpret_cast<bf16*>(aimg + 8192 + off) = __float2bfloat16_rn(t.y);
-      *reinterpret_cast<bf16*>(aimg + 16384 + off) = __float2bfloat16_rn(t.z);
-      *reinterpret_cast<bf16*>(aimg + 24576 + off) = __float2bfloat16_rn(t.w);
+#pragma unroll
+      for (int g4 = 0; g4 < IA_G / 4; ++g4) {
+        float4 t = *reinterpret_cast<float4*>(pp + 4 * g4);
+        t.x *= sum[4 * g4]; t.y *= sum[4 * g4 + 1]; t.z *= sum[4 * g4 + 2]; t.w *= sum[4 * g4 + 3];
+        *reinterpret_cast<float4*>(pp + 4 * g4) = t;
+        *reinterpret_cast<bf16*>(aimg + (4 * g4) * 8192 + off) = __float2bfloat16_rn(t.x);
+        *reinterpret_cast<bf16*>(aimg + (4 * g4 + 1) * 8192 + off) = __float2bfloat16_rn(t.y);
+        *reinterpret_cast<bf16*>(aimg + (4 * g4 + 2) * 8192 + off) = __float2bfloat16_rn(t.z);
+        *reinterpret_cast<bf16*>(aimg + (4 * g4 + 3) * 8192 + off) = __float2bfloat16_rn(t.w);
+      }
     }
   }
   fence_proxy_async();
@@ -466,42 +542,56 @@ __global__ void __launch_bounds__(256, 1) ipa_attention_tc_kernel(
     }
     __syncwarp();
   } else {
-    // o[h][16] and o_pt[h][8][3] (global frame): per query 120 float4 groups (10 per head) x 8 key
-    // segments = 960 tasks over 192 threads; partial sums meet in shared memory.
-    const int seg = (N + 7) >> 3;
-    for (int t = tid - 64; t < 960; t += 192) {
-      const int js = t / 120, grp = t - js * 120, h = grp / 10, e4 = grp - h * 10;
-      const int off = e4 < 4 ? IPA_OFF_KV + h * 32 + 16 + e4 * 4
-                             : IPA_OFF_KVP + (((e4 - 4) * 4) >> 3) * 144 + h * 12 + 4 + (((e4 - 4) * 4) & 7);
-      const float* src = qkv + rowb * IPA_QKV + off;
+    // o[h][16] and o_pt[h][8][3] (global frame): 120 float4 groups (10 value planes per head).  One warp
+    // per group, lanes over keys (coalesced plane reads, conflict-free P reads), butterfly reduction.
+    const float4* vpl = reinterpret_cast<const float4*>(qkv + (size_t)gridDim.y * N * IPA_QW) + (size_t)b * IPA_NPLANE * N;
+    for (int t = warp - 2; t < 120; t += IA_THREADS / 32 - 2) {       // one value plane per pass, its 8 key loads in flight together
+      const int h = t / 10, ev = t - h * 10;
+      const float4* src = vpl + (size_t)(h * IPA_PLANES_PER_HEAD + 7 + ev) * N;
+      float4 vv[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int j = lane + 32 * u;
+        vv[u] = j < N ? src[j] : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
       float acc[IA_G][4];
 #pragma unroll
       for (int g = 0; g < IA_G; ++g) acc[g][0] = acc[g][1] = acc[g][2] = acc[g][3] = 0.f;
-      const int j1 = min(N, (js + 1) * seg);
-#pragma unroll 4
-      for (int j = js * seg; j < j1; ++j) {
-        const float4 v = ld4(src + (size_t)j * IPA_QKV);
-        const float4 a = *reinterpret_cast<const float4*>(P + ((size_t)h * Np + j) * IA_G);
-        const float av[4] = {a.x, a.y, a.z, a.w};
 #pragma unroll
-        for (int g = 0; g < IA_G; ++g) {
-          acc[g][0] = fmaf(av[g], v.x, acc[g][0]); acc[g][1] = fmaf(av[g], v.y, acc[g][1]);
-          acc[g][2] = fmaf(av[g], v.z, acc[g][2]); acc[g][3] = fmaf(av[g], v.w, acc[g][3]);
+      for (int u = 0; u < 8; ++u) {
+        const int j = lane + 32 * u;
+        if (j < N) {
+          const float* pp = P + ((size_t)h * Np + j) * IA_G;
+          const float4 v = vv[u];
+#pragma unroll
+          for (int g4 = 0; g4 < IA_G / 4; ++g4) {
+            const float4 a = *reinterpret_cast<const float4*>(pp + 4 * g4);
+            const float av[4] = {a.x, a.y, a.z, a.w};
+#pragma unroll
+            for (int gg = 0; gg < 4; ++gg) {
+              const int g = 4 * g4 + gg;
+              acc[g][0] = fmaf(av[gg], v.x, acc[g][0]); acc[g][1] = fmaf(av[gg], v.y, acc[g][1]);
+              acc[g][2] = fmaf(av[gg], v.z, acc[g][2]); acc[g][3] = fmaf(av[gg], v.w, acc[g][3]);
+            }
+          }
         }
       }
 #pragma unroll
       for (int g = 0; g < IA_G; ++g)
 #pragma unroll
-        for (int e = 0; e < 4; ++e) atomicAdd(oacc + g * 480 + h * 40 + e4 * 4 + e, acc[g][e]);
+        for (int e = 0; e < 4; ++e) {
+          const float r = warp_sum(acc[g][e]);
+          if (lane == 0) oacc[g * 480 + h * 40 + ev * 4 + e] = r;
+        }
     }
   }
   __syncthreads();
   // ---- 4. inverse frame + norm (invariant_point_attention.py:227-240)
-  for (int e = tid; e < ng * 192; e += 256) {
+  for (int e = tid; e < ng * 192; e += IA_THREADS) {
     const int g = e / 192, x = e - g * 192;
     img_store(cat_img, Rp, (uint32_t)(rowb + i0 + g), x, oacc[g * 480 + (x >> 4) * 40 + (x & 15)]);
   }
-  for (int e = tid; e < ng * 96; e += 256) {
+  for (int e = tid; e < ng * 96; e += IA_THREADS) {
     const int g = e / 96, pt = e - g * 96;
     const float* R = fr + g * 12;
     const float* op = oacc + g * 480 + (pt >> 3) * 40 + 16 + (pt & 7);
@@ -516,7 +606,7 @@ __global__ void __launch_bounds__(256, 1) ipa_attention_tc_kernel(
   // o_pair: TMEM lane = channel c, columns 16 g + h
   {
     const uint32_t q = warp & 3, c = q * 32 + lane;
-    for (int g = (warp >> 2); g < ng; g += 2) {
+    for (int g = (warp >> 2); g < ng; g += IA_THREADS / 128) {
       mbar_wait(done + g, 0);
       tc_fence_after();
       __syncwarp();
@@ -530,7 +620,7 @@ __global__ void __launch_bounds__(256, 1) ipa_attention_tc_kernel(
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 2) tmem_dealloc(tmem, 64);
+  if (warp == 2) tmem_dealloc(tmem, IA_G * 16);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -589,7 +679,7 @@ static bf16* pack_linear(gb_ctx* c, const std::vector<float>& w, int N, int K) {
   return (bf16*)upload_bytes(c, img.data(), img.size() * 2);
 }
 
-int tc_pack_struct_layer(gb_ctx* c, int l, const std::vector<float>& wqkv, const std::vector<float>& wout,
+int tc_pack_struct_layer(gb_ctx* c, int l, const std::vector<float>& wqkv, const std::vector<float>& bqkv, const std::vector<float>& wout,
                          const std::vector<const std::vector<float>*>& w123) {
   TcState* s = static_cast<TcState*>(c->tc_state);
   const int cs = c->d.c_s;
@@ -597,14 +687,22 @@ int tc_pack_struct_layer(gb_ctx* c, int l, const std::vector<float>& wqkv, const
   if ((int)s->st.size() <= l) s->st.resize(l + 1);
   TcStructW& w = s->st[l];
   w = TcStructW();
-  w.Wqkv = pack_linear(c, wqkv, IPA_QKV, cs);
+  {
+    // output columns reordered: q | q_pts | key-major planes (h, e) of 4 floats (ipa_dims.h)
+    std::vector<uint16_t> img((size_t)IPA_QKV * cs);
+    pack_image(img.data(), IPA_QKV, cs, [&](int r, int k) { return wqkv[(size_t)ipa_old_col(r) * cs + k]; });
+    w.Wqkv = (bf16*)upload_bytes(c, img.data(), img.size() * 2);
+    std::vector<float> bp(IPA_QKV);
+    for (int r = 0; r < IPA_QKV; ++r) bp[r] = bqkv[ipa_old_col(r)];
+    w.bqkv = (float*)upload_bytes(c, bp.data(), bp.size() * 4);
+  }
   w.Wout = pack_linear(c, wout, cs, IPA_CAT);
   for (size_t t = 0; t + 2 < w123.size(); t += 3) {
     w.W1.push_back(pack_linear(c, *w123[t], cs, cs));
     w.W2.push_back(pack_linear(c, *w123[t + 1], cs, cs));
     w.W3.push_back(pack_linear(c, *w123[t + 2], cs, cs));
   }
-  if (!w.Wqkv || !w.Wout) return gb_fail(c, GB_ERR_CUDA, "tc_pack_struct_layer: device allocation failed");
+  if (!w.Wqkv || !w.Wout || !w.bqkv) return gb_fail(c, GB_ERR_CUDA, "tc_pack_struct_layer: device allocation failed");
   return GB_OK;
 }
 
@@ -625,11 +723,11 @@ int tc_pack_ipa_bias(gb_ctx* c, const std::vector<const std::vector<float>*>& wb
 }
 
 static int gemm_img(gb_ctx* c, cudaStream_t st, const bf16* A, int K, const bf16* W, int Nw, const float* bias, const float* res,
-                    int ldr, float* C, int ldc, bf16* O, bool relu) {
+                    int ldr, float* C, int ldc, bf16* O, bool relu, int kvsplit = 0) {
   TcState* s = static_cast<TcState*>(c->tc_state);
   GemmImgArgs g;
   g.A = A; g.W = W; g.bias = bias; g.res = res; g.C = C; g.O = O;
-  g.Rp = s->Rp; g.Nw = Nw; g.nkb = K / 64; g.R = c->B * c->N; g.ldc = ldc; g.ldr = ldr; g.relu = relu ? 1 : 0;
+  g.Rp = s->Rp; g.Nw = Nw; g.nkb = K / 64; g.R = c->B * c->N; g.ldc = ldc; g.ldr = ldr; g.relu = relu ? 1 : 0; g.kvsplit = kvsplit;
   gemm_img_tc_kernel<<<dim3(Nw / 64, s->Rp / 128), 256, GI_SMEM, st>>>(g);
   GB_LAUNCH_CHECK(c, "gemm_img_tc");
   return GB_OK;
@@ -655,9 +753,10 @@ int tc_structure_net(gb_ctx* c, float* states_out, cudaStream_t st) {
     for (int l = 0; l < d.n_structure_layer; ++l) {
       const StructLayerW& w = c->st[l];
       const TcStructW& t = s->st[l];
-      if ((rc = gemm_img(c, st, s->s_img, cs, t.Wqkv, IPA_QKV, w.bqkv, nullptr, 0, c->qkv, IPA_QKV, nullptr, false))) return rc;
-      if ((rc = simt_points_to_global(c, st))) return rc;
-      ipa_attention_tc_kernel<<<dim3((N + IA_G - 1) / IA_G, B), 256, IA_SMEM, st>>>(
+      if ((rc = gemm_img(c, st, s->s_img, cs, t.Wqkv, IPA_QKV, t.bqkv, nullptr, 0, c->qkv, IPA_QKV, nullptr, false, N))) return rc;
+      ipa_points_planes_kernel<<<(R * IPA_H + 255) / 256, 256, 0, st>>>(c->qkv, c->rots_w, c->trans_w, R, N);
+      GB_LAUNCH_CHECK(c, "ipa_points_planes");
+      ipa_attention_tc_kernel<<<dim3((N + IA_G - 1) / IA_G, B), IA_THREADS, IA_SMEM, st>>>(
           c->qkv, s->pbias + (size_t)l * B * N * IPA_H * Np, s->z_img, c->rots_w, c->trans_w, w.hw, s->cat_img, N, Np, Rp);
       GB_LAUNCH_CHECK(c, "ipa_attention_tc");
       if ((rc = gemm_img(c, st, s->cat_img, IPA_CAT, t.Wout, cs, w.bout, c->s, cs, c->sA, cs, nullptr, false))) return rc;
