@@ -346,7 +346,7 @@ __global__ void ipa_points_planes_kernel(float* __restrict__ qkv, const float* _
 // ---------------------------------------------------------------------------------------------
 #define IA_G 8          // queries per CTA: every CTA streams the whole K / V of its sample, so the L2 traffic per query is 1/IA_G
 #define IA_ZRING 2
-#define IA_THREADS 512   // the CUDA-core phases run at ~0.2 IPC per warp (dependent FMA chains): occupancy, not bandwidth, bounds them
+#define IA_THREADS 768   // the CUDA-core phases run at ~0.2 IPC per warp (dependent FMA chains): occupancy, not bandwidth, bounds them
 #define IA_OFF_AIMG (IA_ZRING * 16384)
 #define IA_OFF_P (IA_OFF_AIMG + IA_G * 8192)
 #define IA_OFF_QS (IA_OFF_P + 12 * 256 * IA_G * 4)
