@@ -134,3 +134,26 @@ def test_forward_bf16_with_triangle_attention_fixture():
     o, _ = run_cuda_forward(model, t['rots'], t['trans'], t['timesteps'], feats, t['quat'])
     assert rel(o['p'], t['p']) < 2e-2
     assert rel(o['z'], t['z']) < TOL_Z_BF16
+
+
+def test_c5_length_1024_single_gpu():
+    """BASELINE configs[4] (L=1024, B=1) on one GPU: the 537 MB pair tensor and its workspace fit in
+    HBM; the bf16 pair stack must agree with the fp32 CUDA path on the same inputs (the CPU oracle
+    needs minutes at this size, so the full-size check is path-vs-path plus finiteness and masks)."""
+    cfg = O.OracleConfig()
+    sd = W.make_state_dict(cfg, 2, 'activated')
+    g = torch.Generator().manual_seed(4)
+    feats = O.make_features([[1024]])
+    trans = torch.randn(1, 1024, 3, generator=g) * 12
+    rots = O.compute_frenet_frames(trans, feats['chain_index'], feats['residue_mask'])
+    ts = torch.tensor([400], dtype=torch.int32)
+    model = make_denoiser(cfg, sd, precision='fp32')
+    model.return_intermediates = False
+    import genie2_b200
+    f = feats_to(feats, DEV)
+    t = genie2_b200.T(rots.to(DEV), trans.to(DEV))
+    z32 = model(t, ts.to(DEV), f)['z'].cpu()
+    model.set_precision('bf16')
+    z16 = model(t, ts.to(DEV), f)['z'].cpu()
+    assert bool(torch.isfinite(z32).all()) and bool(torch.isfinite(z16).all())
+    assert rel(z16, z32) < TOL_Z_BF16
