@@ -13,6 +13,7 @@
 #include "kernels_pair_simt.cuh"
 #include "kernels_structure.cuh"
 #include "kernels_triatt.cuh"
+#include "shard.h"
 #include "tc_api.h"
 
 static std::string g_create_err;
@@ -31,6 +32,7 @@ extern "C" int gb_version(void) { return GB_VERSION; }
 extern "C" const char* gb_last_error(const gb_ctx* ctx) { return ctx ? ctx->err.c_str() : g_create_err.c_str(); }
 extern "C" int64_t gb_launch_count(const gb_ctx* ctx) { return ctx ? ctx->launches : 0; }
 extern "C" int64_t gb_workspace_bytes(const gb_ctx* ctx) { return ctx ? (int64_t)ctx->ws_bytes : 0; }
+extern "C" int64_t gb_collective_count(const gb_ctx* ctx) { return ctx ? ctx->collectives : 0; }
 
 static const int kSmemPair = (PS_A_FLOATS + PS_W_FLOATS) * 4;
 static const int kSmemTrans = (PS_A_FLOATS + PS_W_FLOATS + PS_A_FLOATS) * 4;
@@ -86,6 +88,7 @@ static void free_features(gb_ctx* c) {
 extern "C" void gb_destroy(gb_ctx* c) {
   if (!c) return;
   cudaSetDevice(c->device);
+  shard_destroy(c);
   tc_destroy(c);
   free_features(c);
   if (c->tape_alloc) cudaFree(c->tape_alloc);
@@ -439,6 +442,9 @@ extern "C" int gb_set_features(gb_ctx* c, const gb_features* f) {
       !f->interface_mask || !f->aatype || !f->atom_positions)
     return gb_fail(c, GB_ERR_INVALID, "gb_set_features: NULL feature pointer");
   if ((size_t)f->N * 13 * 4 + 64 > 200 * 1024) return gb_fail(c, GB_ERR_UNSUPPORTED, "N = %d too large for the frame kernels", f->N);
+  if (c->shard_world > 1 && (f->B != 1 || f->N % (128 * c->shard_world) != 0))
+    return gb_fail(c, GB_ERR_UNSUPPORTED, "row sharding over %d GPUs needs B == 1 and N a multiple of %d (got B = %d, N = %d)",
+                   c->shard_world, 128 * c->shard_world, f->B, f->N);
   GB_CUDA(c, cudaSetDevice(c->device));
   const int B = f->B, N = f->N;
   if (!c->features_set || B != c->B || N != c->N) {
@@ -587,10 +593,15 @@ static int run_ipa(gb_ctx* c, const StructLayerW& w, const float* s, const float
   GB_LAUNCH_CHECK(c, "ipa_points_to_global");
   const size_t smem = ((size_t)IPA_H * N + 192 + 144 + 288) * sizeof(float);
   if (smem > 200 * 1024) return gb_fail(c, GB_ERR_UNSUPPORTED, "N = %d too large for ipa_attention", N);
-  ipa_attention_kernel<<<dim3(N, B), 256, smem, st>>>(c->qkv, p, rots, trans, c->mask, w.Wb, w.bb, w.hw, c->cat, N);
+  // row-sharded (B == 1): attention and output projection for this rank's query rows, then the [N, c_s] result is
+  // all-gathered; everything else in the structure net is O(N) and runs replicated
+  const int W = c->shard_world, rows = N / W, row0 = c->shard_rank * rows;
+  ipa_attention_kernel<<<dim3(rows, B), 256, smem, st>>>(c->qkv, p, rots, trans, c->mask, w.Wb, w.bb, w.hw, c->cat, N, row0);
   GB_LAUNCH_CHECK(c, "ipa_attention");
-  sgemm_nt(st, c->cat, IPA_CAT, w.Wout, IPA_CAT, w.bout, residual, cs, out, cs, R, cs, IPA_CAT, false);
+  sgemm_nt(st, c->cat + (size_t)row0 * IPA_CAT, IPA_CAT, w.Wout, IPA_CAT, w.bout, residual ? residual + (size_t)row0 * cs : nullptr, cs,
+           out + (size_t)row0 * cs, cs, W > 1 ? rows : R, cs, IPA_CAT, false);
   GB_LAUNCH_CHECK(c, "ipa_out");
+  if (W > 1) return shard_all_gather(c, out, (size_t)rows * cs * sizeof(float), st);
   return GB_OK;
 }
 
@@ -634,6 +645,8 @@ extern "C" int gb_denoise(gb_ctx* c, const float* rots, const float* trans, cons
   int rc = check_ready(c, "gb_denoise");
   if (rc) return rc;
   if (!rots || !trans || !timesteps || !z_out) return gb_fail(c, GB_ERR_INVALID, "gb_denoise: NULL pointer");
+  if (c->shard_world > 1 && c->precision != GB_PREC_BF16)
+    return gb_fail(c, GB_ERR_UNSUPPORTED, "row sharding is built for the tensor-core (bf16) pair stack only");
   cudaStream_t st = (cudaStream_t)stream;
   const gb_dims& d = c->d;
   const int B = c->B, N = c->N, R = B * N, cs = d.c_s;
@@ -648,10 +661,11 @@ extern "C" int gb_denoise(gb_ctx* c, const float* rots, const float* trans, cons
   // PairFeatureNet
   sgemm_nt(st, c->s, cs, c->W_pipj, cs, nullptr, nullptr, 0, c->pipj, 256, R, 256, cs, false);
   GB_LAUNCH_CHECK(c, "pair_pipj");
-  pair_embed_kernel<37><<<dim3(N, B), 128, 0, st>>>(c->p, c->pipj, c->rots_w, c->trans_w, c->residue_index, c->chain_index, c->mask,
+  const int W = c->shard_world, rows_l = N / W, row0 = c->shard_rank * rows_l;   // W == 1: all rows
+  pair_embed_kernel<37><<<dim3(rows_l, B), 128, 0, st>>>(c->p, c->pipj, c->rots_w, c->trans_w, c->residue_index, c->chain_index, c->mask,
                                                     c->fsm, c->fst, c->motif_pos, c->WrelT, c->WtT, c->WmT,
                                                     aux ? aux->quat_follow : nullptr, N, d.relpos_k, d.template_dist_min,
-                                                    d.template_dist_step, c->has_motif);
+                                                    d.template_dist_step, c->has_motif, row0);
   GB_LAUNCH_CHECK(c, "pair_embed");
   // PairTransformNet
   for (int l = 0; l < d.n_pair_transform_layer; ++l) {
@@ -660,16 +674,20 @@ extern "C" int gb_denoise(gb_ctx* c, const float* rots, const float* trans, cons
       if ((rc = run_trimul(c, c->pair[l].mul_in, false, c->p, st))) return rc;
     }
     if (d.include_tri_att) {
+      if (W > 1) return gb_fail(c, GB_ERR_UNSUPPORTED, "row sharding: triangle attention is not sharded in this revision");
       if ((rc = run_triatt(c, c->pair[l].att_start, true, c->p, st))) return rc;
       if ((rc = run_triatt(c, c->pair[l].att_end, false, c->p, st))) return rc;
     }
     if ((rc = run_transition(c, c->pair[l].tr, c->p, st))) return rc;
   }
-  if (aux && aux->p) GB_CUDA(c, cudaMemcpyAsync(aux->p, c->p, (size_t)R * N * 128 * 4, cudaMemcpyDeviceToDevice, st));
+  if (aux && aux->p) {
+    if (W > 1 && (rc = shard_all_gather(c, c->p, (size_t)rows_l * N * 128 * 4, st))) return rc;   // every rank returns the whole map
+    GB_CUDA(c, cudaMemcpyAsync(aux->p, c->p, (size_t)R * N * 128 * 4, cudaMemcpyDeviceToDevice, st));
+  }
   // StructureNet
   float* s = c->s;
   int state_idx = 1;
-  const bool tc_struct = c->precision == GB_PREC_BF16 && tc_struct_supported(c, N);
+  const bool tc_struct = c->precision == GB_PREC_BF16 && tc_struct_supported(c, N) && W == 1;
   if (tc_struct) {
     if ((rc = tc_structure_net(c, aux ? aux->states : nullptr, st))) return rc;
   } else

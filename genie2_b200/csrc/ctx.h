@@ -85,6 +85,10 @@ struct gb_ctx {
   int* t_dev = nullptr;                            // [B] timesteps
   void* tape_alloc = nullptr;
   size_t tape_bytes = 0;
+  // row sharding of one long sample over `shard_world` GPUs (shard.cu); 1 = off
+  int shard_world = 1, shard_rank = 0;
+  void* shard_comm = nullptr;   // ncclComm_t
+  int64_t collectives = 0;      // all-gathers enqueued since creation
   // tensor-core scratch (bf16/tf32 operand copies), owned by the tc module
   void* tc_state = nullptr;
 };

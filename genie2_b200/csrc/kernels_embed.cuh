@@ -101,13 +101,13 @@ __global__ void __launch_bounds__(128, 5) pair_embed_kernel(
     const float* __restrict__ motif_pos, const float* __restrict__ WrelT /*[2k+3][128]*/,
     const float* __restrict__ WtT /*[nbin+6][128]*/, const float* __restrict__ WmT /*[nbin+2][128]*/,
     const float* __restrict__ quat_follow, int N, int relpos_k, float dmin, float dstep,
-    int has_motif) {
+    int has_motif, int row0 /* first row of a row-sharded launch (grid.x = rows) */) {
   constexpr int nbin = NBIN;
   // feature-major tiles: the per-channel dot products read four keys per 16-byte broadcast load
   __shared__ __align__(16) float feat[NBIN + 8][PE_TJ];   // bins | quat(4) | fst | relidx | samechain | pm
   __shared__ __align__(16) float mfeat[NBIN][PE_TJ];      // motif bins (already masked)
   __shared__ float Ri[9], xi[3], mi3[3];
-  const int b = blockIdx.y, i = blockIdx.x, c = threadIdx.x;
+  const int b = blockIdx.y, i = blockIdx.x + row0, c = threadIdx.x;
   const size_t row_i = (size_t)b * N + i;
   if (c < 9) Ri[c] = rots[row_i * 9 + c];
   if (c < 3) { xi[c] = trans[row_i * 3 + c]; mi3[c] = motif_pos[row_i * 3 + c]; }

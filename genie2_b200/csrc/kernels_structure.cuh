@@ -57,12 +57,12 @@ __global__ void __launch_bounds__(256) ipa_attention_kernel(const float* __restr
                                                             const float* __restrict__ trans,
                                                             const int* __restrict__ mask, const float* __restrict__ Wb,
                                                             const float* __restrict__ bb, const float* __restrict__ hw,
-                                                            float* __restrict__ cat_out, int N) {
+                                                            float* __restrict__ cat_out, int N, int row0) {
   extern __shared__ __align__(16) float sm[];
   float* logit = sm;                          // [12][N]
   float* qs = sm + IPA_H * N;                 // q (192) + q_pts (144)
   float* red = qs + 192 + 144;                // o_pt accumulators [288] for the inverse-frame stage
-  const int b = blockIdx.y, i = blockIdx.x, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int b = blockIdx.y, i = blockIdx.x + row0, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const size_t row_i = (size_t)b * N + i;
   for (int k = tid; k < 192; k += 256) qs[k] = qkv[row_i * IPA_QKV + k];
   for (int k = tid; k < 144; k += 256) qs[192 + k] = qkv[row_i * IPA_QKV + IPA_OFF_QP + k];

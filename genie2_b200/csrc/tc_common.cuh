@@ -245,6 +245,38 @@ __device__ __forceinline__ PixTile pix_tile(uint32_t blk, int N, int Np) {
   t.b = r / nt2;
   return t;
 }
+// Restricted tile set of a row-sharded launch: row pairs [t2_0, t2_0 + nt2) x column blocks [jb_0, jb_0 + njb).
+struct TileRange { uint32_t t2_0, nt2, jb_0, njb; };
+__device__ __forceinline__ PixTile pix_tile(uint32_t blk, const TileRange& tr) {
+  PixTile t;
+  t.jb = tr.jb_0 + blk % tr.njb;
+  const uint32_t r = blk / tr.njb;
+  t.t2 = tr.t2_0 + r % tr.nt2;
+  t.b = r / tr.nt2;
+  return t;
+}
+static inline TileRange full_tile_range(int N, int Np) { return TileRange{0u, (uint32_t)(N + 1) >> 1, 0u, (uint32_t)Np >> 6}; }
+
+// Addressing of the a / b operand tile images (elements).  One GPU: [b][ch][kb][Np rows][64].  Row-sharded
+// runs cut the image into `world` contiguous blocks, one per producing rank, so that an in-place all-gather
+// assembles it: by rows for the outgoing update (RL = rows per rank), by k-blocks for the incoming one
+// (KBL = k-blocks per rank).  Inside a block: [b][ch][KBL][RL][64].
+struct ImgLayout {
+  uint32_t RL, KBL, nkblk;
+  size_t blk;
+};
+static inline ImgLayout img_layout(int B, int Np, int row_split, int k_split) {
+  ImgLayout L;
+  L.RL = (uint32_t)Np / row_split;
+  L.KBL = (uint32_t)(Np >> 6) / k_split;
+  L.nkblk = k_split;
+  L.blk = (size_t)B * 128 * L.KBL * L.RL * 64;
+  return L;
+}
+__device__ __forceinline__ size_t img_off(const ImgLayout& L, uint32_t b, uint32_t ch, uint32_t kb, uint32_t row) {
+  const uint32_t rb = row / L.RL, kq = kb / L.KBL;
+  return ((size_t)rb * L.nkblk + kq) * L.blk + ((((size_t)b * 128 + ch) * L.KBL + (kb - kq * L.KBL)) * L.RL + (row - rb * L.RL)) * 64;
+}
 
 
 }  // namespace tc

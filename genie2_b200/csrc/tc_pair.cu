@@ -12,6 +12,7 @@
 #include <vector>
 
 #include "common.cuh"
+#include "shard.h"
 #include "tc_api.h"
 #include "tc_common.cuh"
 #include "tc_host.h"
@@ -125,7 +126,8 @@ __device__ __forceinline__ void tmem_to_stage(uint8_t* S, uint32_t taddr, uint32
 #define K5_SMEM (K5_STAGES * K5_STAGE_BYTES + 1024 + 128)
 
 __global__ void __launch_bounds__(256, 2) trimul_contract_tc_kernel(const bf16* __restrict__ a, const bf16* __restrict__ b,
-                                                                    bf16* __restrict__ x, int N, int Np, int NJ) {
+                                                                    bf16* __restrict__ x, int N, int Np, int NJ,
+                                                                    const ImgLayout L, int ib0, int nib) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* sm = smem_base_1024(smem_raw);
   uint64_t* full = reinterpret_cast<uint64_t*>(sm + K5_STAGES * K5_STAGE_BYTES);
@@ -133,13 +135,13 @@ __global__ void __launch_bounds__(256, 2) trimul_contract_tc_kernel(const bf16* 
   uint64_t* done = empty + K5_STAGES;
   uint32_t* tslot = reinterpret_cast<uint32_t*>(done + 1);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int nkb = Np >> 6, nib = (Np + 127) >> 7, njb = (Np + NJ - 1) / NJ;
+  const int nkb = Np >> 6, njb = (Np + NJ - 1) / NJ;
   uint32_t blk = blockIdx.x;
   const uint32_t jb = blk % njb; blk /= njb;
-  const uint32_t ib = blk % nib; blk /= nib;       // blk = b * 128 + c
+  const uint32_t ib = ib0 + blk % nib; blk /= nib;  // blk = b * 128 + c; a row-sharded launch owns row blocks [ib0, ib0 + nib)
   const uint32_t nj = min((uint32_t)NJ, (uint32_t)Np - jb * NJ);   // columns of this block (multiple of 64)
-  const bf16* A0 = a + (size_t)blk * nkb * Np * 64 + (size_t)ib * 128 * 64;
-  const bf16* B0 = b + (size_t)blk * nkb * Np * 64 + (size_t)jb * NJ * 64;
+  const uint32_t bb = blk >> 7, cch = blk & 127;
+  const uint32_t bpiece = (L.RL % nj == 0) ? nj : 128u;            // B rows that are contiguous in the (possibly row-split) image
   const uint32_t a_rows = min(128u, (uint32_t)Np - ib * 128u);      // rows present in the plane (64 or 128)
 
   if (tid == 0) {
@@ -160,8 +162,9 @@ __global__ void __launch_bounds__(256, 2) trimul_contract_tc_kernel(const bf16* 
         if (kb >= K5_STAGES) mbar_wait(empty + s, ((kb / K5_STAGES) - 1) & 1);
         uint8_t* st = sm + s * K5_STAGE_BYTES;
         mbar_expect_tx(full + s, (a_rows + nj) * 128u);
-        bulk_g2s(st, A0 + (size_t)kb * Np * 64, a_rows * 128u, full + s);
-        bulk_g2s(st + 16384, B0 + (size_t)kb * Np * 64, nj * 128u, full + s);
+        bulk_g2s(st, a + img_off(L, bb, cch, kb, ib * 128u), a_rows * 128u, full + s);
+        for (uint32_t r = 0; r < nj; r += bpiece)
+          bulk_g2s(st + 16384 + r * 128u, b + img_off(L, bb, cch, kb, jb * NJ + r), min(bpiece, nj - r) * 128u, full + s);
       }
     }
     __syncwarp();
@@ -189,7 +192,6 @@ __global__ void __launch_bounds__(256, 2) trimul_contract_tc_kernel(const bf16* 
   const uint32_t t_lane = tmem + ((q * 32u) << 16);
   // x tile images: [b][t2 = i / 2][jb64][ii = i & 1][channel][64 j], 16-byte chunks swizzled by channel & 7:
   // the 32 KB block of one (t2, jb64) pixel tile is exactly K6's MN-major A operand.
-  const uint32_t bb = blk >> 7, cch = blk & 127;
   for (uint32_t c0 = h * 32; c0 < nj; c0 += 64) {
     uint32_t v[32];
     tmem_ld32(t_lane + c0, v);
@@ -235,7 +237,7 @@ __global__ void __launch_bounds__(256, 2) trimul_contract_tc_kernel(const bf16* 
 
 __global__ void __launch_bounds__(256, 3) trimul_out_tc_kernel(
     const bf16* __restrict__ x, const bf16* __restrict__ g, float* __restrict__ p, int N, int Np,
-    const bf16* __restrict__ Wzimg, const float* __restrict__ uvec, const float* __restrict__ vvec) {
+    const bf16* __restrict__ Wzimg, const float* __restrict__ uvec, const float* __restrict__ vvec, const TileRange tr) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* sm = smem_base_1024(smem_raw);
   uint8_t* X = sm;
@@ -245,7 +247,7 @@ __global__ void __launch_bounds__(256, 3) trimul_out_tc_kernel(
   uint32_t* tslot = reinterpret_cast<uint32_t*>(bar_w + 2);
   float* red = reinterpret_cast<float*>(sm + 65536 + 64);     // [2][128] partials, then mean [128], rstd [128]
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const PixTile T = pix_tile(blockIdx.x, N, Np);
+  const PixTile T = pix_tile(blockIdx.x, tr);
   if (tid == 0) {
     mbar_init(bar_w, 1);
     mbar_init(bar_mma, 1);
@@ -439,20 +441,32 @@ int tc_bind_workspace(gb_ctx* c, void* base, size_t bytes, int B, int N) {
 int tc_trimul_stage(gb_ctx* c, const TriMulW& w, bool outgoing, int stage, float* p, cudaStream_t st) {
   if (c->precision != GB_PREC_BF16) return gb_fail(c, GB_ERR_UNSUPPORTED, "tensor-core path: tf32 kernels are not built in this revision (use bf16 or fp32)");
   TcState* s = static_cast<TcState*>(c->tc_state);
-  const int B = c->B, N = c->N, Np = s->Np;
-  const unsigned tiles = (unsigned)B * ((N + 1) / 2) * (Np / 64);
+  const int B = c->B, N = c->N, Np = s->Np, W = c->shard_world;
   if (stage == 0 || stage == 1) {
-    const int rc = tc_launch_trimul_proj(c, w, outgoing, p, st);
+    int rc = tc_launch_trimul_proj(c, w, outgoing, p, st);
     if (rc != GB_OK) return rc;
+    if (W > 1) {
+      // each rank wrote its block of the operand images; K5 needs every row of b (and, for the incoming
+      // update, every k-block of a as well): in-place all-gather over NVLink
+      const size_t piece = (size_t)B * 128 * Np * Np * 2 / W;
+      if (!outgoing && (rc = shard_all_gather(c, s->a, piece, st)) != GB_OK) return rc;
+      if ((rc = shard_all_gather(c, s->b, piece, st)) != GB_OK) return rc;
+    }
   }
   if (stage == 0 || stage == 2) {
     const int NJ = 256;
-    const unsigned cgrid = (unsigned)B * 128 * ((Np + 127) / 128) * ((Np + NJ - 1) / NJ);
-    trimul_contract_tc_kernel<<<cgrid, 256, K5_SMEM, st>>>(s->a, s->b, s->x, N, Np, NJ);
+    // sharded: both operand images are complete after the all-gather; this rank contracts its own 128-row blocks
+    const ImgLayout L = W > 1 ? (outgoing ? img_layout(B, Np, W, 1) : img_layout(B, Np, 1, W)) : img_layout(B, Np, 1, 1);
+    const int nib = W > 1 ? (N / W) / 128 : (Np + 127) / 128, ib0 = W > 1 ? c->shard_rank * nib : 0;
+    const unsigned cgrid = (unsigned)B * 128 * nib * ((Np + NJ - 1) / NJ);
+    trimul_contract_tc_kernel<<<cgrid, 256, K5_SMEM, st>>>(s->a, s->b, s->x, N, Np, NJ, L, ib0, nib);
     GB_LAUNCH_CHECK(c, "trimul_contract_tc");
   }
   if (stage == 0 || stage == 3) {
-    trimul_out_tc_kernel<<<tiles, 256, K6_SMEM, st>>>(s->x, s->g, p, N, Np, (const bf16*)w.tc_Wz, w.tc_uv, w.tc_uv + 128);
+    TileRange tr = full_tile_range(N, Np);
+    if (W > 1) { tr.nt2 = (uint32_t)(N / W) >> 1; tr.t2_0 = c->shard_rank * tr.nt2; }
+    const unsigned tiles = (unsigned)B * tr.nt2 * tr.njb;
+    trimul_out_tc_kernel<<<tiles, 256, K6_SMEM, st>>>(s->x, s->g, p, N, Np, (const bf16*)w.tc_Wz, w.tc_uv, w.tc_uv + 128, tr);
     GB_LAUNCH_CHECK(c, "trimul_out_tc");
   }
   return GB_OK;

@@ -38,7 +38,7 @@ __device__ __forceinline__ uint32_t relu_pack_bf16(float lo, float hi) {
 }
 
 __global__ void __launch_bounds__(K7_THREADS, 1) pair_transition_tc_kernel(
-    float* __restrict__ p, uint32_t M, int N, uint32_t npairs, const int* __restrict__ rmask, const bf16* __restrict__ W1img,
+    float* __restrict__ p, uint32_t M, uint32_t px0, int N, uint32_t npairs, const int* __restrict__ rmask, const bf16* __restrict__ W1img,
     const float* __restrict__ b1, const bf16* __restrict__ W2img, const float* __restrict__ b2, uint32_t C) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* sm = smem_base_1024(smem_raw);
@@ -148,6 +148,7 @@ __global__ void __launch_bounds__(K7_THREADS, 1) pair_transition_tc_kernel(
     const uint32_t t_lane = tmem + ((q * 32u) << 16);
     auto pair_mask = [&](uint32_t row) -> float {
       if (row >= M) return 0.f;
+      row += px0;                                   // p points at pixel px0 of the map (row-sharded launch)
       const uint32_t NN = (uint32_t)N * N, b = row / NN, rem = row - b * NN, i = rem / N, j = rem - i * N;
       return (float)(rmask[b * N + i] * rmask[b * N + j]);
     };
@@ -343,12 +344,16 @@ int tc_pack_transition(gb_ctx* c, TransitionW& w, const std::vector<float>& w1, 
 
 int tc_pair_transition(gb_ctx* c, const TransitionW& w, float* p, cudaStream_t st) {
   if (c->precision != GB_PREC_BF16) return gb_fail(c, GB_ERR_UNSUPPORTED, "tensor-core path: tf32 kernels are not built in this revision (use bf16 or fp32)");
-  const size_t M = (size_t)c->B * c->N * c->N;
+  size_t M = (size_t)c->B * c->N * c->N, px0 = 0;
   if (M >= (1ull << 31)) return gb_fail(c, GB_ERR_UNSUPPORTED, "pair map too large");
+  if (c->shard_world > 1) {                         // B == 1: this rank's rows are one contiguous pixel range
+    M /= c->shard_world;
+    px0 = M * c->shard_rank;
+  }
   TcState* s = static_cast<TcState*>(c->tc_state);
   const uint32_t npairs = (uint32_t)((M + 255) / 256);
   const uint32_t grid = npairs < (uint32_t)s->num_sms ? npairs : (uint32_t)s->num_sms;
-  pair_transition_tc_kernel<<<grid, K7_THREADS, K7_SMEM, st>>>(p, (uint32_t)M, c->N, npairs, c->mask, (const bf16*)w.tc_W1, w.tc_b1,
+  pair_transition_tc_kernel<<<grid, K7_THREADS, K7_SMEM, st>>>(p + px0 * 128, (uint32_t)M, (uint32_t)px0, c->N, npairs, c->mask, (const bf16*)w.tc_W1, w.tc_b1,
                                                                (const bf16*)w.tc_W2, w.b2, (uint32_t)c->d.pair_transition_n);
   GB_LAUNCH_CHECK(c, "pair_transition_tc");
   return GB_OK;

@@ -157,6 +157,7 @@ class Denoiser(nn.Module):
         self._dirty = True
         self._feat_key = None
         self._keep = None
+        self._shard = None                  # (world, rank, 128-byte NCCL unique id) when row-sharded
 
     # ---- weight / context life cycle -------------------------------------------------
     def _apply(self, fn, *a, **k):
@@ -181,6 +182,19 @@ class Denoiser(nn.Module):
         self.precision = precision
         if self._ctx is not None:
             _lib.check(_lib.load().gb_set_precision(self._ctx, _lib.PRECISIONS[precision]), self._ctx, 'gb_set_precision')
+
+    def shard_rows(self, group=None):
+        """Row-shard every following forward over the ranks of ``group`` (default: the world): ONE sample
+        (B = 1, N a multiple of 128 * world) is split by rows of the pair representation, each rank on its
+        own GPU; all ranks must make the same calls with the same inputs and all receive the full result
+        (csrc/shard.cu).  Collective.  Needs precision 'bf16'."""
+        import torch.distributed as dist
+        from . import shard
+        world, rank = dist.get_world_size(group), dist.get_rank(group)
+        self._shard = (world, rank, shard.exchange_unique_id(group)) if world > 1 else None
+        if self._ctx is not None:           # the communicator is created with the context
+            _lib.load().gb_destroy(self._ctx)
+            self._ctx = None
 
     def __del__(self):
         try:
@@ -209,6 +223,9 @@ class Denoiser(nn.Module):
             self._ctx, self._ctx_device = h, idx
             self._dirty, self._feat_key = True, None
             _lib.check(lib.gb_set_precision(h, _lib.PRECISIONS[self.precision]), h, 'gb_set_precision')
+            if self._shard is not None:
+                world, rank, uid = self._shard
+                _lib.check(lib.gb_shard_init(h, world, rank, uid), h, 'gb_shard_init')
         if self._dirty:
             sd = self.state_dict()
             arr = (_lib.gb_tensor * len(sd))()
@@ -296,6 +313,9 @@ class Denoiser(nn.Module):
         out['z'] = z
         out['ts'] = T(o_rots, o_trans)
         return out
+
+    def collective_count(self):
+        return int(_lib.load().gb_collective_count(self._ctx)) if self._ctx is not None else 0
 
     def launch_count(self):
         return int(_lib.load().gb_launch_count(self._ctx)) if self._ctx is not None else 0

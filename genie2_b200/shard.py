@@ -1,0 +1,66 @@
+"""Row sharding of ONE long sample over the GPUs of a box (BASELINE config C5).
+
+No reference counterpart: the reference only farms whole samples (genie/utils/multiprocessor.py:73-100).
+Host-side logic only; the exchange itself is NCCL inside the CUDA library (csrc/shard.cu):
+
+* ``row_range(N, world, rank)``    rows of the pair representation a rank owns;
+* ``check_shardable(B, N, world)`` the constraints of the kernels (one sample, whole 128-row blocks per rank);
+* ``exchange_unique_id(group)``    rank 0 draws the 128-byte NCCL unique id, every rank receives it over the
+                                   process group that launched the job (``nccl`` under torchrun, ``gloo`` in tests);
+* ``traffic_bytes(N, world, ...)`` bytes each rank receives per denoiser eval (for the bench line).
+"""
+import ctypes as C
+
+UNIQUE_ID_BYTES = 128
+
+
+def row_range(N, world, rank):
+    if world < 1 or not 0 <= rank < world:
+        raise ValueError('bad rank %d of %d' % (rank, world))
+    if N % world:
+        raise ValueError('N = %d is not divisible by world = %d' % (N, world))
+    rows = N // world
+    return rank * rows, (rank + 1) * rows
+
+
+def check_shardable(B, N, world):
+    """Raises ValueError with the reason when (B, N) cannot be row-sharded over ``world`` GPUs."""
+    if world == 1:
+        return
+    if B != 1:
+        raise ValueError('row sharding handles one sample per call (B = %d); batches shard by sample instead' % B)
+    if N % (128 * world):
+        raise ValueError('row sharding over %d GPUs needs N to be a multiple of %d (got %d)' % (world, 128 * world, N))
+
+
+def traffic_bytes(N, world, n_pair_layer=5, n_struct_layer=8, c_p=128, c_s=384):
+    """Bytes RECEIVED per rank per denoiser eval: per pair layer one bf16 image for the outgoing update and
+    two for the incoming one, per structure layer the fp32 single representation."""
+    if world == 1:
+        return 0
+    image = N * N * c_p * 2
+    per_eval = n_pair_layer * 3 * image + n_struct_layer * N * c_s * 4
+    return per_eval * (world - 1) // world
+
+
+def _draw_unique_id():
+    from . import _lib
+    buf = (C.c_uint8 * UNIQUE_ID_BYTES)()
+    _lib.check(_lib.load().gb_shard_unique_id(buf), None, 'gb_shard_unique_id')
+    return bytes(buf)
+
+
+def exchange_unique_id(group=None, draw=_draw_unique_id):
+    """Collective over ``group``: returns the same 128 bytes on every rank."""
+    import torch
+    import torch.distributed as dist
+    rank = dist.get_rank(group)
+    payload = draw() if rank == 0 else bytes(UNIQUE_ID_BYTES)
+    if len(payload) != UNIQUE_ID_BYTES:
+        raise ValueError('unique id must be %d bytes' % UNIQUE_ID_BYTES)
+    t = torch.tensor(list(payload), dtype=torch.uint8)
+    on_gpu = dist.get_backend(group) == 'nccl'
+    if on_gpu:
+        t = t.cuda()
+    dist.broadcast(t, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
+    return bytes(t.cpu().tolist())

@@ -151,6 +151,24 @@ int gb_sample_host(gb_ctx* ctx, const float* x_T_host, float* x_out_host, int t_
 int64_t gb_launch_count(const gb_ctx* ctx);
 int64_t gb_workspace_bytes(const gb_ctx* ctx);
 
+/* ---- row sharding of ONE long sample (B = 1) over the GPUs of a box (BASELINE config C5) ----
+ * No reference counterpart: the reference farms whole samples, one process per GPU
+ * (genie/utils/multiprocessor.py:73-100), and a length-1024 sample runs on a single device.
+ * One process per GPU; every rank creates its own context on its own device, loads the same
+ * weights, binds the same features and makes the same calls.  Rank r owns rows
+ * [r N / world, (r+1) N / world) of the pair representation; gb_denoise all-gathers the triangle
+ * operands (bf16) and the per-layer IPA result over NCCL on the caller's stream, and every rank
+ * returns the full z.  The result is bit-identical to the single-GPU one.
+ *   gb_shard_unique_id: rank 0 fills 128 bytes (an ncclUniqueId) that the caller distributes
+ *                       to the other ranks by any means (torch.distributed, a file, MPI).
+ *   gb_shard_init:      collective; before gb_set_features.  world == 1 turns sharding off.
+ * Requirements: bf16 precision, B == 1, N a multiple of 128 * world, no triangle attention.
+ * libnccl.so.2 is resolved with dlopen on first use (GB_ERR_MISSING if absent). */
+int gb_shard_unique_id(void* out128);
+int gb_shard_init(gb_ctx* ctx, int world, int rank, const void* id128);
+int gb_shard_info(const gb_ctx* ctx, int* world, int* rank);
+int64_t gb_collective_count(const gb_ctx* ctx); /* all-gathers enqueued by this context */
+
 /* ---- per-kernel entry points (unit parity tests; same kernels the forward uses) ---- */
 
 /* geo_utils.py:21-85 without a context. */

@@ -1,0 +1,106 @@
+"""One rank of the row-sharding check / timing (launched by torchrun from test_gpu_shard.py or by hand):
+
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29533 \
+        tests/shard_worker.py --length 256 --check [--time 20]
+
+Every rank first runs the denoiser on its own GPU unsharded, then row-sharded over all ranks, on the same
+seeded inputs, and compares: z (and p, when it fits) must be bit-identical, on every rank.  --time K also
+times K evals of each and prints one JSON line on rank 0 (device time, max over ranks)."""
+import argparse
+import json
+import os
+import sys
+
+import torch
+import torch.distributed as dist
+
+sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+from common import O, W, feats_to, make_denoiser  # noqa: E402
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--length', type=int, default=256)
+    ap.add_argument('--check', action='store_true')
+    ap.add_argument('--time', type=int, default=0)
+    ap.add_argument('--out', default='')
+    a = ap.parse_args()
+    import genie2_b200
+    from genie2_b200 import shard
+
+    rank, world = int(os.environ['RANK']), int(os.environ['WORLD_SIZE'])
+    local = int(os.environ.get('LOCAL_RANK', rank))
+    torch.cuda.set_device(local)
+    dev = 'cuda:%d' % local
+    dist.init_process_group('nccl', device_id=torch.device(dev))
+    N = a.length
+    shard.check_shardable(1, N, world)
+    cfg = O.OracleConfig()
+    sd = W.make_state_dict(cfg, 2, 'activated')
+    g = torch.Generator().manual_seed(4)
+    feats = O.make_features([[N]])
+    trans = torch.randn(1, N, 3, generator=g) * 12
+    rots = O.compute_frenet_frames(trans, feats['chain_index'], feats['residue_mask'])
+    ts = torch.tensor([400], dtype=torch.int32, device=dev)
+    model = make_denoiser(cfg, sd, precision='bf16', device=dev)
+    with_p = a.check and N <= 512
+    model.return_intermediates = with_p
+    f = feats_to(feats, dev)
+    t = genie2_b200.T(rots.to(dev), trans.to(dev))
+
+    def timed(k):
+        for _ in range(3):
+            model(t, ts, f)
+        dist.barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(k):
+            model(t, ts, f)
+        e1.record()
+        torch.cuda.synchronize()
+        ms = torch.tensor([e0.elapsed_time(e1) / k], device=dev)
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms)
+
+    one = model(t, ts, f)
+    one = {k: v.clone() for k, v in one.items() if k in ('z', 'p')}
+    ms_one = timed(a.time) if a.time else None
+    model.return_intermediates = False
+    model.shard_rows()
+    model.return_intermediates = with_p
+    many = model(t, ts, f)
+    torch.cuda.synchronize()
+    ok = bool(torch.isfinite(many['z']).all())
+    if a.check:
+        # N > 256: both runs use the same kernels on the same tiles, so z is bit-identical.  N <= 256: the unsharded
+        # run takes the bf16 tensor-core structure net, the sharded one the fp32 structure kernels, so only the pair
+        # representation is bit-identical and z agrees to bf16 accuracy (tolerance of test_gpu_tensorcore.py).
+        if N > 256:
+            ok = ok and torch.equal(one['z'], many['z'])
+        else:
+            ok = ok and float((one['z'] - many['z']).norm() / one['z'].norm()) < 3e-2
+        if with_p:
+            ok = ok and torch.equal(one['p'], many['p'])
+        if not ok:
+            dz = float((one['z'] - many['z']).abs().max())
+            print('rank %d: MISMATCH max |dz| = %g' % (rank, dz), flush=True)
+    n_coll = model.collective_count()
+    model.return_intermediates = False
+    ms_many = timed(a.time) if a.time else None
+    flag = torch.tensor([1 if ok else 0], device=dev)
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    if rank == 0:
+        line = {'workload': 'C5 row-sharded denoiser eval, L=%d B=1, bf16' % N, 'world': world, 'ok': bool(int(flag)),
+                'collectives_per_eval': n_coll, 'recv_bytes_per_rank_per_eval': shard.traffic_bytes(N, world),
+                'ms_per_eval_one_gpu': ms_one, 'ms_per_eval_sharded': ms_many}
+        print(json.dumps(line), flush=True)
+        if a.out:
+            with open(a.out, 'w') as fh:
+                fh.write(json.dumps(line) + '\n')
+    dist.destroy_process_group()
+    sys.exit(0 if int(flag) else 1)
+
+
+if __name__ == '__main__':
+    main()
