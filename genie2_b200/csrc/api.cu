@@ -687,7 +687,7 @@ extern "C" int gb_denoise(gb_ctx* c, const float* rots, const float* trans, cons
   // StructureNet
   float* s = c->s;
   int state_idx = 1;
-  const bool tc_struct = c->precision == GB_PREC_BF16 && tc_struct_supported(c, N) && W == 1;
+  const bool tc_struct = c->precision == GB_PREC_BF16 && tc_struct_supported(c, N);
   if (tc_struct) {
     if ((rc = tc_structure_net(c, aux ? aux->states : nullptr, st))) return rc;
   } else

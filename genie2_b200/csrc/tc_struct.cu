@@ -13,6 +13,7 @@
 
 #include "common.cuh"
 #include "ipa_dims.h"
+#include "shard.h"
 #include "tc_api.h"
 #include "tc_common.cuh"
 #include "tc_host.h"
@@ -36,6 +37,7 @@ struct GemmImgArgs {
   float* C;           // fp32 out [R][ldc] or null
   bf16* O;            // bf16 image out [Nw/64][Rp][64] or null
   int Rp, Nw, nkb, R, ldc, ldr, relu;
+  int mblk0;          // first 128-row block of this launch (row-sharded launches compute their own rows only)
   int kvsplit;        // > 0: IPA projection scatter, value = N (keys per sample): columns < IPA_QW go to rows [R][IPA_QW],
                       // the rest to key-major planes [B][IPA_NPLANE][N][4] behind them (see ipa_dims.h)
 };
@@ -48,7 +50,7 @@ __global__ void __launch_bounds__(256, 1) gemm_img_tc_kernel(const GemmImgArgs g
   uint64_t* done = empty + GI_STAGES;
   uint32_t* tslot = reinterpret_cast<uint32_t*>(done + 1);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const uint32_t n0 = blockIdx.x * 64u, m0 = blockIdx.y * 128u;
+  const uint32_t n0 = blockIdx.x * 64u, m0 = (g.mblk0 + blockIdx.y) * 128u;
   if (tid == 0) {
     for (int s = 0; s < GI_STAGES; ++s) { mbar_init(full + s, 1); mbar_init(empty + s, 1); }
     mbar_init(done, 1);
@@ -205,7 +207,7 @@ __global__ void ln_img_kernel(const float* __restrict__ in, float* __restrict__ 
 __global__ void __launch_bounds__(256, 2) ipa_prep_tc_kernel(const float* __restrict__ p, int B, int N, int Np,
                                                              const int* __restrict__ rmask, const bf16* __restrict__ Wimg,
                                                              const float* __restrict__ bias96, float* __restrict__ pbias,
-                                                             bf16* __restrict__ z_img, int ncol) {
+                                                             bf16* __restrict__ z_img, int ncol, const TileRange tr) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* sm = smem_base_1024(smem_raw);
   uint8_t* A = sm;
@@ -214,7 +216,7 @@ __global__ void __launch_bounds__(256, 2) ipa_prep_tc_kernel(const float* __rest
   uint64_t* bar_mma = bar_w + 1;
   uint32_t* tslot = reinterpret_cast<uint32_t*>(bar_w + 2);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const PixTile T = pix_tile(blockIdx.x, N, Np);
+  const PixTile T = pix_tile(blockIdx.x, tr);
   if (tid == 0) {
     mbar_init(bar_w, 1);
     mbar_init(bar_mma, 1);
@@ -332,10 +334,10 @@ __global__ void ipa_points_planes_kernel(float* __restrict__ qkv, const float* _
 }
 
 // ---------------------------------------------------------------------------------------------
-// ipa_attention_tc_kernel (invariant_point_attention.py:181-259), Np <= 256.
-// One CTA = IA_G consecutive query rows i0.. of sample b (256 threads):
+// ipa_attention_tc_kernel (invariant_point_attention.py:181-259), Np <= 1024.
+// One CTA = G consecutive query rows i0.. of sample b (IA_THREADS threads):
 //   1. logits: thread j owns key j; per head it loads k / k_pts of its key once (registers) and scores
-//      it against the IA_G queries (q, q_pts broadcast from shared memory); + precomputed pair bias.
+//      it against the G queries (q, q_pts broadcast from shared memory); + precomputed pair bias.
 //   2. softmax over j per (head, query) in shared memory; probabilities are kept fp32 (for o, o_pt)
 //      and written as bf16 B-operand images a_img[g] = [Np/64 kb][16 rows = head][64 j].
 //   3. warp 0 streams z_img of each query row in 64-key chunks (2 x 8 KB, cp.async.bulk, 4-deep ring),
@@ -344,16 +346,50 @@ __global__ void ipa_points_planes_kernel(float* __restrict__ qkv, const float* _
 //   4. epilogue: inverse frame + norms for o_pt; everything is written as bf16 straight into the
 //      operand image of the output projection (cat_img, K = 2112: o | o_pt.x | .y | .z | |o_pt| | o_pair).
 // ---------------------------------------------------------------------------------------------
-#define IA_G 8          // queries per CTA: every CTA streams the whole K / V of its sample, so the L2 traffic per query is 1/IA_G
 #define IA_ZRING 2
 #define IA_THREADS 768   // the CUDA-core phases run at ~0.2 IPC per warp (dependent FMA chains): occupancy, not bandwidth, bounds them
-#define IA_OFF_AIMG (IA_ZRING * 16384)
-#define IA_OFF_P (IA_OFF_AIMG + IA_G * 8192)
-#define IA_OFF_QS (IA_OFF_P + 12 * 256 * IA_G * 4)
-#define IA_OFF_RED (IA_OFF_QS + IA_G * 12 * 28 * 4)
-#define IA_OFF_FR (IA_OFF_RED + IA_G * 480 * 4)
-#define IA_OFF_BAR (IA_OFF_FR + IA_G * 12 * 4)
-#define IA_SMEM (IA_OFF_BAR + 128 + 1024)
+// Queries per CTA (template parameter G): every CTA streams the whole K / V of its sample from L2, so that traffic
+// per query is 1 / G; the fp32 logits [12][Np][G] and the probability images must fit in shared memory:
+// G = 8 up to 256 keys, 4 up to 512, 2 up to 1024.
+struct IaSmem { uint32_t aimg, P, qs, red, fr, bar, total; };
+__host__ __device__ inline IaSmem ia_smem(int G, int Np) {
+  IaSmem o;
+  o.aimg = IA_ZRING * 16384;
+  o.P = o.aimg + G * (Np >> 6) * 2048;
+  o.qs = o.P + 12 * Np * G * 4;
+  o.red = o.qs + G * 12 * 28 * 4;
+  o.fr = o.red + G * 480 * 4;
+  o.bar = o.fr + G * 12 * 4;
+  o.total = o.bar + 128 + 1024;
+  return o;
+}
+static inline int ia_queries_per_cta(int Np) { return Np <= 256 ? 8 : Np <= 512 ? 4 : 2; }
+
+// G consecutive floats of the logit / probability array
+template <int G> __device__ __forceinline__ void p_load(const float* pp, float (&t)[G]) {
+  if constexpr (G % 4 == 0) {
+#pragma unroll
+    for (int g4 = 0; g4 < G / 4; ++g4) {
+      const float4 v = *reinterpret_cast<const float4*>(pp + 4 * g4);
+      t[4 * g4] = v.x; t[4 * g4 + 1] = v.y; t[4 * g4 + 2] = v.z; t[4 * g4 + 3] = v.w;
+    }
+  } else {
+#pragma unroll
+    for (int g2 = 0; g2 < G / 2; ++g2) {
+      const float2 v = *reinterpret_cast<const float2*>(pp + 2 * g2);
+      t[2 * g2] = v.x; t[2 * g2 + 1] = v.y;
+    }
+  }
+}
+template <int G> __device__ __forceinline__ void p_store(float* pp, const float (&t)[G]) {
+  if constexpr (G % 4 == 0) {
+#pragma unroll
+    for (int g4 = 0; g4 < G / 4; ++g4) *reinterpret_cast<float4*>(pp + 4 * g4) = make_float4(t[4 * g4], t[4 * g4 + 1], t[4 * g4 + 2], t[4 * g4 + 3]);
+  } else {
+#pragma unroll
+    for (int g2 = 0; g2 < G / 2; ++g2) *reinterpret_cast<float2*>(pp + 2 * g2) = make_float2(t[2 * g2], t[2 * g2 + 1]);
+  }
+}
 
 // 2-byte store of element k of row r of a [.][Rp][64] operand image
 __device__ __forceinline__ void img_store(bf16* img, int Rp, uint32_t r, uint32_t k, float v) {
@@ -361,30 +397,34 @@ __device__ __forceinline__ void img_store(bf16* img, int Rp, uint32_t r, uint32_
   *reinterpret_cast<bf16*>(base + ((((k & 63) >> 3) ^ (r & 7u)) << 4) + ((k & 7) << 1)) = __float2bfloat16_rn(v);
 }
 
+template <int G>
 __global__ void __launch_bounds__(IA_THREADS, 1) ipa_attention_tc_kernel(
     const float* __restrict__ qkv, const float* __restrict__ pbias, const bf16* __restrict__ z_img,
     const float* __restrict__ rots, const float* __restrict__ trans, const float* __restrict__ hw,
-    bf16* __restrict__ cat_img, int N, int Np, int Rp) {
+    bf16* __restrict__ cat_img, int N, int Np, int Rp, int row0) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* sm = smem_base_1024(smem_raw);
+  const IaSmem L = ia_smem(G, Np);
   uint8_t* zring = sm;
-  uint8_t* aimg = sm + IA_OFF_AIMG;
-  float* P = reinterpret_cast<float*>(sm + IA_OFF_P);          // [12 h][Np j][IA_G]
-  float* qs = reinterpret_cast<float*>(sm + IA_OFF_QS);        // [g][h][28]: q*sc (16) | q_pts c*4+p (12)
-  float* oacc = reinterpret_cast<float*>(sm + IA_OFF_RED);     // [g][h*40 + e]: o (e < 16) | o_pt global frame (16 + c*8 + p)
-  float* fr = reinterpret_cast<float*>(sm + IA_OFF_FR);        // [g][12] R (9) t (3)
-  uint64_t* full = reinterpret_cast<uint64_t*>(sm + IA_OFF_BAR);
+  uint8_t* aimg = sm + L.aimg;                                 // [g][Np/64 kb][16 rows = head][64 j]
+  float* P = reinterpret_cast<float*>(sm + L.P);               // [12 h][Np j][G]
+  float* qs = reinterpret_cast<float*>(sm + L.qs);             // [g][h][28]: q*sc (16) | q_pts c*4+p (12)
+  float* oacc = reinterpret_cast<float*>(sm + L.red);          // [g][h*40 + e]: o (e < 16) | o_pt global frame (16 + c*8 + p)
+  float* fr = reinterpret_cast<float*>(sm + L.fr);             // [g][12] R (9) t (3)
+  uint64_t* full = reinterpret_cast<uint64_t*>(sm + L.bar);
   uint64_t* empty = full + IA_ZRING;
-  uint64_t* done = empty + IA_ZRING;                           // [IA_G]
-  uint32_t* tslot = reinterpret_cast<uint32_t*>(done + IA_G);
+  uint64_t* done = empty + IA_ZRING;                           // [G]
+  uint32_t* tslot = reinterpret_cast<uint32_t*>(done + G);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int b = blockIdx.y, i0 = blockIdx.x * IA_G;
-  const int ng = min(IA_G, N - i0), nch = Np >> 6;
+  const int b = blockIdx.y, i0 = row0 + blockIdx.x * G;        // row0: first query row of a row-sharded launch
+  const int ng = min(G, N - i0), nch = Np >> 6;
+  const uint32_t aimg_g = (uint32_t)nch * 2048u;               // bytes of one query's probability image
+  constexpr uint32_t TCOLS = G * 16 < 32 ? 32 : G * 16;
   const size_t rowb = (size_t)b * N;
 
   if (tid == 0) {
     for (int s = 0; s < IA_ZRING; ++s) { mbar_init(full + s, 1); mbar_init(empty + s, 1); }
-    for (int g = 0; g < IA_G; ++g) mbar_init(done + g, 1);
+    for (int g = 0; g < G; ++g) mbar_init(done + g, 1);
     fence_mbar_init();
     // prefetch the first ring of z chunks: independent of everything this kernel computes
     const int tot = ng * nch;
@@ -396,10 +436,10 @@ __global__ void __launch_bounds__(IA_THREADS, 1) ipa_attention_tc_kernel(
       bulk_g2s(zring + it * 16384 + 8192, src + (size_t)Np * 128, 8192, full + it);
     }
   }
-  if (warp == 2) tmem_alloc(tslot, IA_G * 16);
-  // q, q_pts of the IA_G queries; a_img cleared (rows 12..15 and padded keys must read as zero)
+  if (warp == 2) tmem_alloc(tslot, TCOLS);
+  // q, q_pts of the G queries; a_img cleared (rows 12..15 and padded keys must read as zero)
   const float sc_qk = sqrtf(1.f / (3.f * IPA_C));
-  for (int e = tid; e < IA_G * 12 * 28; e += IA_THREADS) {
+  for (int e = tid; e < G * 12 * 28; e += IA_THREADS) {
     const int g = e / 336, r = e - g * 336, h = r / 28, x = r - h * 28;
     float v = 0.f;
     if (g < ng) {
@@ -408,9 +448,9 @@ __global__ void __launch_bounds__(IA_THREADS, 1) ipa_attention_tc_kernel(
     }
     qs[e] = v;
   }
-  for (int e = tid; e < IA_G * 8192 / 16; e += IA_THREADS) reinterpret_cast<uint4*>(aimg)[e] = make_uint4(0, 0, 0, 0);
-  for (int e = tid; e < IA_G * 480; e += IA_THREADS) oacc[e] = 0.f;
-  if (tid < IA_G * 12) {
+  for (int e = tid; e < (int)(G * aimg_g / 16); e += IA_THREADS) reinterpret_cast<uint4*>(aimg)[e] = make_uint4(0, 0, 0, 0);
+  for (int e = tid; e < G * 480; e += IA_THREADS) oacc[e] = 0.f;
+  if (tid < G * 12) {
     const int g = tid / 12, x = tid - g * 12;
     fr[tid] = g < ng ? (x < 9 ? rots[(rowb + i0 + g) * 9 + x] : trans[(rowb + i0 + g) * 3 + x - 9]) : 0.f;
   }
@@ -419,91 +459,80 @@ __global__ void __launch_bounds__(IA_THREADS, 1) ipa_attention_tc_kernel(
   tc_fence_after();
   const uint32_t tmem = *tslot;
 
-  // ---- 1. logits
+  // ---- 1. logits: thread (j mod 256, head group); keys in blocks of 256
   {
-    const int j = tid & 255, hg = tid >> 8;      // two thread groups of 256 keys, six heads each
-    const bool kv = j < N;
-    const float4* kpl = reinterpret_cast<const float4*>(qkv + (size_t)gridDim.y * N * IPA_QW) + (size_t)b * IPA_NPLANE * N + (kv ? j : 0);
+    constexpr int HPG = 12 / (IA_THREADS / 256);   // heads per thread group
+    const int hg = tid >> 8;
+    for (int j = tid & 255; j < Np; j += 256) {
+      const bool kv = j < N;
+      const float4* kpl = reinterpret_cast<const float4*>(qkv + (size_t)gridDim.y * N * IPA_QW) + (size_t)b * IPA_NPLANE * N + (kv ? j : 0);
 #pragma unroll
-    for (int hh = 0; hh < 12 / (IA_THREADS / 256); ++hh) {       // unrolled: the K planes and pair-bias words of later heads are in flight early
-      const int h = hg * (12 / (IA_THREADS / 256)) + hh;
-      float out[IA_G];
+      for (int hh = 0; hh < HPG; ++hh) {       // unrolled: the K planes and pair-bias words of later heads are in flight early
+        const int h = hg * HPG + hh;
+        float out[G];
 #pragma unroll
-      for (int g = 0; g < IA_G; ++g) out[g] = -3.0e38f;
-      if (kv) {
-        float k[28];
+        for (int g = 0; g < G; ++g) out[g] = -3.0e38f;
+        if (kv) {
+          float k[28];
 #pragma unroll
-        for (int e = 0; e < 7; ++e) {       // planes 0..3 = k, 4..6 = k_pts x / y / z: consecutive keys, consecutive 16-byte words
-          const float4 t = kpl[(size_t)(h * IPA_PLANES_PER_HEAD + e) * N];
-          k[4 * e] = t.x; k[4 * e + 1] = t.y; k[4 * e + 2] = t.z; k[4 * e + 3] = t.w;
-        }
-        const float gam = -0.5f * hw[h];
-#pragma unroll
-        for (int g = 0; g < IA_G; ++g) {
-          const float4* q4 = reinterpret_cast<const float4*>(qs + (g * 12 + h) * 28);
-          float qk = 0.f, d2 = 0.f;
-#pragma unroll
-          for (int e = 0; e < 4; ++e) { const float4 t = q4[e]; qk = fmaf(t.x, k[4 * e], qk); qk = fmaf(t.y, k[4 * e + 1], qk); qk = fmaf(t.z, k[4 * e + 2], qk); qk = fmaf(t.w, k[4 * e + 3], qk); }
-#pragma unroll
-          for (int e = 4; e < 7; ++e) {
-            const float4 t = q4[e];
-            const float dx = t.x - k[4 * e], dy = t.y - k[4 * e + 1], dz = t.z - k[4 * e + 2], dw = t.w - k[4 * e + 3];
-            d2 = fmaf(dx, dx, d2); d2 = fmaf(dy, dy, d2); d2 = fmaf(dz, dz, d2); d2 = fmaf(dw, dw, d2);
+          for (int e = 0; e < 7; ++e) {       // planes 0..3 = k, 4..6 = k_pts x / y / z: consecutive keys, consecutive 16-byte words
+            const float4 t = kpl[(size_t)(h * IPA_PLANES_PER_HEAD + e) * N];
+            k[4 * e] = t.x; k[4 * e + 1] = t.y; k[4 * e + 2] = t.z; k[4 * e + 3] = t.w;
           }
-          float pb = 0.f;
-          if (g < ng) pb = pbias[((rowb + i0 + g) * 12 + h) * Np + j];
-          out[g] = qk + pb + gam * d2;
-        }
-      }
-      if (j < Np) {
+          const float gam = -0.5f * hw[h];
 #pragma unroll
-        for (int g4 = 0; g4 < IA_G / 4; ++g4)
-          *reinterpret_cast<float4*>(P + ((size_t)h * Np + j) * IA_G + 4 * g4) = make_float4(out[4 * g4], out[4 * g4 + 1], out[4 * g4 + 2], out[4 * g4 + 3]);
+          for (int g = 0; g < G; ++g) {
+            const float4* q4 = reinterpret_cast<const float4*>(qs + (g * 12 + h) * 28);
+            float qk = 0.f, d2 = 0.f;
+#pragma unroll
+            for (int e = 0; e < 4; ++e) { const float4 t = q4[e]; qk = fmaf(t.x, k[4 * e], qk); qk = fmaf(t.y, k[4 * e + 1], qk); qk = fmaf(t.z, k[4 * e + 2], qk); qk = fmaf(t.w, k[4 * e + 3], qk); }
+#pragma unroll
+            for (int e = 4; e < 7; ++e) {
+              const float4 t = q4[e];
+              const float dx = t.x - k[4 * e], dy = t.y - k[4 * e + 1], dz = t.z - k[4 * e + 2], dw = t.w - k[4 * e + 3];
+              d2 = fmaf(dx, dx, d2); d2 = fmaf(dy, dy, d2); d2 = fmaf(dz, dz, d2); d2 = fmaf(dw, dw, d2);
+            }
+            float pb = 0.f;
+            if (g < ng) pb = pbias[((rowb + i0 + g) * 12 + h) * Np + j];
+            out[g] = qk + pb + gam * d2;
+          }
+        }
+        p_store<G>(P + ((size_t)h * Np + j) * G, out);
       }
     }
   }
   __syncthreads();
-  // ---- 2. softmax over j; warp w owns heads w, w+8
+  // ---- 2. softmax over j; one warp per head
   for (int h = warp; h < 12; h += IA_THREADS / 32) {
-    float mx[IA_G], sum[IA_G];
+    float mx[G], sum[G], t[G];
 #pragma unroll
-    for (int g = 0; g < IA_G; ++g) { mx[g] = -3.0e38f; sum[g] = 0.f; }
+    for (int g = 0; g < G; ++g) { mx[g] = -3.0e38f; sum[g] = 0.f; }
     for (int j = lane; j < Np; j += 32) {
-      const float* pp = P + ((size_t)h * Np + j) * IA_G;
+      p_load<G>(P + ((size_t)h * Np + j) * G, t);
 #pragma unroll
-      for (int g4 = 0; g4 < IA_G / 4; ++g4) {
-        const float4 t = *reinterpret_cast<const float4*>(pp + 4 * g4);
-        mx[4 * g4] = fmaxf(mx[4 * g4], t.x); mx[4 * g4 + 1] = fmaxf(mx[4 * g4 + 1], t.y);
-        mx[4 * g4 + 2] = fmaxf(mx[4 * g4 + 2], t.z); mx[4 * g4 + 3] = fmaxf(mx[4 * g4 + 3], t.w);
-      }
+      for (int g = 0; g < G; ++g) mx[g] = fmaxf(mx[g], t[g]);
     }
 #pragma unroll
-    for (int g = 0; g < IA_G; ++g) mx[g] = warp_max(mx[g]);
+    for (int g = 0; g < G; ++g) mx[g] = warp_max(mx[g]);
     for (int j = lane; j < Np; j += 32) {
-      float* pp = P + ((size_t)h * Np + j) * IA_G;
+      float* pp = P + ((size_t)h * Np + j) * G;
+      p_load<G>(pp, t);
 #pragma unroll
-      for (int g4 = 0; g4 < IA_G / 4; ++g4) {
-        float4 t = *reinterpret_cast<float4*>(pp + 4 * g4);
-        t.x = __expf(t.x - mx[4 * g4]); t.y = __expf(t.y - mx[4 * g4 + 1]); t.z = __expf(t.z - mx[4 * g4 + 2]); t.w = __expf(t.w - mx[4 * g4 + 3]);
-        sum[4 * g4] += t.x; sum[4 * g4 + 1] += t.y; sum[4 * g4 + 2] += t.z; sum[4 * g4 + 3] += t.w;
-        *reinterpret_cast<float4*>(pp + 4 * g4) = t;
-      }
+      for (int g = 0; g < G; ++g) { t[g] = __expf(t[g] - mx[g]); sum[g] += t[g]; }
+      p_store<G>(pp, t);
     }
 #pragma unroll
-    for (int g = 0; g < IA_G; ++g) sum[g] = 1.f / warp_sum(sum[g]);
+    for (int g = 0; g < G; ++g) sum[g] = 1.f / warp_sum(sum[g]);
     for (int j = lane; j < Np; j += 32) {
-      float* pp = P + ((size_t)h * Np + j) * IA_G;
+      float* pp = P + ((size_t)h * Np + j) * G;
       const uint32_t off = (j >> 6) * 2048u + h * 128u + (((((uint32_t)j & 63) >> 3) ^ ((uint32_t)h & 7u)) << 4) + ((j & 7) << 1);
+      p_load<G>(pp, t);
 #pragma unroll
-      for (int g4 = 0; g4 < IA_G / 4; ++g4) {
-        float4 t = *reinterpret_cast<float4*>(pp + 4 * g4);
-        t.x *= sum[4 * g4]; t.y *= sum[4 * g4 + 1]; t.z *= sum[4 * g4 + 2]; t.w *= sum[4 * g4 + 3];
-        *reinterpret_cast<float4*>(pp + 4 * g4) = t;
-        *reinterpret_cast<bf16*>(aimg + (4 * g4) * 8192 + off) = __float2bfloat16_rn(t.x);
-        *reinterpret_cast<bf16*>(aimg + (4 * g4 + 1) * 8192 + off) = __float2bfloat16_rn(t.y);
-        *reinterpret_cast<bf16*>(aimg + (4 * g4 + 2) * 8192 + off) = __float2bfloat16_rn(t.z);
-        *reinterpret_cast<bf16*>(aimg + (4 * g4 + 3) * 8192 + off) = __float2bfloat16_rn(t.w);
+      for (int g = 0; g < G; ++g) {
+        t[g] *= sum[g];
+        *reinterpret_cast<bf16*>(aimg + g * aimg_g + off) = __float2bfloat16_rn(t[g]);
       }
+      p_store<G>(pp, t);
     }
   }
   fence_proxy_async();
@@ -531,7 +560,7 @@ __global__ void __launch_bounds__(IA_THREADS, 1) ipa_attention_tc_kernel(
           const int s = it % IA_ZRING;
           mbar_wait(full + s, (it / IA_ZRING) & 1);
           tc_fence_after();
-          const uint32_t za = smem_u32(zring + s * 16384), ab = smem_u32(aimg + g * 8192 + ch * 2048);
+          const uint32_t za = smem_u32(zring + s * 16384), ab = smem_u32(aimg + g * aimg_g + ch * 2048);
 #pragma unroll
           for (int k = 0; k < 4; ++k)
             umma(tmem + g * 16, umma_desc_mn(za + k * 2048, 8192), umma_desc(ab + k * 32), idesc, (ch | k) ? 1u : 0u);
@@ -545,39 +574,36 @@ __global__ void __launch_bounds__(IA_THREADS, 1) ipa_attention_tc_kernel(
     // o[h][16] and o_pt[h][8][3] (global frame): 120 float4 groups (10 value planes per head).  One warp
     // per group, lanes over keys (coalesced plane reads, conflict-free P reads), butterfly reduction.
     const float4* vpl = reinterpret_cast<const float4*>(qkv + (size_t)gridDim.y * N * IPA_QW) + (size_t)b * IPA_NPLANE * N;
-    for (int t = warp - 2; t < 120; t += IA_THREADS / 32 - 2) {       // one value plane per pass, its 8 key loads in flight together
+    for (int t = warp - 2; t < 120; t += IA_THREADS / 32 - 2) {       // one value plane per pass, 8 key loads in flight together
       const int h = t / 10, ev = t - h * 10;
       const float4* src = vpl + (size_t)(h * IPA_PLANES_PER_HEAD + 7 + ev) * N;
-      float4 vv[8];
+      float acc[G][4];
 #pragma unroll
-      for (int u = 0; u < 8; ++u) {
-        const int j = lane + 32 * u;
-        vv[u] = j < N ? src[j] : make_float4(0.f, 0.f, 0.f, 0.f);
-      }
-      float acc[IA_G][4];
+      for (int g = 0; g < G; ++g) acc[g][0] = acc[g][1] = acc[g][2] = acc[g][3] = 0.f;
+      for (int j0 = 0; j0 < N; j0 += 256) {
+        float4 vv[8];
 #pragma unroll
-      for (int g = 0; g < IA_G; ++g) acc[g][0] = acc[g][1] = acc[g][2] = acc[g][3] = 0.f;
+        for (int u = 0; u < 8; ++u) {
+          const int j = j0 + lane + 32 * u;
+          vv[u] = j < N ? src[j] : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
 #pragma unroll
-      for (int u = 0; u < 8; ++u) {
-        const int j = lane + 32 * u;
-        if (j < N) {
-          const float* pp = P + ((size_t)h * Np + j) * IA_G;
-          const float4 v = vv[u];
+        for (int u = 0; u < 8; ++u) {
+          const int j = j0 + lane + 32 * u;
+          if (j < N) {
+            float av[G];
+            p_load<G>(P + ((size_t)h * Np + j) * G, av);
+            const float4 v = vv[u];
 #pragma unroll
-          for (int g4 = 0; g4 < IA_G / 4; ++g4) {
-            const float4 a = *reinterpret_cast<const float4*>(pp + 4 * g4);
-            const float av[4] = {a.x, a.y, a.z, a.w};
-#pragma unroll
-            for (int gg = 0; gg < 4; ++gg) {
-              const int g = 4 * g4 + gg;
-              acc[g][0] = fmaf(av[gg], v.x, acc[g][0]); acc[g][1] = fmaf(av[gg], v.y, acc[g][1]);
-              acc[g][2] = fmaf(av[gg], v.z, acc[g][2]); acc[g][3] = fmaf(av[gg], v.w, acc[g][3]);
+            for (int g = 0; g < G; ++g) {
+              acc[g][0] = fmaf(av[g], v.x, acc[g][0]); acc[g][1] = fmaf(av[g], v.y, acc[g][1]);
+              acc[g][2] = fmaf(av[g], v.z, acc[g][2]); acc[g][3] = fmaf(av[g], v.w, acc[g][3]);
             }
           }
         }
       }
 #pragma unroll
-      for (int g = 0; g < IA_G; ++g)
+      for (int g = 0; g < G; ++g)
 #pragma unroll
         for (int e = 0; e < 4; ++e) {
           const float r = warp_sum(acc[g][e]);
@@ -620,7 +646,7 @@ __global__ void __launch_bounds__(IA_THREADS, 1) ipa_attention_tc_kernel(
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 2) tmem_dealloc(tmem, IA_G * 16);
+  if (warp == 2) tmem_dealloc(tmem, TCOLS);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -632,14 +658,16 @@ int tc_struct_init(gb_ctx* c) {
   cudaError_t e;
   if ((e = cudaFuncSetAttribute(gemm_img_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, GI_SMEM)) != cudaSuccess ||
       (e = cudaFuncSetAttribute(ipa_prep_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PREP_SMEM)) != cudaSuccess ||
-      (e = cudaFuncSetAttribute(ipa_attention_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, IA_SMEM)) != cudaSuccess)
+      (e = cudaFuncSetAttribute(ipa_attention_tc_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, ia_smem(8, 256).total)) != cudaSuccess ||
+      (e = cudaFuncSetAttribute(ipa_attention_tc_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, ia_smem(4, 512).total)) != cudaSuccess ||
+      (e = cudaFuncSetAttribute(ipa_attention_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, ia_smem(2, 1024).total)) != cudaSuccess)
     return gb_fail(c, GB_ERR_CUDA, "tc_struct_init: cudaFuncSetAttribute failed: %s", cudaGetErrorString(e));
   return GB_OK;
 }
 
 bool tc_struct_supported(const gb_ctx* c, int N) {
   const int cs = c->d.c_s;
-  return cs % 128 == 0 && cs <= 512 && N <= 256 && c->d.n_structure_layer * IPA_H <= 96;
+  return cs % 128 == 0 && cs <= 512 && N <= 1024 && c->d.n_structure_layer * IPA_H <= 96;
 }
 
 size_t tc_struct_workspace_bytes(const gb_ctx* c, int B, int N) {
@@ -723,12 +751,13 @@ int tc_pack_ipa_bias(gb_ctx* c, const std::vector<const std::vector<float>*>& wb
 }
 
 static int gemm_img(gb_ctx* c, cudaStream_t st, const bf16* A, int K, const bf16* W, int Nw, const float* bias, const float* res,
-                    int ldr, float* C, int ldc, bf16* O, bool relu, int kvsplit = 0) {
+                    int ldr, float* C, int ldc, bf16* O, bool relu, int kvsplit = 0, int mblk0 = 0, int nmblk = 0) {
   TcState* s = static_cast<TcState*>(c->tc_state);
   GemmImgArgs g;
+  g.mblk0 = mblk0;
   g.A = A; g.W = W; g.bias = bias; g.res = res; g.C = C; g.O = O;
   g.Rp = s->Rp; g.Nw = Nw; g.nkb = K / 64; g.R = c->B * c->N; g.ldc = ldc; g.ldr = ldr; g.relu = relu ? 1 : 0; g.kvsplit = kvsplit;
-  gemm_img_tc_kernel<<<dim3(Nw / 64, s->Rp / 128), 256, GI_SMEM, st>>>(g);
+  gemm_img_tc_kernel<<<dim3(Nw / 64, nmblk ? nmblk : s->Rp / 128), 256, GI_SMEM, st>>>(g);
   GB_LAUNCH_CHECK(c, "gemm_img_tc");
   return GB_OK;
 }
@@ -741,9 +770,14 @@ int tc_structure_net(gb_ctx* c, float* states_out, cudaStream_t st) {
   if (!Rp || (int)s->st.size() < d.n_structure_layer || !s->Wb_img) return gb_fail(c, GB_ERR_INVALID, "tc_structure_net: not bound");
   const size_t Rcs = (size_t)R * cs;
   int rc;
-  const unsigned ptiles = (unsigned)B * ((N + 1) / 2) * (Np / 64);
+  // row-sharded (B == 1): pair bias, z images, attention and the output projection for this rank's query rows only;
+  // the [N, c_s] result of every layer is all-gathered and the O(N) rest runs replicated
+  const int W = c->shard_world, rows = N / W, row0 = c->shard_rank * rows;
+  TileRange tr = full_tile_range(N, Np);
+  if (W > 1) { tr.nt2 = (uint32_t)rows >> 1; tr.t2_0 = (uint32_t)row0 >> 1; }
+  const unsigned ptiles = (unsigned)B * tr.nt2 * tr.njb;
   ipa_prep_tc_kernel<<<ptiles, 256, PREP_SMEM, st>>>(c->p, B, N, Np, c->mask, s->Wb_img, s->bias96, s->pbias, s->z_img,
-                                                     d.n_structure_layer * IPA_H);
+                                                     d.n_structure_layer * IPA_H, tr);
   GB_LAUNCH_CHECK(c, "ipa_prep_tc");
   const unsigned lnb = (unsigned)((R * 32 + 255) / 256);
   ln_img_kernel<<<lnb, 256, 0, st>>>(c->s, nullptr, nullptr, s->s_img, nullptr, nullptr, R, cs, Rp, 0);
@@ -756,10 +790,20 @@ int tc_structure_net(gb_ctx* c, float* states_out, cudaStream_t st) {
       if ((rc = gemm_img(c, st, s->s_img, cs, t.Wqkv, IPA_QKV, t.bqkv, nullptr, 0, c->qkv, IPA_QKV, nullptr, false, N))) return rc;
       ipa_points_planes_kernel<<<(R * IPA_H + 255) / 256, 256, 0, st>>>(c->qkv, c->rots_w, c->trans_w, R, N);
       GB_LAUNCH_CHECK(c, "ipa_points_planes");
-      ipa_attention_tc_kernel<<<dim3((N + IA_G - 1) / IA_G, B), IA_THREADS, IA_SMEM, st>>>(
-          c->qkv, s->pbias + (size_t)l * B * N * IPA_H * Np, s->z_img, c->rots_w, c->trans_w, w.hw, s->cat_img, N, Np, Rp);
+      {
+        const int G = ia_queries_per_cta(Np), nq = W > 1 ? rows : N;
+        const dim3 grid((nq + G - 1) / G, B);
+        const float* pb = s->pbias + (size_t)l * B * N * IPA_H * Np;
+        const size_t smem = ia_smem(G, Np).total;
+        if (G == 8) ipa_attention_tc_kernel<8><<<grid, IA_THREADS, smem, st>>>(c->qkv, pb, s->z_img, c->rots_w, c->trans_w, w.hw, s->cat_img, N, Np, Rp, row0);
+        else if (G == 4) ipa_attention_tc_kernel<4><<<grid, IA_THREADS, smem, st>>>(c->qkv, pb, s->z_img, c->rots_w, c->trans_w, w.hw, s->cat_img, N, Np, Rp, row0);
+        else ipa_attention_tc_kernel<2><<<grid, IA_THREADS, smem, st>>>(c->qkv, pb, s->z_img, c->rots_w, c->trans_w, w.hw, s->cat_img, N, Np, Rp, row0);
+      }
       GB_LAUNCH_CHECK(c, "ipa_attention_tc");
-      if ((rc = gemm_img(c, st, s->cat_img, IPA_CAT, t.Wout, cs, w.bout, c->s, cs, c->sA, cs, nullptr, false))) return rc;
+      if (W > 1) {
+        if ((rc = gemm_img(c, st, s->cat_img, IPA_CAT, t.Wout, cs, w.bout, c->s, cs, c->sA, cs, nullptr, false, 0, row0 / 128, rows / 128))) return rc;
+        if ((rc = shard_all_gather(c, c->sA, (size_t)rows * cs * sizeof(float), st))) return rc;
+      } else if ((rc = gemm_img(c, st, s->cat_img, IPA_CAT, t.Wout, cs, w.bout, c->s, cs, c->sA, cs, nullptr, false))) return rc;
       ln_img_kernel<<<lnb, 256, 0, st>>>(c->sA, c->sB, nullptr, s->ln1_img, w.ln1_g, w.ln1_b, R, cs, Rp, 1);
       GB_LAUNCH_CHECK(c, "ipa_layer_norm");
       float* cur = c->sB;
