@@ -38,6 +38,8 @@ def parse():
     ap.add_argument('--precision', default=os.environ.get('GB_BENCH_PRECISION', 'auto'))
     ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
     ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--workload', default='c2', choices=['c2', 'c5'],
+                    help="c2 (default, the contract's line): L=256 batch 4; c5: ONE L=1024 sample, row-sharded over the ranks")
     return ap.parse_args()
 
 
@@ -378,9 +380,97 @@ def run_b200(args):
         dist.destroy_process_group()
 
 
+def run_c5(args):
+    """BASELINE configs[4]: one unconditional L=1024 sample.  With N > 1 (torchrun) the pair representation is sharded
+    by rows over the ranks (csrc/shard.cu: NCCL all-gather / all-to-all of the triangle operands inside gb_denoise);
+    every rank holds the same x_t and the same noise, so this is STRONG scaling of one sample."""
+    import torch
+    import torch.distributed as dist
+    import genie2_b200
+    from genie2_b200 import _lib, shard
+    from oracle import genie_oracle as O, weights as W     # seeded weights / synthetic features (host side only)
+
+    world, rank, local = (int(os.environ.get(k, d)) for k, d in (('WORLD_SIZE', '1'), ('RANK', '0'), ('LOCAL_RANK', '0')))
+    torch.cuda.set_device(local)
+    dev = torch.device('cuda', local)
+    if world > 1:
+        dist.init_process_group('nccl', device_id=dev)
+    K = args.steps if args.steps is not None else 20
+    W_ = max(args.warmup if args.warmup is not None else 3, 3)
+    n = 1024
+    lib = _lib.load()
+    cfg = O.OracleConfig()
+    genie = genie2_b200.Genie(genie2_b200.Config())
+    genie.model.load_state_dict(W.make_state_dict(cfg, 0, 'activated'))
+    genie = genie.to(dev)
+    genie.setup_schedule()
+    genie.model.set_precision('bf16')
+    if world > 1:
+        shard.check_shardable(1, n, world)
+        genie.model.shard_rows()
+    feats = {k: v.to(dev) for k, v in O.make_features([[n]]).items()}
+    ctx = genie.model.bind_features(feats, dev)
+    genie.bind_schedule(ctx)
+    x = torch.randn(1, n, 3, generator=torch.Generator().manual_seed(1)).to(dev)     # same on every rank
+    rots = genie2_b200.compute_frenet_frames(genie.model, feats, x)
+    stream = torch.cuda.current_stream(dev).cuda_stream
+
+    def loop(t_start, cnt):
+        _lib.check(lib.gb_sample_loop(ctx, x.data_ptr(), rots.data_ptr(), t_start, t_start - cnt + 1, SCALE, None, 1234, stream),
+                   ctx, 'gb_sample_loop')
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    loop(T_STEPS, W_)
+    barrier()
+    clocks = ClockSampler(local)
+    l0, c0 = genie.model.launch_count(), genie.model.collective_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    loop(T_STEPS - W_, K)
+    e1.record()
+    barrier()
+    ms = torch.tensor([e0.elapsed_time(e1)], device=dev, dtype=torch.float64)
+    digest = x.double().sum().reshape(1)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        lo, hi = digest.clone(), digest.clone()
+        dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+        dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+        same = bool(lo == hi)
+    else:
+        same = True
+    clk = clocks.stop()
+    if rank == 0:
+        ms = float(ms)
+        fl = flops_per_eval(n, 1)
+        pk = peaks()
+        print(json.dumps({
+            'metric': 'denoiser evals/sec at L=1024 batch 1', 'value': K / (ms * 1e-3), 'unit': UNIT, 'n_gpus': world, 'steps': K,
+            'warmup': W_, 'ms_per_step': ms / K, 'higher_is_better': True, 'scaling': 'strong', 'vs_baseline': None, 'dtype': 'bf16',
+            'data': 'synthetic',
+            'config': {'workload': 'unconditional L=1024 batch 1, base config, scale 0.6 (BASELINE configs[4])',
+                       'parallelism': 'pair rows sharded over %d GPUs, NCCL all-gather / all-to-all' % world if world > 1 else 'single GPU',
+                       'weights': 'seeded activated random init'},
+            'seconds_per_1000_step_sample': ms / K,
+            'gpu_launches': int(genie.model.launch_count() - l0), 'collectives': int(genie.model.collective_count() - c0),
+            'recv_bytes_per_rank_per_step': shard.traffic_bytes(n, world), 'ranks_agree_bitwise': same,
+            'finite': bool(torch.isfinite(x).all()), 'clocks': clk,
+            'whole_eval': {'algorithmic_tflop_per_eval': fl / 1e12, 'achieved_tflops': fl / (ms / K * 1e-3) / 1e12,
+                           'frac_of_tensor_sustained': fl / (ms / K * 1e-3) / 1e12 / pk['tensor_sustained'] / world},
+        }), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
 if __name__ == '__main__':
     a = parse()
     if a.impl == 'reference':
         run_reference(a)
+    elif a.workload == 'c5':
+        run_c5(a)
     else:
         run_b200(a)

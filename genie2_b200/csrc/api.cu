@@ -2,6 +2,7 @@
 // the orchestration of Denoiser.forward / the reverse-diffusion step as a fixed kernel sequence.
 #include <stdarg.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <cmath>
@@ -461,6 +462,13 @@ extern "C" int gb_set_features(gb_ctx* c, const gb_features* f) {
       return gb_fail(c, GB_ERR_CUDA, "workspace allocation of %zu bytes failed: %s", kw.off + tcb, cudaGetErrorString(e));
     }
     c->ws_bytes = kf.off + kw.off + tcb + 768;
+    // GB_DEBUG_POISON=1: fill the fresh workspace with NaN patterns so that any read of a never-written location shows
+    // up in the parity tests (cudaMalloc does not promise zeroed memory)
+    if (const char* env = getenv("GB_DEBUG_POISON"))
+      if (env[0] == '1') {
+        GB_CUDA(c, cudaMemset(c->ws_alloc, 0xFF, kw.off + 512 + tcb));
+        GB_CUDA(c, cudaMemset(c->feat_alloc, 0xFF, kf.off + 256));
+      }
     Carver kf2{(char*)c->feat_alloc}, kw2{(char*)c->ws_alloc};
     carve_features(c, kf2, B, N);
     carve_workspace(c, kw2, B, N);

@@ -5,7 +5,7 @@
 //   pair embedding, K4 / K5 / K6 of both triangle updates, the pair transition, the IPA attention and
 //   its output projection.  What is exchanged:
 //     outgoing update   all-gather of the b operand image      (bf16, N^2 * 128 * 2 bytes in total)
-//     incoming update   all-gather of the a and b images       (2 x that)
+//     incoming update   all-gather of b, all-to-all of a       ((1 + 1 / world) x that)
 //     each IPA layer    all-gather of the [N, c_s] fp32 result (1.5 MB at N = 1024)
 //   p itself never moves (only when the caller asks for aux.p).  The operand images are laid out so that
 //   each rank's contribution is one contiguous block (tc_common.cuh, ImgLayout), hence plain in-place
@@ -34,6 +34,10 @@ struct NcclApi {
   ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
   ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
   ncclResult_t (*AllGather)(const void*, void*, size_t, int, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*Send)(const void*, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*Recv)(void*, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*GroupStart)() = nullptr;
+  ncclResult_t (*GroupEnd)() = nullptr;
   const char* (*GetErrorString)(ncclResult_t) = nullptr;
   ncclResult_t (*GetVersion)(int*) = nullptr;
 };
@@ -51,9 +55,14 @@ const char* load_nccl() {
   a.CommInitRank = (decltype(a.CommInitRank))dlsym(h, "ncclCommInitRank");
   a.CommDestroy = (decltype(a.CommDestroy))dlsym(h, "ncclCommDestroy");
   a.AllGather = (decltype(a.AllGather))dlsym(h, "ncclAllGather");
+  a.Send = (decltype(a.Send))dlsym(h, "ncclSend");
+  a.Recv = (decltype(a.Recv))dlsym(h, "ncclRecv");
+  a.GroupStart = (decltype(a.GroupStart))dlsym(h, "ncclGroupStart");
+  a.GroupEnd = (decltype(a.GroupEnd))dlsym(h, "ncclGroupEnd");
   a.GetErrorString = (decltype(a.GetErrorString))dlsym(h, "ncclGetErrorString");
   a.GetVersion = (decltype(a.GetVersion))dlsym(h, "ncclGetVersion");
-  if (!a.GetUniqueId || !a.CommInitRank || !a.CommDestroy || !a.AllGather || !a.GetErrorString) return "libnccl: missing symbols";
+  if (!a.GetUniqueId || !a.CommInitRank || !a.CommDestroy || !a.AllGather || !a.GetErrorString || !a.Send || !a.Recv || !a.GroupStart ||
+      !a.GroupEnd) return "libnccl: missing symbols";
   g_nccl = a;
   return nullptr;
 }
@@ -110,6 +119,25 @@ int shard_all_gather(gb_ctx* c, void* base, size_t piece_bytes, cudaStream_t st)
   const ncclResult_t r = g_nccl.AllGather((const char*)base + (size_t)c->shard_rank * piece_bytes, base, piece_bytes, ncclUint8,
                                           (ncclComm_t)c->shard_comm, st);
   if (r != 0) return gb_fail(c, GB_ERR_CUDA, "ncclAllGather: %s", g_nccl.GetErrorString(r));
+  c->collectives++;
+  return GB_OK;
+}
+
+int shard_all_to_all(gb_ctx* c, void* base, size_t block_bytes, cudaStream_t st) {
+  const int W = c->shard_world, me = c->shard_rank;
+  if (W <= 1) return GB_OK;
+  if (!c->shard_comm) return gb_fail(c, GB_ERR_INVALID, "shard_all_to_all: no communicator");
+  ncclComm_t comm = (ncclComm_t)c->shard_comm;
+  char* b = (char*)base;
+  ncclResult_t r = g_nccl.GroupStart();
+  for (int peer = 0; peer < W && r == 0; ++peer) {
+    if (peer == me) continue;
+    r = g_nccl.Send(b + ((size_t)peer * W + me) * block_bytes, block_bytes, ncclUint8, peer, comm, st);
+    if (r == 0) r = g_nccl.Recv(b + ((size_t)me * W + peer) * block_bytes, block_bytes, ncclUint8, peer, comm, st);
+  }
+  const ncclResult_t e = g_nccl.GroupEnd();
+  if (r == 0) r = e;
+  if (r != 0) return gb_fail(c, GB_ERR_CUDA, "all-to-all (ncclSend / ncclRecv): %s", g_nccl.GetErrorString(r));
   c->collectives++;
   return GB_OK;
 }

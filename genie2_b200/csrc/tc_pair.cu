@@ -127,7 +127,7 @@ __device__ __forceinline__ void tmem_to_stage(uint8_t* S, uint32_t taddr, uint32
 
 __global__ void __launch_bounds__(256, 2) trimul_contract_tc_kernel(const bf16* __restrict__ a, const bf16* __restrict__ b,
                                                                     bf16* __restrict__ x, int N, int Np, int NJ,
-                                                                    const ImgLayout L, int ib0, int nib) {
+                                                                    const ImgLayout La, const ImgLayout Lb, int ib0, int nib) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* sm = smem_base_1024(smem_raw);
   uint64_t* full = reinterpret_cast<uint64_t*>(sm + K5_STAGES * K5_STAGE_BYTES);
@@ -141,7 +141,7 @@ __global__ void __launch_bounds__(256, 2) trimul_contract_tc_kernel(const bf16* 
   const uint32_t ib = ib0 + blk % nib; blk /= nib;  // blk = b * 128 + c; a row-sharded launch owns row blocks [ib0, ib0 + nib)
   const uint32_t nj = min((uint32_t)NJ, (uint32_t)Np - jb * NJ);   // columns of this block (multiple of 64)
   const uint32_t bb = blk >> 7, cch = blk & 127;
-  const uint32_t bpiece = (L.RL % nj == 0) ? nj : 128u;            // B rows that are contiguous in the (possibly row-split) image
+  const uint32_t bpiece = (Lb.RL % nj == 0) ? nj : 128u;            // B rows that are contiguous in the (possibly row-split) image
   const uint32_t a_rows = min(128u, (uint32_t)Np - ib * 128u);      // rows present in the plane (64 or 128)
 
   if (tid == 0) {
@@ -162,9 +162,9 @@ __global__ void __launch_bounds__(256, 2) trimul_contract_tc_kernel(const bf16* 
         if (kb >= K5_STAGES) mbar_wait(empty + s, ((kb / K5_STAGES) - 1) & 1);
         uint8_t* st = sm + s * K5_STAGE_BYTES;
         mbar_expect_tx(full + s, (a_rows + nj) * 128u);
-        bulk_g2s(st, a + img_off(L, bb, cch, kb, ib * 128u), a_rows * 128u, full + s);
+        bulk_g2s(st, a + img_off(La, bb, cch, kb, ib * 128u), a_rows * 128u, full + s);
         for (uint32_t r = 0; r < nj; r += bpiece)
-          bulk_g2s(st + 16384 + r * 128u, b + img_off(L, bb, cch, kb, jb * NJ + r), min(bpiece, nj - r) * 128u, full + s);
+          bulk_g2s(st + 16384 + r * 128u, b + img_off(Lb, bb, cch, kb, jb * NJ + r), min(bpiece, nj - r) * 128u, full + s);
       }
     }
     __syncwarp();
@@ -446,20 +446,22 @@ int tc_trimul_stage(gb_ctx* c, const TriMulW& w, bool outgoing, int stage, float
     int rc = tc_launch_trimul_proj(c, w, outgoing, p, st);
     if (rc != GB_OK) return rc;
     if (W > 1) {
-      // each rank wrote its block of the operand images; K5 needs every row of b (and, for the incoming
-      // update, every k-block of a as well): in-place all-gather over NVLink
+      // each rank wrote its block of the operand images.  K5 needs every row of b: in-place all-gather over NVLink.
+      // For the incoming update it also needs its own rows of a for every k: a is a W x W grid of blocks
+      // (destination row block, source k block) and block (d, s) travels from rank s to rank d: in-place all-to-all.
       const size_t piece = (size_t)B * 128 * Np * Np * 2 / W;
-      if (!outgoing && (rc = shard_all_gather(c, s->a, piece, st)) != GB_OK) return rc;
+      if (!outgoing && (rc = shard_all_to_all(c, s->a, piece / W, st)) != GB_OK) return rc;
       if ((rc = shard_all_gather(c, s->b, piece, st)) != GB_OK) return rc;
     }
   }
   if (stage == 0 || stage == 2) {
     const int NJ = 256;
     // sharded: both operand images are complete after the all-gather; this rank contracts its own 128-row blocks
-    const ImgLayout L = W > 1 ? (outgoing ? img_layout(B, Np, W, 1) : img_layout(B, Np, 1, W)) : img_layout(B, Np, 1, 1);
+    const ImgLayout Lb = W > 1 ? (outgoing ? img_layout(B, Np, W, 1) : img_layout(B, Np, 1, W)) : img_layout(B, Np, 1, 1);
+    const ImgLayout La = W > 1 && !outgoing ? img_layout(B, Np, W, W) : Lb;
     const int nib = W > 1 ? (N / W) / 128 : (Np + 127) / 128, ib0 = W > 1 ? c->shard_rank * nib : 0;
     const unsigned cgrid = (unsigned)B * 128 * nib * ((Np + NJ - 1) / NJ);
-    trimul_contract_tc_kernel<<<cgrid, 256, K5_SMEM, st>>>(s->a, s->b, s->x, N, Np, NJ, L, ib0, nib);
+    trimul_contract_tc_kernel<<<cgrid, 256, K5_SMEM, st>>>(s->a, s->b, s->x, N, Np, NJ, La, Lb, ib0, nib);
     GB_LAUNCH_CHECK(c, "trimul_contract_tc");
   }
   if (stage == 0 || stage == 3) {

@@ -56,7 +56,7 @@ __device__ __forceinline__ void k4_mma_T64(uint32_t tmem_d, uint32_t w_rows, uin
 __global__ void __launch_bounds__(K4_THREADS, 1) trimul_proj_tc_kernel(
     const float* __restrict__ p, int N, int Np, int ntiles, const int* __restrict__ rmask, const bf16* __restrict__ Wimg,
     const float* __restrict__ bias, bf16* __restrict__ a_out, bf16* __restrict__ b_out, bf16* __restrict__ g_out, int incoming,
-    const TileRange tr, const ImgLayout L) {
+    const TileRange tr, const ImgLayout La, const ImgLayout Lb) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* sm = smem_base_1024(smem_raw);
   uint8_t* W = sm;                       // g weight image 32K (a / b weights live in tensor memory)
@@ -222,9 +222,8 @@ __global__ void __launch_bounds__(K4_THREADS, 1) trimul_proj_tc_kernel(
     for (int it = 0; it < my_tiles; ++it) {
       const PixTile T = pix_tile(blockIdx.x + it * gridDim.x, tr);
       const float* cm = cmask + (it % 3) * 64 + c2 * 32;
-      const size_t img0 = img_off(L, T.b, ch, T.jb, 2 * T.t2);
-      uint8_t* const dst_a = reinterpret_cast<uint8_t*>(a_out + img0);
-      uint8_t* const dst_b = reinterpret_cast<uint8_t*>(b_out + img0);
+      uint8_t* const dst_a = reinterpret_cast<uint8_t*>(a_out + img_off(La, T.b, ch, T.jb, 2 * T.t2));
+      uint8_t* const dst_b = reinterpret_cast<uint8_t*>(b_out + img_off(Lb, T.b, ch, T.jb, 2 * T.t2));
       mbar_wait(full_x + (it & 1), (it >> 1) & 1);      // orders the producers' mask writes before our reads
       const bool cols_on = cfull[(it % 3) * 2 + c2] != 0.f;
       const float rm0 = rowm[(it % 3) * 2], rm1 = rowm[(it % 3) * 2 + 1];
@@ -353,17 +352,17 @@ int tc_launch_trimul_proj(gb_ctx* c, const TriMulW& w, bool outgoing, const floa
   TcState* s = static_cast<TcState*>(c->tc_state);
   const int B = c->B, N = c->N, Np = s->Np, W = c->shard_world;
   TileRange tr = full_tile_range(N, Np);
-  ImgLayout L = img_layout(B, Np, 1, 1);
+  ImgLayout La = img_layout(B, Np, 1, 1), Lb = La;
   if (W > 1) {
     // this rank's rows of p: image rows [r0, r0 + RB) (outgoing) or k-blocks [r0 / 64, ...) of every image row (incoming)
     const uint32_t RB = (uint32_t)N / W, r0 = c->shard_rank * RB;
-    if (outgoing) { tr = TileRange{r0 >> 1, RB >> 1, 0u, (uint32_t)Np >> 6}; L = img_layout(B, Np, W, 1); }
-    else { tr = TileRange{0u, (uint32_t)(N + 1) >> 1, r0 >> 6, RB >> 6}; L = img_layout(B, Np, 1, W); }
+    if (outgoing) { tr = TileRange{r0 >> 1, RB >> 1, 0u, (uint32_t)Np >> 6}; La = Lb = img_layout(B, Np, W, 1); }
+    else { tr = TileRange{0u, (uint32_t)(N + 1) >> 1, r0 >> 6, RB >> 6}; La = img_layout(B, Np, W, W); Lb = img_layout(B, Np, 1, W); }
   }
   const int tiles = B * (int)(tr.nt2 * tr.njb);
   const int grid = tiles < s->num_sms ? tiles : s->num_sms;
   trimul_proj_tc_kernel<<<grid, K4_THREADS, K4_SMEM, st>>>(p, N, Np, tiles, c->mask, (const bf16*)w.tc_Wproj, w.tc_bproj, s->a, s->b,
-                                                           s->g, outgoing ? 0 : 1, tr, L);
+                                                           s->g, outgoing ? 0 : 1, tr, La, Lb);
   GB_LAUNCH_CHECK(c, "trimul_proj_tc");
   return GB_OK;
 }

@@ -34,13 +34,15 @@ def check_shardable(B, N, world):
 
 
 def traffic_bytes(N, world, n_pair_layer=5, n_struct_layer=8, c_p=128, c_s=384):
-    """Bytes RECEIVED per rank per denoiser eval: per pair layer one bf16 image for the outgoing update and
-    two for the incoming one, per structure layer the fp32 single representation."""
+    """Bytes RECEIVED per rank per denoiser eval: per pair layer the bf16 b image of the outgoing update, the b
+    image of the incoming one (all-gathers) and this rank's rows of the incoming a image (all-to-all); per
+    structure layer the fp32 single representation."""
     if world == 1:
         return 0
     image = N * N * c_p * 2
-    per_eval = n_pair_layer * 3 * image + n_struct_layer * N * c_s * 4
-    return per_eval * (world - 1) // world
+    gathered = n_pair_layer * 2 * image + n_struct_layer * N * c_s * 4       # all-gathers: (world - 1) / world of it arrives
+    exchanged = n_pair_layer * image // world                                # all-to-all of a: this rank's row block
+    return (gathered + exchanged) * (world - 1) // world
 
 
 def _draw_unique_id():

@@ -28,7 +28,7 @@ def test_row_ranges_and_rules():
         shard.check_shardable(1, 768, 4)             # 192 rows per rank: not whole 128-row blocks
     assert shard.traffic_bytes(1024, 1) == 0
     img = 1024 * 1024 * 128 * 2
-    assert shard.traffic_bytes(1024, 8) == (5 * 3 * img + 8 * 1024 * 384 * 4) * 7 // 8
+    assert shard.traffic_bytes(1024, 8) == (5 * 2 * img + 8 * 1024 * 384 * 4 + 5 * img // 8) * 7 // 8
 
 
 def img_off(Np, B, row_split, k_split, b, ch, kb, row):
@@ -63,6 +63,26 @@ def test_image_layout_is_a_partition(world, mode):
     for row0 in range(0, Np, 128):
         a = img_off(Np, B, rs, ks, 0, 9, 1, row0)
         assert img_off(Np, B, rs, ks, 0, 9, 1, row0 + 127) == a + 127 * 64
+
+
+@pytest.mark.parametrize('world', [2, 4])
+def test_incoming_a_image_is_a_block_grid(world):
+    """Incoming update: a is cut by destination row block AND source k block; rank s writes column s of the
+    world x world block grid, the in-place all-to-all moves block (d, s) to rank d, whose contraction then reads
+    row d only (csrc/shard.cu, shard_all_to_all)."""
+    Np, B = 128 * world, 1
+    blk = B * 128 * ((Np // 64) // world) * (Np // world) * 64
+    for src in range(world):                                      # writer: k blocks of rank src, every image row
+        for kb in range(src * (Np // 64) // world, (src + 1) * (Np // 64) // world):
+            for row in (0, Np // world - 1, Np // world, Np - 1):
+                off = img_off(Np, B, world, world, 0, 17, kb, row)
+                d = row // (Np // world)
+                assert (d * world + src) * blk <= off < (d * world + src + 1) * blk
+    for dst in range(world):                                      # reader: its own rows, every k block
+        lo, hi = dst * world * blk, (dst + 1) * world * blk
+        for kb in range(Np // 64):
+            for row in range(dst * Np // world, (dst + 1) * Np // world, 37):
+                assert lo <= img_off(Np, B, world, world, 0, 3, kb, row) < hi
 
 
 def _free_port():
