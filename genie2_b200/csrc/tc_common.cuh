@@ -235,6 +235,14 @@ __device__ __forceinline__ uint8_t* smem_base_1024(uint8_t* raw) {
 // Pixel tile of the triangle / IPA-prep kernels: 128 pixels = 2 consecutive rows x 64 consecutive
 // columns of one sample's N x N pair map; tile-local pixel m = 64 * ii + jj,
 // row = 2 * t2 + ii, col = 64 * jb + jj.
+// Programmatic dependent launch.  Every kernel of the chain runs its prologue (barriers, tensor-memory allocation,
+// weight prefetch: nothing the previous kernel writes), then pdl_wait() -- the previous grid has completed and its
+// writes are visible -- then pdl_launch(), which lets the NEXT kernel start its own prologue while this one computes.
+// Wait-then-launch keeps at most one waiting grid resident and makes everything older than the previous grid
+// complete before a kernel starts (so a prologue may read data produced two or more launches back).
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 struct PixTile { uint32_t b, t2, jb; };
 __device__ __forceinline__ PixTile pix_tile(uint32_t blk, int N, int Np) {
   const uint32_t njb = Np >> 6, nt2 = (N + 1) >> 1;

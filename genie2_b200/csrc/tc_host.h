@@ -1,5 +1,6 @@
 // Host-side helpers of the tensor-core modules: bf16 rounding and operand tile-image packing.
 #pragma once
+#include <stdlib.h>
 #include <string.h>
 
 #include "ctx.h"
@@ -31,3 +32,28 @@ static void* upload_bytes(gb_ctx* c, const void* src, size_t bytes) {
   return p;
 }
 
+
+// Launch with the programmatic-stream-serialization attribute: the kernel may start while its predecessor in the
+// stream is still running and synchronises with it through tc::pdl_wait().  Only for kernels that call pdl_wait()
+// before touching anything the predecessor writes or reads.  GB_NO_PDL=1 turns the attribute off (plain stream order).
+template <typename... KArgs, typename... Args>
+static inline void launch_pdl_cls(int cls, void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
+  static const int mask = [] { const char* e = getenv("GB_PDL_MASK"); return e ? atoi(e) : 0xff; }();
+  const bool off = !((mask >> cls) & 1);
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = off ? 0 : 1;
+  cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);   // errors surface through cudaGetLastError in GB_LAUNCH_CHECK
+}
+
+template <typename... KArgs, typename... Args>
+static inline void launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
+  launch_pdl_cls(0, kern, grid, block, smem, st, static_cast<Args&&>(args)...);
+}

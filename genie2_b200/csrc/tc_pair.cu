@@ -154,6 +154,8 @@ __global__ void __launch_bounds__(256, 2) trimul_contract_tc_kernel(const bf16* 
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *tslot;
+  pdl_wait();
+  pdl_launch();
 
   if (warp == 0) {
     if (lane == 0) {
@@ -253,7 +255,6 @@ __global__ void __launch_bounds__(256, 3) trimul_out_tc_kernel(
     mbar_init(bar_mma, 1);
     fence_mbar_init();
     mbar_expect_tx(bar_w, 65536);
-    bulk_g2s(X, x + (((size_t)T.b * (Np >> 1) + T.t2) * (Np >> 6) + T.jb) * 16384, 32768, bar_w);
     bulk_g2s(W, Wzimg, 32768, bar_w);
   }
   if (warp == 1) tmem_alloc(tslot, 128);
@@ -261,6 +262,9 @@ __global__ void __launch_bounds__(256, 3) trimul_out_tc_kernel(
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *tslot;
+  pdl_wait();            // x comes from the contraction kernel
+  pdl_launch();
+  if (tid == 0) bulk_g2s(X, x + (((size_t)T.b * (Np >> 1) + T.t2) * (Np >> 6) + T.jb) * 16384, 32768, bar_w);
   if (tid == 0) {
     mbar_wait(bar_w, 0);
     tc_fence_after();
@@ -461,14 +465,14 @@ int tc_trimul_stage(gb_ctx* c, const TriMulW& w, bool outgoing, int stage, float
     const ImgLayout La = W > 1 && !outgoing ? img_layout(B, Np, W, W) : Lb;
     const int nib = W > 1 ? (N / W) / 128 : (Np + 127) / 128, ib0 = W > 1 ? c->shard_rank * nib : 0;
     const unsigned cgrid = (unsigned)B * 128 * nib * ((Np + NJ - 1) / NJ);
-    trimul_contract_tc_kernel<<<cgrid, 256, K5_SMEM, st>>>(s->a, s->b, s->x, N, Np, NJ, La, Lb, ib0, nib);
+    launch_pdl_cls(2, trimul_contract_tc_kernel, cgrid, 256, K5_SMEM, st, s->a, s->b, s->x, N, Np, NJ, La, Lb, ib0, nib);
     GB_LAUNCH_CHECK(c, "trimul_contract_tc");
   }
   if (stage == 0 || stage == 3) {
     TileRange tr = full_tile_range(N, Np);
     if (W > 1) { tr.nt2 = (uint32_t)(N / W) >> 1; tr.t2_0 = c->shard_rank * tr.nt2; }
     const unsigned tiles = (unsigned)B * tr.nt2 * tr.njb;
-    trimul_out_tc_kernel<<<tiles, 256, K6_SMEM, st>>>(s->x, s->g, p, N, Np, (const bf16*)w.tc_Wz, w.tc_uv, w.tc_uv + 128, tr);
+    launch_pdl_cls(3, trimul_out_tc_kernel, tiles, 256, K6_SMEM, st, s->x, s->g, p, N, Np, (const bf16*)w.tc_Wz, w.tc_uv, w.tc_uv + 128, tr);
     GB_LAUNCH_CHECK(c, "trimul_out_tc");
   }
   return GB_OK;

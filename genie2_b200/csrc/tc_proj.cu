@@ -108,6 +108,8 @@ __global__ void __launch_bounds__(K4_THREADS, 1) trimul_proj_tc_kernel(
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  pdl_wait();            // weights are in tensor memory; from here on p is read and the images are written
+  pdl_launch();
   const int my_tiles = (ntiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
 
   if (warp == 16) {
@@ -361,6 +363,9 @@ int tc_launch_trimul_proj(gb_ctx* c, const TriMulW& w, bool outgoing, const floa
   }
   const int tiles = B * (int)(tr.nt2 * tr.njb);
   const int grid = tiles < s->num_sms ? tiles : s->num_sms;
+  // plain stream order for this one: launched with the programmatic-serialization attribute it runs 16 us SLOWER per
+  // launch (measured, also with the wait at the very top of the kernel); its pdl_wait / pdl_launch are then no-ops
+  // for itself but pdl_launch still lets the contraction kernel start early
   trimul_proj_tc_kernel<<<grid, K4_THREADS, K4_SMEM, st>>>(p, N, Np, tiles, c->mask, (const bf16*)w.tc_Wproj, w.tc_bproj, s->a, s->b,
                                                            s->g, outgoing ? 0 : 1, tr, La, Lb);
   GB_LAUNCH_CHECK(c, "trimul_proj_tc");

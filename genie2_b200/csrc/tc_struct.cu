@@ -63,13 +63,23 @@ __global__ void __launch_bounds__(256, 1) gemm_img_tc_kernel(const GemmImgArgs g
   const uint32_t tmem = *tslot;
   if (warp == 0) {
     if (lane == 0) {
+      // the weight halves of the first ring of stages do not depend on the previous kernel: in flight before pdl_wait
+      const int npre = g.nkb < GI_STAGES ? g.nkb : GI_STAGES;
+      for (int kb = 0; kb < npre; ++kb) {
+        mbar_expect_tx(full + kb, GI_STAGE_BYTES);
+        bulk_g2s(sm + kb * GI_STAGE_BYTES + 16384, g.W + ((size_t)kb * g.Nw + n0) * 64, 8192, full + kb);
+      }
+      pdl_wait();
+      pdl_launch();
       for (int kb = 0; kb < g.nkb; ++kb) {
         const int s = kb % GI_STAGES;
-        if (kb >= GI_STAGES) mbar_wait(empty + s, ((kb / GI_STAGES) - 1) & 1);
         uint8_t* st = sm + s * GI_STAGE_BYTES;
-        mbar_expect_tx(full + s, GI_STAGE_BYTES);
+        if (kb >= GI_STAGES) {
+          mbar_wait(empty + s, ((kb / GI_STAGES) - 1) & 1);
+          mbar_expect_tx(full + s, GI_STAGE_BYTES);
+          bulk_g2s(st + 16384, g.W + ((size_t)kb * g.Nw + n0) * 64, 8192, full + s);
+        }
         bulk_g2s(st, g.A + ((size_t)kb * g.Rp + m0) * 64, 16384, full + s);
-        bulk_g2s(st + 16384, g.W + ((size_t)kb * g.Nw + n0) * 64, 8192, full + s);
       }
     }
     __syncwarp();
@@ -89,6 +99,7 @@ __global__ void __launch_bounds__(256, 1) gemm_img_tc_kernel(const GemmImgArgs g
       __syncwarp();
     }
   }
+  pdl_wait();        // (the residual read and the output writes of the epilogue; the loader thread has already waited)
   mbar_wait(done, 0);
   tc_fence_after();
   __syncwarp();
@@ -148,8 +159,12 @@ __global__ void __launch_bounds__(256, 1) gemm_img_tc_kernel(const GemmImgArgs g
 // ---------------------------------------------------------------------------------------------
 __global__ void ln_img_kernel(const float* __restrict__ in, float* __restrict__ out, float* __restrict__ out2,
                               bf16* __restrict__ img, const float* __restrict__ gamma, const float* __restrict__ beta,
-                              int R, int C, int Rp, int normalize) {
+                              int R, int C, int Rp, int normalize, const float* __restrict__ Wbb = nullptr,
+                              const float* __restrict__ bbb = nullptr, float* __restrict__ rots = nullptr,
+                              float* __restrict__ trans = nullptr) {
   const int row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  pdl_wait();
+  pdl_launch();
   if (row >= R) return;
   const int nq = C >> 7;
   float4 v[4];
@@ -191,6 +206,41 @@ __global__ void ln_img_kernel(const float* __restrict__ in, float* __restrict__ 
       *reinterpret_cast<uint2*>(dst + (((uint32_t)((c & 63) >> 3) ^ (row & 7u)) << 4) + ((c & 7) >> 2) * 8) = o;
     }
   }
+  if (Wbb) {
+    // BackboneUpdate of this row on the row just written (backbone_update.py:40-66, affine_utils.py:109-116): the warp
+    // already holds it in registers, so the separate kernel (one more pass over s and one more launch) is folded in
+    float acc[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      if (q >= nq) break;
+      const int c = (q * 32 + lane) * 4;
+#pragma unroll
+      for (int o = 0; o < 6; ++o) {
+        const float4 w4 = ld4(Wbb + o * C + c);
+        acc[o] = fmaf(v[q].x, w4.x, acc[o]); acc[o] = fmaf(v[q].y, w4.y, acc[o]);
+        acc[o] = fmaf(v[q].z, w4.z, acc[o]); acc[o] = fmaf(v[q].w, w4.w, acc[o]);
+      }
+    }
+#pragma unroll
+    for (int o = 0; o < 6; ++o) acc[o] = warp_sum(acc[o]) + bbb[o];
+    if (lane == 0) {
+      const float denom = sqrtf(acc[0] * acc[0] + acc[1] * acc[1] + acc[2] * acc[2] + 1.f);
+      float ru[9], r1[9], rn[9];
+      quat_to_rot(1.f / denom, acc[0] / denom, acc[1] / denom, acc[2] / denom, ru);
+      float* Rm = rots + (size_t)row * 9;
+      float* Tm = trans + (size_t)row * 3;
+#pragma unroll
+      for (int e = 0; e < 9; ++e) r1[e] = Rm[e];
+      mat3_mul(r1, ru, rn);
+      const float tx = acc[3], ty = acc[4], tz = acc[5];
+      const float nt0 = r1[0] * tx + r1[1] * ty + r1[2] * tz + Tm[0];
+      const float nt1 = r1[3] * tx + r1[4] * ty + r1[5] * tz + Tm[1];
+      const float nt2 = r1[6] * tx + r1[7] * ty + r1[8] * tz + Tm[2];
+#pragma unroll
+      for (int e = 0; e < 9; ++e) Rm[e] = rn[e];
+      Tm[0] = nt0; Tm[1] = nt1; Tm[2] = nt2;
+    }
+  }
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -225,6 +275,7 @@ __global__ void __launch_bounds__(256, 2) ipa_prep_tc_kernel(const float* __rest
     bulk_g2s(W, Wimg, 24576, bar_w);
   }
   if (warp == 1) tmem_alloc(tslot, 128);
+  pdl_wait();            // p comes from the last pair-transition kernel
   {
     const uint32_t kb = lane >> 4, chunk = (lane & 15) >> 1, half = lane & 1;
 #pragma unroll
@@ -257,6 +308,7 @@ __global__ void __launch_bounds__(256, 2) ipa_prep_tc_kernel(const float* __rest
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *tslot;
+  pdl_launch();
   if (tid == 0) {
     mbar_wait(bar_w, 0);
     tc_fence_after();
@@ -298,6 +350,8 @@ __global__ void __launch_bounds__(256, 2) ipa_prep_tc_kernel(const float* __rest
 __global__ void ipa_points_planes_kernel(float* __restrict__ qkv, const float* __restrict__ rots, const float* __restrict__ trans,
                                          int R, int N) {
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  pdl_wait();
+  pdl_launch();
   if (idx >= R * IPA_H) return;
   const int row = idx / IPA_H, h = idx - row * IPA_H, b = row / N, j = row - b * N;
   const float* Rm = rots + (size_t)row * 9;
@@ -437,6 +491,7 @@ __global__ void __launch_bounds__(IA_THREADS, 1) ipa_attention_tc_kernel(
     }
   }
   if (warp == 2) tmem_alloc(tslot, TCOLS);
+  pdl_wait();          // the z prefetch above reads what ipa_prep wrote (several launches back); q / k / v come from the previous kernel
   // q, q_pts of the G queries; a_img cleared (rows 12..15 and padded keys must read as zero)
   const float sc_qk = sqrtf(1.f / (3.f * IPA_C));
   for (int e = tid; e < G * 12 * 28; e += IA_THREADS) {
@@ -458,6 +513,7 @@ __global__ void __launch_bounds__(IA_THREADS, 1) ipa_attention_tc_kernel(
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *tslot;
+  pdl_launch();        // after the tensor-memory allocation: a dependent CTA on this SM can no longer get in its way
 
   // ---- 1. logits: thread (j mod 256, head group); keys in blocks of 256
   {
@@ -757,7 +813,7 @@ static int gemm_img(gb_ctx* c, cudaStream_t st, const bf16* A, int K, const bf16
   g.mblk0 = mblk0;
   g.A = A; g.W = W; g.bias = bias; g.res = res; g.C = C; g.O = O;
   g.Rp = s->Rp; g.Nw = Nw; g.nkb = K / 64; g.R = c->B * c->N; g.ldc = ldc; g.ldr = ldr; g.relu = relu ? 1 : 0; g.kvsplit = kvsplit;
-  gemm_img_tc_kernel<<<dim3(Nw / 64, nmblk ? nmblk : s->Rp / 128), 256, GI_SMEM, st>>>(g);
+  launch_pdl(gemm_img_tc_kernel, dim3(Nw / 64, nmblk ? nmblk : s->Rp / 128), 256, GI_SMEM, st, g);
   GB_LAUNCH_CHECK(c, "gemm_img_tc");
   return GB_OK;
 }
@@ -776,11 +832,11 @@ int tc_structure_net(gb_ctx* c, float* states_out, cudaStream_t st) {
   TileRange tr = full_tile_range(N, Np);
   if (W > 1) { tr.nt2 = (uint32_t)rows >> 1; tr.t2_0 = (uint32_t)row0 >> 1; }
   const unsigned ptiles = (unsigned)B * tr.nt2 * tr.njb;
-  ipa_prep_tc_kernel<<<ptiles, 256, PREP_SMEM, st>>>(c->p, B, N, Np, c->mask, s->Wb_img, s->bias96, s->pbias, s->z_img,
+  launch_pdl_cls(5, ipa_prep_tc_kernel, ptiles, 256, PREP_SMEM, st, c->p, B, N, Np, c->mask, s->Wb_img, s->bias96, s->pbias, s->z_img,
                                                      d.n_structure_layer * IPA_H, tr);
   GB_LAUNCH_CHECK(c, "ipa_prep_tc");
   const unsigned lnb = (unsigned)((R * 32 + 255) / 256);
-  ln_img_kernel<<<lnb, 256, 0, st>>>(c->s, nullptr, nullptr, s->s_img, nullptr, nullptr, R, cs, Rp, 0);
+  launch_pdl(ln_img_kernel, lnb, 256, 0, st, c->s, nullptr, nullptr, s->s_img, nullptr, nullptr, R, cs, Rp, 0, nullptr, nullptr, nullptr, nullptr);
   GB_LAUNCH_CHECK(c, "s_to_img");
   int state_idx = 1;
   for (int blk = 0; blk < d.n_structure_block; ++blk)
@@ -788,29 +844,29 @@ int tc_structure_net(gb_ctx* c, float* states_out, cudaStream_t st) {
       const StructLayerW& w = c->st[l];
       const TcStructW& t = s->st[l];
       if ((rc = gemm_img(c, st, s->s_img, cs, t.Wqkv, IPA_QKV, t.bqkv, nullptr, 0, c->qkv, IPA_QKV, nullptr, false, N))) return rc;
-      ipa_points_planes_kernel<<<(R * IPA_H + 255) / 256, 256, 0, st>>>(c->qkv, c->rots_w, c->trans_w, R, N);
+      launch_pdl(ipa_points_planes_kernel, (R * IPA_H + 255) / 256, 256, 0, st, c->qkv, c->rots_w, c->trans_w, R, N);
       GB_LAUNCH_CHECK(c, "ipa_points_planes");
       {
         const int G = ia_queries_per_cta(Np), nq = W > 1 ? rows : N;
         const dim3 grid((nq + G - 1) / G, B);
         const float* pb = s->pbias + (size_t)l * B * N * IPA_H * Np;
         const size_t smem = ia_smem(G, Np).total;
-        if (G == 8) ipa_attention_tc_kernel<8><<<grid, IA_THREADS, smem, st>>>(c->qkv, pb, s->z_img, c->rots_w, c->trans_w, w.hw, s->cat_img, N, Np, Rp, row0);
-        else if (G == 4) ipa_attention_tc_kernel<4><<<grid, IA_THREADS, smem, st>>>(c->qkv, pb, s->z_img, c->rots_w, c->trans_w, w.hw, s->cat_img, N, Np, Rp, row0);
-        else ipa_attention_tc_kernel<2><<<grid, IA_THREADS, smem, st>>>(c->qkv, pb, s->z_img, c->rots_w, c->trans_w, w.hw, s->cat_img, N, Np, Rp, row0);
+        if (G == 8) launch_pdl(ipa_attention_tc_kernel<8>, grid, IA_THREADS, smem, st, c->qkv, pb, s->z_img, c->rots_w, c->trans_w, w.hw, s->cat_img, N, Np, Rp, row0);
+        else if (G == 4) launch_pdl(ipa_attention_tc_kernel<4>, grid, IA_THREADS, smem, st, c->qkv, pb, s->z_img, c->rots_w, c->trans_w, w.hw, s->cat_img, N, Np, Rp, row0);
+        else launch_pdl(ipa_attention_tc_kernel<2>, grid, IA_THREADS, smem, st, c->qkv, pb, s->z_img, c->rots_w, c->trans_w, w.hw, s->cat_img, N, Np, Rp, row0);
       }
       GB_LAUNCH_CHECK(c, "ipa_attention_tc");
       if (W > 1) {
         if ((rc = gemm_img(c, st, s->cat_img, IPA_CAT, t.Wout, cs, w.bout, c->s, cs, c->sA, cs, nullptr, false, 0, row0 / 128, rows / 128))) return rc;
         if ((rc = shard_all_gather(c, c->sA, (size_t)rows * cs * sizeof(float), st))) return rc;
       } else if ((rc = gemm_img(c, st, s->cat_img, IPA_CAT, t.Wout, cs, w.bout, c->s, cs, c->sA, cs, nullptr, false))) return rc;
-      ln_img_kernel<<<lnb, 256, 0, st>>>(c->sA, c->sB, nullptr, s->ln1_img, w.ln1_g, w.ln1_b, R, cs, Rp, 1);
+      launch_pdl(ln_img_kernel, lnb, 256, 0, st, c->sA, c->sB, nullptr, s->ln1_img, w.ln1_g, w.ln1_b, R, cs, Rp, 1, nullptr, nullptr, nullptr, nullptr);
       GB_LAUNCH_CHECK(c, "ipa_layer_norm");
       float* cur = c->sB;
       float* other = c->sA;
       for (int tl = 0; tl < d.n_structure_transition_layer; ++tl) {
         if (tl > 0) {
-          ln_img_kernel<<<lnb, 256, 0, st>>>(cur, nullptr, nullptr, s->ln1_img, nullptr, nullptr, R, cs, Rp, 0);
+          launch_pdl(ln_img_kernel, lnb, 256, 0, st, cur, nullptr, nullptr, s->ln1_img, nullptr, nullptr, R, cs, Rp, 0, nullptr, nullptr, nullptr, nullptr);
           GB_LAUNCH_CHECK(c, "to_img");
         }
         if ((rc = gemm_img(c, st, s->ln1_img, cs, t.W1[tl], cs, w.b1[tl], nullptr, 0, nullptr, 0, s->h1_img, true))) return rc;
@@ -819,10 +875,9 @@ int tc_structure_net(gb_ctx* c, float* states_out, cudaStream_t st) {
         float* tmp = cur; cur = other; other = tmp;
       }
       float* st_out = states_out ? states_out + (size_t)state_idx * Rcs : nullptr;
-      ln_img_kernel<<<lnb, 256, 0, st>>>(cur, c->s, st_out, s->s_img, w.ln2_g, w.ln2_b, R, cs, Rp, 1);
-      GB_LAUNCH_CHECK(c, "transition_layer_norm");
+      launch_pdl(ln_img_kernel, lnb, 256, 0, st, cur, c->s, st_out, s->s_img, w.ln2_g, w.ln2_b, R, cs, Rp, 1, w.Wbb, w.bbb, c->rots_w, c->trans_w);
+      GB_LAUNCH_CHECK(c, "transition_layer_norm_backbone_update");
       ++state_idx;
-      if ((rc = simt_backbone_update(c, w, st))) return rc;
     }
   return GB_OK;
 }

@@ -70,6 +70,10 @@ __global__ void __launch_bounds__(K7_THREADS, 1) pair_transition_tc_kernel(
   const uint32_t tmem = *tslot;
   const uint32_t iters = (npairs - blockIdx.x + gridDim.x - 1) / gridDim.x;
   const uint32_t T_D1 = 0, T_H = 128, T_D2 = 256;
+  if (warp != 17) {      // the weight loader touches nothing the previous kernel wrote: it starts streaming at once
+    pdl_wait();
+    pdl_launch();
+  }
 
   if (warp == 17) {
     // ------------------------------------------------------------------ weight-block loader
@@ -353,7 +357,7 @@ int tc_pair_transition(gb_ctx* c, const TransitionW& w, float* p, cudaStream_t s
   TcState* s = static_cast<TcState*>(c->tc_state);
   const uint32_t npairs = (uint32_t)((M + 255) / 256);
   const uint32_t grid = npairs < (uint32_t)s->num_sms ? npairs : (uint32_t)s->num_sms;
-  pair_transition_tc_kernel<<<grid, K7_THREADS, K7_SMEM, st>>>(p + px0 * 128, (uint32_t)M, (uint32_t)px0, c->N, npairs, c->mask, (const bf16*)w.tc_W1, w.tc_b1,
+  launch_pdl_cls(4, pair_transition_tc_kernel, grid, K7_THREADS, K7_SMEM, st, p + px0 * 128, (uint32_t)M, (uint32_t)px0, c->N, npairs, c->mask, (const bf16*)w.tc_W1, w.tc_b1,
                                                                (const bf16*)w.tc_W2, w.b2, (uint32_t)c->d.pair_transition_n);
   GB_LAUNCH_CHECK(c, "pair_transition_tc");
   return GB_OK;

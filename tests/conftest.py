@@ -10,6 +10,9 @@ if ROOT not in sys.path:
 
 def pytest_configure(config):
     config.addinivalue_line('markers', 'gpu: needs a CUDA device (run on the B200 box)')
+    # the CPU oracle's fp32 sums depend on the thread count: pin it so that live oracle runs are comparable across boxes
+    import torch
+    torch.set_num_threads(min(8, os.cpu_count() or 1))
 
 
 def pytest_collection_modifyitems(config, items):
