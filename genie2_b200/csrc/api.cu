@@ -676,6 +676,11 @@ extern "C" int gb_denoise(gb_ctx* c, const float* rots, const float* trans, cons
                                                     d.template_dist_step, c->has_motif, row0);
   GB_LAUNCH_CHECK(c, "pair_embed");
   // PairTransformNet
+  static const int per_sample_mode = [] { const char* e = getenv("GB_PAIR_PER_SAMPLE"); return e ? atoi(e) : 0; }();
+  const bool per_sample = per_sample_mode && c->precision == GB_PREC_BF16 && W == 1 && B > 1 && d.include_mul_update && !d.include_tri_att;
+  if (per_sample) {
+    if ((rc = tc_pair_stack_per_sample(c, st))) return rc;
+  } else
   for (int l = 0; l < d.n_pair_transform_layer; ++l) {
     if (d.include_mul_update) {
       if ((rc = run_trimul(c, c->pair[l].mul_out, true, c->p, st))) return rc;
