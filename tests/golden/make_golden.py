@@ -120,22 +120,24 @@ def gen_primitives():
     print('primitives ok')
 
 
-def gen_trajectory():
+def gen_trajectory(name='traj_uncond', T_=6, L=14, B=2, seed=21, n_pair=2, n_struct=3, quat_dtype=np.float32):
     """BaseSampler._sample (sampler/base.py:216-289) run unmodified through
     UnconditionalSampler with n_timestep = 6, L = 14, B = 2 and torch.randn_like inside
-    genie.sampler.base rebound to consume a seeded tape (module-attribute patch)."""
+    genie.sampler.base rebound to consume a seeded tape (module-attribute patch).
+    name='traj_c1': BASELINE.json configs[0] -- L = 64, batch 1, 50 steps, the full base configuration (5 pair
+    layers, 8 structure layers); quaternion signs stored as fp16 (only their sign is consumed)."""
     ns = R.load()
     from genie.config import Config
     from genie.diffusion.genie import Genie
     from genie.sampler.unconditional import UnconditionalSampler
     import genie.sampler.base as base
-    T_, L, B, seed, scale = 6, 14, 2, 21, 0.6
-    cfg = O.OracleConfig(n_timestep=T_, n_pair_transform_layer=2, n_structure_layer=3)
+    scale = 0.6
+    cfg = O.OracleConfig(n_timestep=T_, n_pair_transform_layer=n_pair, n_structure_layer=n_struct)
     sd = W.make_state_dict(cfg, seed, 'activated')
     config = Config(os.path.join(R.REFERENCE_ROOT, 'results/base/configuration'))
     config.diffusion['n_timestep'] = T_
-    config.model['n_pair_transform_layer'] = 2
-    config.model['n_structure_layer'] = 3
+    config.model['n_pair_transform_layer'] = n_pair
+    config.model['n_structure_layer'] = n_struct
     genie = Genie(config).eval()
     genie.model.load_state_dict(sd)
     sampler = UnconditionalSampler(genie)
@@ -161,14 +163,17 @@ def gen_trajectory():
     assert not draws and len(rec.records) == T_
     final = np.stack([o['atom_positions'] for o in out])
     np.savez_compressed(
-        os.path.join(HERE, 'traj_uncond.npz'), T=T_, L=L, B=B, seed=seed, scale=scale,
+        os.path.join(HERE, name + '.npz'), T=T_, L=L, B=B, seed=seed, scale=scale, n_pair=n_pair, n_struct=n_struct,
         weights_checksum=W.checksum(sd), tape=tape.numpy(),
-        quats=torch.stack(rec.records).numpy(), final=final.astype(np.float32))
-    print('traj ok', np.abs(final).max())
+        quats=torch.stack(rec.records).numpy().astype(quat_dtype), final=final.astype(np.float32))
+    print(name, 'ok', np.abs(final).max())
 
 
 if __name__ == '__main__':
     torch.set_num_threads(8)
+    if 'c1' in sys.argv[1:]:
+        gen_trajectory('traj_c1', T_=50, L=64, B=1, seed=31, n_pair=5, n_struct=8, quat_dtype=np.float16)
+        sys.exit(0)
     gen_primitives()
     for c in CASES:
         gen_forward_case(c)
