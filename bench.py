@@ -21,6 +21,8 @@ import sys
 import tempfile
 import time
 
+import numpy as np
+
 ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
@@ -38,6 +40,7 @@ def parse():
     ap.add_argument('--precision', default=os.environ.get('GB_BENCH_PRECISION', 'auto'))
     ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
     ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--no-sample-1000', action='store_true', help='skip the measured whole 1000-step sample (about 4 s)')
     ap.add_argument('--workload', default='c2', choices=['c2', 'c5'],
                     help="c2 (default, the contract's line): L=256 batch 4; c5: ONE L=1024 sample, row-sharded over the ranks")
     return ap.parse_args()
@@ -364,6 +367,22 @@ def run_b200(args):
                        'frac_of_tensor_sustained': fl / (ms / K * 1e-3) / 1e12 / pk['tensor_sustained']},
         'finite': finite,
     }
+    # ---- metric (ii) of SURVEY 8(d), measured rather than extrapolated: wall time of ONE whole 1000-step batch through the
+    # public sampler API (BaseSampler._sample, base.py:216-289): feature build + upload, 1000 x (denoise + posterior +
+    # frames), download of the final coordinates.  Rank 0 only, after the timed region above.
+    if not args.no_sample_1000:
+        sampler = genie2_b200.UnconditionalSampler(genie)
+        params = {'length': L, 'scale': SCALE, 'num_samples': B, 'outdir': tempfile.gettempdir(), 'prefix': 'bench', 'offset': 0,
+                  'noise': 'philox', 'seed': 7}
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        outs = sampler._sample(params)
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        line['sample_1000'] = {'seconds': dt, 'steps': T_STEPS, 'batch': B, 'length': L,
+                               'api': 'UnconditionalSampler._sample (features + 1000 reverse steps + download), in-kernel Philox noise',
+                               'finite': bool(all(np.isfinite(o['atom_positions']).all() for o in outs))}
+        line['seconds_per_1000_step_sample'] = dt
     if not args.no_cpu_baseline and world == 1:
         step, xc, threads = oracle_stepper()
         with torch.no_grad():

@@ -79,7 +79,15 @@ extern "C" int gb_create(gb_ctx** out, const gb_dims* d, int device) {
   return GB_OK;
 }
 
+static void drop_step_graph(gb_ctx* c) {
+  if (c->step_graph) cudaGraphExecDestroy((cudaGraphExec_t)c->step_graph);
+  c->step_graph = nullptr;
+  c->step_key = gb_ctx::StepKey();
+  ++c->epoch;
+}
+
 static void free_features(gb_ctx* c) {
+  drop_step_graph(c);
   if (c->feat_alloc) cudaFree(c->feat_alloc);
   if (c->ws_alloc) cudaFree(c->ws_alloc);
   c->feat_alloc = c->ws_alloc = nullptr;
@@ -92,6 +100,7 @@ extern "C" void gb_destroy(gb_ctx* c) {
   shard_destroy(c);
   tc_destroy(c);
   free_features(c);
+  if (c->cap_stream) cudaStreamDestroy((cudaStream_t)c->cap_stream);
   if (c->tape_alloc) cudaFree(c->tape_alloc);
   if (c->alphas) cudaFree(c->alphas);
   for (void* p : c->weight_allocs) cudaFree(p);
@@ -354,6 +363,7 @@ extern "C" int gb_load_weights(gb_ctx* c, const gb_tensor* tensors, int n) {
   for (void* p : c->weight_allocs) if (!p) return gb_fail(c, GB_ERR_CUDA, "gb_load_weights: device allocation failed");
   c->host.clear();
   c->weights_loaded = true;
+  ++c->epoch;
   return GB_OK;
 }
 
@@ -424,6 +434,7 @@ static void carve_workspace(gb_ctx* c, Carver& k, int B, int N) {
   c->trans_io = k.take<float>(R * 3);
   c->rots_io = k.take<float>(R * 9);
   c->t_dev = k.take<int>(B);
+  c->step_dev = k.take<int>(1);
   c->p = k.take<float>(M * 128);
   c->a = k.take<float>(M * 128);
   c->b = k.take<float>(M * 128);
@@ -511,6 +522,7 @@ extern "C" int gb_set_features(gb_ctx* c, const gb_features* f) {
   if (e != cudaSuccess) return gb_fail(c, GB_ERR_CUDA, "static embedding kernels failed: %s", cudaGetErrorString(e));
   c->launches += 3;
   c->features_set = true;
+  ++c->epoch;
   return GB_OK;
 }
 
@@ -537,6 +549,13 @@ __global__ void fill_int_kernel(int* p, int v, int n) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) p[i] = v;
 }
+
+// graph-replayed reverse step: timesteps[b] = *step at the start of a step, *step -= 1 at its end
+__global__ void step_begin_kernel(int* __restrict__ t_dev, const int* __restrict__ step, int n) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) t_dev[i] = *step;
+}
+__global__ void step_end_kernel(int* step) { *step -= 1; }
 
 static int check_ready(gb_ctx* c, const char* who) {
   if (!c) return GB_ERR_INVALID;
@@ -676,11 +695,6 @@ extern "C" int gb_denoise(gb_ctx* c, const float* rots, const float* trans, cons
                                                     d.template_dist_step, c->has_motif, row0);
   GB_LAUNCH_CHECK(c, "pair_embed");
   // PairTransformNet
-  static const int per_sample_mode = [] { const char* e = getenv("GB_PAIR_PER_SAMPLE"); return e ? atoi(e) : 0; }();
-  const bool per_sample = per_sample_mode && c->precision == GB_PREC_BF16 && W == 1 && B > 1 && d.include_mul_update && !d.include_tri_att;
-  if (per_sample) {
-    if ((rc = tc_pair_stack_per_sample(c, st))) return rc;
-  } else
   for (int l = 0; l < d.n_pair_transform_layer; ++l) {
     if (d.include_mul_update) {
       if ((rc = run_trimul(c, c->pair[l].mul_out, true, c->p, st))) return rc;
@@ -736,10 +750,10 @@ extern "C" int gb_denoise(gb_ctx* c, const float* rots, const float* trans, cons
 }
 
 static int launch_ddpm(gb_ctx* c, float* trans, float* rots, const float* z, int step, float scale, const float* noise,
-                       size_t noise_step_stride, uint64_t seed, cudaStream_t st) {
+                       size_t noise_step_stride, uint64_t seed, cudaStream_t st, const int* step_dev = nullptr) {
   const size_t smem = (size_t)c->N * 13 * 4;
   ddpm_step_kernel<<<c->B, 256, smem, st>>>(trans, rots, z, noise, c->chain_index, c->mask, c->alphas, c->sqrt_alphas,
-                                            c->sqrt_omac, c->sqrt_betas, step, nullptr, noise_step_stride, scale, seed, c->N);
+                                            c->sqrt_omac, c->sqrt_betas, step, step_dev, noise_step_stride, scale, seed, c->N);
   GB_LAUNCH_CHECK(c, "ddpm_step");
   return GB_OK;
 }
@@ -764,6 +778,57 @@ extern "C" int gb_sample_loop(gb_ctx* c, float* trans_inout, float* rots_inout, 
     return gb_fail(c, GB_ERR_INVALID, "gb_sample_loop: bad step range [%d, %d]", t_start, t_end);
   cudaStream_t st = (cudaStream_t)stream;
   const size_t stride = (size_t)c->B * c->N * 3;
+  // Three or more steps on one GPU: capture ONE step (its ~105 launches, programmatic-dependent-launch edges included) as
+  // a CUDA graph whose kernels read the step index from device memory, and replay it.  Short chains at L <= 128 are
+  // otherwise bound by the host's launch rate, not by the GPU.  The capture runs on a private stream (the caller's may be
+  // the legacy default stream, which cannot capture); replays go to the caller's stream.  GB_STEP_GRAPH=0 keeps the plain
+  // launch loop (also used for row-sharded runs: NCCL calls stay outside graphs here).
+  static const int graph_mode = [] { const char* e = getenv("GB_STEP_GRAPH"); return e ? atoi(e) : 1; }();
+  if (graph_mode && c->shard_world == 1 && t_start - t_end + 1 >= 3) {
+    gb_ctx::StepKey key;
+    key.trans = trans_inout; key.rots = rots_inout; key.tape = noise_tape; key.scale = scale; key.seed = seed;
+    key.epoch = c->epoch; key.precision = c->precision;
+    if (!c->step_graph || !(key == c->step_key)) {
+      if (c->step_graph) cudaGraphExecDestroy((cudaGraphExec_t)c->step_graph);
+      c->step_graph = nullptr;
+      const int64_t l0 = c->launches;
+      if (!c->cap_stream) {
+        cudaStream_t ns = nullptr;
+        GB_CUDA(c, cudaStreamCreateWithFlags(&ns, cudaStreamNonBlocking));
+        c->cap_stream = ns;
+      }
+      cudaStream_t cs = (cudaStream_t)c->cap_stream;
+      GB_CUDA(c, cudaStreamBeginCapture(cs, cudaStreamCaptureModeThreadLocal));
+      step_begin_kernel<<<1, 256, 0, cs>>>(c->t_dev, c->step_dev, c->B);
+      rc = cudaGetLastError() == cudaSuccess ? GB_OK : gb_fail(c, GB_ERR_CUDA, "step_begin launch failed during capture");
+      c->launches++;
+      if (rc == GB_OK) rc = gb_denoise(c, rots_inout, trans_inout, c->t_dev, c->z, nullptr, cs);
+      if (rc == GB_OK) rc = launch_ddpm(c, trans_inout, rots_inout, c->z, 0, scale, noise_tape, noise_tape ? stride : 0, seed, cs, c->step_dev);
+      if (rc == GB_OK) {
+        step_end_kernel<<<1, 1, 0, cs>>>(c->step_dev);
+        c->launches++;
+      }
+      cudaGraph_t graph = nullptr;
+      const cudaError_t ce = cudaStreamEndCapture(cs, &graph);
+      c->step_launches = c->launches - l0;
+      c->launches = l0;                                  // nothing ran yet: replays are counted below
+      if (rc != GB_OK) { if (graph) cudaGraphDestroy(graph); return rc; }
+      if (ce != cudaSuccess || !graph) return gb_fail(c, GB_ERR_CUDA, "gb_sample_loop: stream capture failed: %s", cudaGetErrorString(ce));
+      cudaGraphExec_t exec = nullptr;
+      const cudaError_t ie = cudaGraphInstantiate(&exec, graph, 0);
+      cudaGraphDestroy(graph);
+      if (ie != cudaSuccess) return gb_fail(c, GB_ERR_CUDA, "gb_sample_loop: cudaGraphInstantiate failed: %s", cudaGetErrorString(ie));
+      c->step_graph = exec;
+      c->step_key = key;
+    }
+    fill_int_kernel<<<1, 32, 0, st>>>(c->step_dev, t_start, 1);
+    GB_LAUNCH_CHECK(c, "set_step");
+    for (int step = t_start; step >= t_end; --step) {
+      GB_CUDA(c, cudaGraphLaunch((cudaGraphExec_t)c->step_graph, st));
+      c->launches += c->step_launches;
+    }
+    return GB_OK;
+  }
   for (int step = t_start; step >= t_end; --step) {
     fill_int_kernel<<<1, 256, 0, st>>>(c->t_dev, step, c->B);
     GB_LAUNCH_CHECK(c, "fill_timesteps");

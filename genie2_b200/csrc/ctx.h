@@ -83,6 +83,21 @@ struct gb_ctx {
   float *qkv = nullptr, *cat = nullptr, *rots_w = nullptr, *trans_w = nullptr, *z = nullptr;
   float *trans_io = nullptr, *rots_io = nullptr;   // gb_sample_host state
   int* t_dev = nullptr;                            // [B] timesteps
+  // gb_sample_loop: one reverse step captured as a CUDA graph and replayed; the step index lives on the device
+  int* step_dev = nullptr;                         // [1] step of the next replay, decremented by the graph itself
+  void* step_graph = nullptr;                      // cudaGraphExec_t
+  int64_t step_launches = 0;                       // kernels in one captured step
+  void* cap_stream = nullptr;                      // private stream the capture runs on
+  struct StepKey {
+    const void *trans = nullptr, *rots = nullptr, *tape = nullptr;
+    float scale = 0.f;
+    uint64_t seed = 0, epoch = 0;
+    int precision = -1;
+    bool operator==(const StepKey& o) const {
+      return trans == o.trans && rots == o.rots && tape == o.tape && scale == o.scale && seed == o.seed && epoch == o.epoch && precision == o.precision;
+    }
+  } step_key;
+  uint64_t epoch = 0;                              // bumped by everything that invalidates a captured step (features, weights, schedule, sharding)
   void* tape_alloc = nullptr;
   size_t tape_bytes = 0;
   // row sharding of one long sample over `shard_world` GPUs (shard.cu); 1 = off

@@ -27,8 +27,6 @@ int tc_bind_workspace(gb_ctx* c, void* base, size_t bytes, int B, int N);
 int tc_trimul(gb_ctx* c, const TriMulW& w, bool outgoing, float* p, cudaStream_t st);
 // one kernel of the update only: stage 1 = K4 projections, 2 = K5 contraction, 3 = K6 output (0 = all)
 int tc_trimul_stage(gb_ctx* c, const TriMulW& w, bool outgoing, int stage, float* p, cudaStream_t st);
-// the whole PairTransformNet on c->p, one sample at a time (L2-resident working set); W == 1, bf16, no triangle attention
-int tc_pair_stack_per_sample(gb_ctx* c, cudaStream_t st);
 // p = (p + PairTransition(p)) * mask
 int tc_pair_transition(gb_ctx* c, const TransitionW& w, float* p, cudaStream_t st);
 

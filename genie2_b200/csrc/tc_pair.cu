@@ -480,32 +480,6 @@ int tc_trimul_stage(gb_ctx* c, const TriMulW& w, bool outgoing, int stage, float
 
 int tc_trimul(gb_ctx* c, const TriMulW& w, bool outgoing, float* p, cudaStream_t st) { return tc_trimul_stage(c, w, outgoing, 0, p, st); }
 
-// The pair stack sample by sample (W == 1, tri-mul on, triangle attention off).  Samples are independent through
-// PairTransformNet, and one sample's working set at N = 256 (p 33.5 MB fp32 + a, b, x, g 16.8 MB each) fits the 126 MB
-// L2, so running all layers of sample 0, then of sample 1, ... lets K5 / K6 / K7 / the next K4 find what the previous
-// kernel wrote in L2 instead of HBM.  Every kernel sees a batch of one through offset pointers.
-int tc_pair_stack_per_sample(gb_ctx* c, cudaStream_t st) {
-  TcState* s = static_cast<TcState*>(c->tc_state);
-  const int B = c->B, N = c->N, Np = s->Np;
-  const size_t img = (size_t)128 * Np * Np, pix = (size_t)N * N * 128;
-  bf16 *a0 = s->a, *b0 = s->b, *x0 = s->x, *g0 = s->g;
-  int* m0 = c->mask;
-  int rc = GB_OK;
-  c->B = 1;
-  for (int b = 0; b < B && rc == GB_OK; ++b) {
-    s->a = a0 + b * img; s->b = b0 + b * img; s->x = x0 + b * img; s->g = g0 + b * pix;
-    c->mask = m0 + (size_t)b * N;
-    float* p = c->p + b * pix;
-    for (int l = 0; l < c->d.n_pair_transform_layer && rc == GB_OK; ++l) {
-      if ((rc = tc_trimul(c, c->pair[l].mul_out, true, p, st)) != GB_OK) break;
-      if ((rc = tc_trimul(c, c->pair[l].mul_in, false, p, st)) != GB_OK) break;
-      rc = tc_pair_transition(c, c->pair[l].tr, p, st);
-    }
-  }
-  c->B = B; s->a = a0; s->b = b0; s->x = x0; s->g = g0; c->mask = m0;
-  return rc;
-}
-
 extern "C" int gb_dbg_tc_copy(gb_ctx* c, int which, void* dst, int64_t bytes) {
   if (!c || !c->tc_state || !c->features_set) return GB_ERR_INVALID;
   TcState* s = static_cast<TcState*>(c->tc_state);
