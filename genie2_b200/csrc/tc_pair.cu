@@ -235,7 +235,7 @@ __global__ void __launch_bounds__(256, 2) trimul_contract_tc_kernel(const bf16* 
 // from shared memory while the tensor core runs.  u is summed from the bf16-rounded W' so the mean
 // term cancels exactly.  Shared: X 32K | W' 32K (then the 64K fp32 staging tile); 128 TMEM columns.
 // ---------------------------------------------------------------------------------------------
-#define K6_SMEM (65536 + 1024 + 64 + 3072)
+#define K6_SMEM (65536 + 1024 + 64 + 5120)
 
 __global__ void __launch_bounds__(256, 3) trimul_out_tc_kernel(
     const bf16* __restrict__ x, const bf16* __restrict__ g, float* __restrict__ p, int N, int Np,
@@ -247,7 +247,7 @@ __global__ void __launch_bounds__(256, 3) trimul_out_tc_kernel(
   uint64_t* bar_w = reinterpret_cast<uint64_t*>(sm + 65536);
   uint64_t* bar_mma = bar_w + 1;
   uint32_t* tslot = reinterpret_cast<uint32_t*>(bar_w + 2);
-  float* red = reinterpret_cast<float*>(sm + 65536 + 64);     // [2][128] partials, then mean [128], rstd [128]
+  float* red = reinterpret_cast<float*>(sm + 65536 + 64);     // [8][128] partials, then mean [128], rstd [128]
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const PixTile T = pix_tile(blockIdx.x, tr);
   if (tid == 0) {
@@ -258,6 +258,19 @@ __global__ void __launch_bounds__(256, 3) trimul_out_tc_kernel(
     bulk_g2s(W, Wzimg, 32768, bar_w);
   }
   if (warp == 1) tmem_alloc(tslot, 128);
+  {
+    // the tile's p and g rows are only read at the very end (after the GEMM, the statistics and the TMEM drain), with few
+    // bytes in flight per warp: ask L2 for them now.  Safe before the dependency wait: L2 is the point of coherence.
+    if (tid >= 32 && tid < 36) {
+      const uint32_t ii = (tid >> 1) & 1, row = 2 * T.t2 + ii, col = 64 * T.jb;
+      if (row < (uint32_t)N && col < (uint32_t)N) {
+        const uint32_t npx = min(64u, (uint32_t)N - col);
+        const size_t px = ((size_t)T.b * N + row) * N + col;
+        if (tid & 1) l2_prefetch(g + px * 128, npx * 256u);
+        else l2_prefetch(p + px * 128, npx * 512u);
+      }
+    }
+  }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -275,30 +288,73 @@ __global__ void __launch_bounds__(256, 3) trimul_out_tc_kernel(
     umma_commit(bar_mma);
   }
   __syncwarp();
-  // per-pixel statistics over the 128 channels, from the same shared tile (two passes, fp32)
+  // per-pixel statistics over the 128 channels, from the same shared tile (two passes, fp32).  A thread owns one 16-byte
+  // chunk column (8 consecutive pixels) of 8 channel rows: 8 conflict-free LDS.128 bring its 64 values into registers;
+  // partial sums meet through a shuffle (lane ^ 16 = the neighbouring channel group) and an [8][128] shared array.
   mbar_wait(bar_w, 0);
   {
-    const uint32_t mm = tid & 127, hh = tid >> 7;                 // pixel, channel half
-    // element (pixel mm, channel c): block mm >> 6, row c, chunk ((mm & 63) >> 3) ^ (c & 7), lane mm & 7
-    const uint8_t* base = X + (mm >> 6) * 16384u + hh * 64u * 128u + ((mm & 7) << 1);
-    const uint32_t q8 = (mm & 63) >> 3;
-    float sum = 0.f;
-#pragma unroll 16
-    for (uint32_t c = 0; c < 64; ++c) sum += __bfloat162float(*reinterpret_cast<const bf16*>(base + c * 128u + ((q8 ^ (c & 7u)) << 4)));
-    red[hh * 128 + mm] = sum;
-    __syncthreads();
-    const float mean = (red[mm] + red[128 + mm]) * (1.f / 128.f);
-    float d2 = 0.f;
-#pragma unroll 16
-    for (uint32_t c = 0; c < 64; ++c) {
-      const float d = __bfloat162float(*reinterpret_cast<const bf16*>(base + c * 128u + ((q8 ^ (c & 7u)) << 4))) - mean;
-      d2 = fmaf(d, d, d2);
+    const uint32_t pc = tid & 15, cg = tid >> 4;                  // pixel chunk (8 pixels), channel group (8 channels)
+    const uint32_t q8 = pc & 7;
+    const uint8_t* base = X + (pc >> 3) * 16384u + cg * 1024u;    // channel row c = 8 cg + k holds chunk q8 at position q8 ^ k
+    uint4 w[8];
+#pragma unroll
+    for (uint32_t k = 0; k < 8; ++k) w[k] = *reinterpret_cast<const uint4*>(base + k * 128u + ((q8 ^ k) << 4));
+    float acc[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc[i] = 0.f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const uint32_t ww[4] = {w[k].x, w[k].y, w[k].z, w[k].w};
+#pragma unroll
+      for (int t = 0; t < 4; ++t) {
+        acc[2 * t] += __uint_as_float(ww[t] << 16);
+        acc[2 * t + 1] += __uint_as_float(ww[t] & 0xffff0000u);
+      }
     }
-    red[256 + hh * 128 + mm] = d2;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc[i] += __shfl_xor_sync(0xffffffffu, acc[i], 16);
+    float* part = red + (cg >> 1) * 128 + pc * 8;                 // red: [8][128] partials | mean [128] | rstd [128]
+    if ((lane & 16) == 0) {
+      st4(part, make_float4(acc[0], acc[1], acc[2], acc[3]));
+      st4(part + 4, make_float4(acc[4], acc[5], acc[6], acc[7]));
+    }
     __syncthreads();
-    if (hh == 0) {
-      red[512 + mm] = mean;
-      red[640 + mm] = rsqrtf((red[256 + mm] + red[384 + mm]) * (1.f / 128.f) + 1e-5f);
+    if (tid < 128) {
+      float t = 0.f;
+#pragma unroll
+      for (int r = 0; r < 8; ++r) t += red[r * 128 + tid];
+      red[1024 + tid] = t * (1.f / 128.f);
+    }
+    __syncthreads();
+    float mean[8];
+    {
+      const float4 m0 = ld4(red + 1024 + pc * 8), m1 = ld4(red + 1024 + pc * 8 + 4);
+      mean[0] = m0.x; mean[1] = m0.y; mean[2] = m0.z; mean[3] = m0.w; mean[4] = m1.x; mean[5] = m1.y; mean[6] = m1.z; mean[7] = m1.w;
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc[i] = 0.f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const uint32_t ww[4] = {w[k].x, w[k].y, w[k].z, w[k].w};
+#pragma unroll
+      for (int t = 0; t < 4; ++t) {
+        const float d0 = __uint_as_float(ww[t] << 16) - mean[2 * t], d1 = __uint_as_float(ww[t] & 0xffff0000u) - mean[2 * t + 1];
+        acc[2 * t] = fmaf(d0, d0, acc[2 * t]);
+        acc[2 * t + 1] = fmaf(d1, d1, acc[2 * t + 1]);
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc[i] += __shfl_xor_sync(0xffffffffu, acc[i], 16);
+    if ((lane & 16) == 0) {                                       // the partials of pass 1 were consumed before the last barrier
+      st4(part, make_float4(acc[0], acc[1], acc[2], acc[3]));
+      st4(part + 4, make_float4(acc[4], acc[5], acc[6], acc[7]));
+    }
+    __syncthreads();
+    if (tid < 128) {
+      float t = 0.f;
+#pragma unroll
+      for (int r = 0; r < 8; ++r) t += red[r * 128 + tid];
+      red[1152 + tid] = rsqrtf(t * (1.f / 128.f) + 1e-5f);
     }
   }
   mbar_wait(bar_mma, 0);
@@ -308,7 +364,7 @@ __global__ void __launch_bounds__(256, 3) trimul_out_tc_kernel(
   const uint32_t t_lane = tmem + ((q * 32u) << 16);
   uint8_t* S = sm;
   {
-    const float mean = red[512 + m], rstd = red[640 + m];
+    const float mean = red[1024 + m], rstd = red[1152 + m];
 #pragma unroll 1
     for (int cc = 0; cc < 2; ++cc) {
       const uint32_t col0 = h * 64 + cc * 32;

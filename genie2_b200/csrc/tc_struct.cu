@@ -417,7 +417,14 @@ __host__ __device__ inline IaSmem ia_smem(int G, int Np) {
   o.total = o.bar + 128 + 1024;
   return o;
 }
-static inline int ia_queries_per_cta(int Np) { return Np <= 256 ? 8 : Np <= 512 ? 4 : 2; }
+// Short chains and small batches: a CTA's fixed cost (prologue, 120 reductions, epilogue) dominates, so take the smallest
+// G that still fits all CTAs in one wave (B * ceil(N / G) <= SMs); otherwise the largest the shared memory allows.
+static inline int ia_queries_per_cta(int Np, int B = 0, int N = 0, int num_sms = 0) {
+  const int gmax = Np <= 256 ? 8 : Np <= 512 ? 4 : 2;
+  for (int g = 2; g < gmax && num_sms > 0; g *= 2)
+    if (B * ((N + g - 1) / g) <= num_sms) return g;
+  return gmax;
+}
 
 // G consecutive floats of the logit / probability array
 template <int G> __device__ __forceinline__ void p_load(const float* pp, float (&t)[G]) {
@@ -658,13 +665,32 @@ __global__ void __launch_bounds__(IA_THREADS, 1) ipa_attention_tc_kernel(
           }
         }
       }
+      // 4 G per-lane partial sums -> lane v ends up with the warp total of value v = 4 g + e: at every step a lane keeps
+      // one half of its values and trades the other half with its partner (4 G - 1 shuffles instead of 5 per value)
+      {
+        constexpr int NV = 4 * G;
+        float a[NV];
 #pragma unroll
-      for (int g = 0; g < G; ++g)
+        for (int g = 0; g < G; ++g)
 #pragma unroll
-        for (int e = 0; e < 4; ++e) {
-          const float r = warp_sum(acc[g][e]);
-          if (lane == 0) oacc[g * 480 + h * 40 + ev * 4 + e] = r;
+          for (int e = 0; e < 4; ++e) a[4 * g + e] = acc[g][e];
+        // lane distances 16 .. NV first (plain butterfly), then the trading steps NV / 2 .. 1: every value is summed over
+        // the same tree (16, 8, 4, 2, 1) whatever G is, so the result does not depend on the queries-per-CTA choice
+#pragma unroll
+        for (int o = 16; o >= NV; o >>= 1)
+#pragma unroll
+          for (int i = 0; i < NV; ++i) a[i] += __shfl_xor_sync(0xffffffffu, a[i], o);
+#pragma unroll
+        for (int sft = NV / 2; sft >= 1; sft >>= 1) {
+          const bool up = (lane & sft) != 0;
+#pragma unroll
+          for (int i = 0; i < sft; ++i) {
+            const float keep = up ? a[i + sft] : a[i], send = up ? a[i] : a[i + sft];
+            a[i] = keep + __shfl_xor_sync(0xffffffffu, send, sft);
+          }
         }
+        if (lane < NV) oacc[(lane >> 2) * 480 + h * 40 + ev * 4 + (lane & 3)] = a[0];
+      }
     }
   }
   __syncthreads();
@@ -847,7 +873,7 @@ int tc_structure_net(gb_ctx* c, float* states_out, cudaStream_t st) {
       launch_pdl(ipa_points_planes_kernel, (R * IPA_H + 255) / 256, 256, 0, st, c->qkv, c->rots_w, c->trans_w, R, N);
       GB_LAUNCH_CHECK(c, "ipa_points_planes");
       {
-        const int G = ia_queries_per_cta(Np), nq = W > 1 ? rows : N;
+        const int nq = W > 1 ? rows : N, G = ia_queries_per_cta(Np, B, nq, s->num_sms);
         const dim3 grid((nq + G - 1) / G, B);
         const float* pb = s->pbias + (size_t)l * B * N * IPA_H * Np;
         const size_t smem = ia_smem(G, Np).total;
