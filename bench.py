@@ -66,8 +66,15 @@ def oracle_stepper(n_threads=None):
     workload: a full denoiser eval + posterior step at L=256, batch 1."""
     import torch
     from oracle import genie_oracle as O, weights as W
-    if n_threads:
-        torch.set_num_threads(n_threads)
+    # all the host cores this process may use: torchrun exports OMP_NUM_THREADS=1 to its workers, which would time the
+    # reference on a single core
+    if not n_threads:
+        try:
+            n_threads = len(os.sched_getaffinity(0))
+        except AttributeError:
+            n_threads = os.cpu_count() or 1
+        n_threads = min(n_threads, 32)     # beyond 32 threads the [1, 256, 256, 128]-sized eager ops stop scaling
+    torch.set_num_threads(n_threads)
     cfg = O.OracleConfig()
     sd = W.make_state_dict(cfg, 0, 'activated')
     feats = O.make_features([[L]])

@@ -225,6 +225,141 @@ __global__ void __launch_bounds__(256, 2) trimul_contract_tc_kernel(const bf16* 
 }
 
 // ---------------------------------------------------------------------------------------------
+// K5, persistent form: one CTA per SM walks the (b, channel, row block, column block) units round robin.  Warp 0 streams
+// k-blocks through a 4-stage ring that runs ahead across unit boundaries, warp 1 issues the MMAs into one of TWO 256-column
+// TMEM accumulators, warps 2-9 drain the other one -- load, MMA and drain of consecutive units overlap instead of
+// relying on a second resident CTA.  Same operands, same k order, same stores as the kernel above: bit-identical x.
+// ---------------------------------------------------------------------------------------------
+#define K5P_STAGES 4
+#define K5P_THREADS 320
+#define K5P_SMEM (K5P_STAGES * K5_STAGE_BYTES + 1024 + 128)
+
+__global__ void __launch_bounds__(K5P_THREADS, 1) trimul_contract_pers_tc_kernel(
+    const bf16* __restrict__ a, const bf16* __restrict__ b, bf16* __restrict__ x, int N, int Np, int NJ, const ImgLayout La,
+    const ImgLayout Lb, int ib0, int nib, uint32_t nunits) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* sm = smem_base_1024(smem_raw);
+  uint64_t* full = reinterpret_cast<uint64_t*>(sm + K5P_STAGES * K5_STAGE_BYTES);
+  uint64_t* empty = full + K5P_STAGES;
+  uint64_t* acc_full = empty + K5P_STAGES;      // [2] MMAs of a unit complete
+  uint64_t* acc_empty = acc_full + 2;           // [2] the 8 epilogue warps have read the accumulator
+  uint32_t* tslot = reinterpret_cast<uint32_t*>(acc_empty + 2);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const uint32_t nkb = (uint32_t)Np >> 6, njb = (uint32_t)(Np + NJ - 1) / NJ;
+
+  if (tid == 0) {
+    for (int s = 0; s < K5P_STAGES; ++s) { mbar_init(full + s, 1); mbar_init(empty + s, 1); }
+    for (int s = 0; s < 2; ++s) { mbar_init(acc_full + s, 1); mbar_init(acc_empty + s, 8); }
+    fence_mbar_init();
+  }
+  if (warp == 2) tmem_alloc(tslot, 512);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tslot;
+  pdl_wait();
+  pdl_launch();
+
+  if (warp == 0) {
+    if (lane == 0) {
+      uint32_t it = 0;
+      for (uint32_t u = blockIdx.x; u < nunits; u += gridDim.x) {
+        uint32_t blk = u;
+        const uint32_t jb = blk % njb; blk /= njb;
+        const uint32_t ib = ib0 + blk % nib; blk /= nib;
+        const uint32_t nj = min((uint32_t)NJ, (uint32_t)Np - jb * NJ);
+        const uint32_t bb = blk >> 7, cch = blk & 127;
+        const uint32_t bpiece = (Lb.RL % nj == 0) ? nj : 128u;
+        const uint32_t a_rows = min(128u, (uint32_t)Np - ib * 128u);
+        for (uint32_t kb = 0; kb < nkb; ++kb, ++it) {
+          const uint32_t s = it % K5P_STAGES;
+          if (it >= K5P_STAGES) mbar_wait(empty + s, ((it / K5P_STAGES) - 1) & 1);
+          uint8_t* st = sm + s * K5_STAGE_BYTES;
+          mbar_expect_tx(full + s, (a_rows + nj) * 128u);
+          bulk_g2s(st, a + img_off(La, bb, cch, kb, ib * 128u), a_rows * 128u, full + s);
+          for (uint32_t r = 0; r < nj; r += bpiece)
+            bulk_g2s(st + 16384 + r * 128u, b + img_off(Lb, bb, cch, kb, jb * NJ + r), min(bpiece, nj - r) * 128u, full + s);
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    const uint32_t tm = warp_uniform(tmem);
+    uint32_t it = 0, n = 0;
+    for (uint32_t u = blockIdx.x; u < nunits; u += gridDim.x, ++n) {
+      const uint32_t jb = u % njb;
+      const uint32_t nj = min((uint32_t)NJ, (uint32_t)Np - jb * NJ);
+      const uint32_t idesc = umma_idesc(128, nj), slot = n & 1u, acc = tm + slot * 256u;
+      if (n >= 2) {
+        mbar_wait(acc_empty + slot, ((n >> 1) - 1) & 1);
+        tc_fence_after();
+      }
+      for (uint32_t kb = 0; kb < nkb; ++kb, ++it) {
+        const uint32_t s = it % K5P_STAGES;
+        mbar_wait(full + s, (it / K5P_STAGES) & 1);
+        tc_fence_after();
+        const uint32_t sa = smem_u32(sm + s * K5_STAGE_BYTES), sb = sa + 16384;
+        if (elect_one()) {
+#pragma unroll
+          for (int k = 0; k < 4; ++k) umma(acc, umma_desc(sa + k * 32), umma_desc(sb + k * 32), idesc, (kb | k) ? 1u : 0u);
+          umma_commit(empty + s);
+          if (kb == nkb - 1) umma_commit(acc_full + slot);
+        }
+        __syncwarp();
+      }
+    }
+  } else {
+    // epilogue warps 2..9: thread = output row (TMEM lane quarter = warp & 3); warps 2-5 take even 32-column groups, 6-9 odd ones
+    const uint32_t q = warp & 3, h = (uint32_t)(warp - 2) >> 2;
+    uint32_t n = 0;
+    for (uint32_t u = blockIdx.x; u < nunits; u += gridDim.x, ++n) {
+      uint32_t blk = u;
+      const uint32_t jb = blk % njb; blk /= njb;
+      const uint32_t ib = ib0 + blk % nib; blk /= nib;
+      const uint32_t nj = min((uint32_t)NJ, (uint32_t)Np - jb * NJ);
+      const uint32_t bb = blk >> 7, cch = blk & 127, slot = n & 1u;
+      const uint32_t i = ib * 128 + q * 32 + lane;
+      const uint32_t t_lane = tmem + ((q * 32u) << 16) + slot * 256u;
+      mbar_wait(acc_full + slot, (n >> 1) & 1);
+      tc_fence_after();
+      __syncwarp();
+      for (uint32_t c0 = h * 32; c0 < nj; c0 += 64) {
+        uint32_t v[32];
+        tmem_ld32(t_lane + c0, v);
+        tmem_ld_wait();
+        if (i < (uint32_t)N) {
+          const uint32_t j = jb * NJ + c0, jb64 = j >> 6, q0 = (j & 63) >> 3;
+          uint8_t* dst = reinterpret_cast<uint8_t*>(x) +
+                         (((((size_t)bb * (Np >> 1) + (i >> 1)) * (Np >> 6) + jb64) * 2 + (i & 1)) * 128 + cch) * 128;
+          const uint32_t sw = cch & 7u;
+#pragma unroll
+          for (int kp = 0; kp < 2; ++kp) {
+            uint4 o[2];
+#pragma unroll
+            for (int k4 = 0; k4 < 2; ++k4) {
+              const uint32_t* vv = v + 16 * kp + 8 * k4;
+              o[k4].x = pack_bf16(__uint_as_float(vv[0]), __uint_as_float(vv[1]));
+              o[k4].y = pack_bf16(__uint_as_float(vv[2]), __uint_as_float(vv[3]));
+              o[k4].z = pack_bf16(__uint_as_float(vv[4]), __uint_as_float(vv[5]));
+              o[k4].w = pack_bf16(__uint_as_float(vv[6]), __uint_as_float(vv[7]));
+            }
+            const bool swap = sw & 1u;
+            st_global_32B(dst + (((q0 + 2 * kp) ^ (sw & 6u)) << 4), swap ? o[1] : o[0], swap ? o[0] : o[1]);
+          }
+        }
+      }
+      // every lane's TMEM reads have completed (tmem_ld_wait): hand the accumulator back to the MMA warp
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(acc_empty + slot);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) tmem_dealloc(tmem, 512);
+}
+
+// ---------------------------------------------------------------------------------------------
 // K6 trimul_out_tc (triangular_multiplicative_update.py:105-108 + residual, pair_transform_net.py:111-112)
 //   p[pixel] += (W_z LN_out(x[:, pixel]) + b_z) * g[pixel]
 // The LayerNorm over channels is applied AFTER the GEMM:  with W' = W_z * gamma (bf16),
@@ -425,6 +560,7 @@ __global__ void __launch_bounds__(256, 3) trimul_out_tc_kernel(
 int tc_init(gb_ctx* c) {
   cudaError_t e;
   if ((e = cudaFuncSetAttribute(trimul_contract_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, K5_SMEM)) != cudaSuccess ||
+      (e = cudaFuncSetAttribute(trimul_contract_pers_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, K5P_SMEM)) != cudaSuccess ||
       (e = cudaFuncSetAttribute(trimul_out_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, K6_SMEM)) != cudaSuccess)
     return gb_fail(c, GB_ERR_CUDA, "tc_init: cudaFuncSetAttribute failed: %s", cudaGetErrorString(e));
   c->tc_state = new TcState();
@@ -521,6 +657,11 @@ int tc_trimul_stage(gb_ctx* c, const TriMulW& w, bool outgoing, int stage, float
     const ImgLayout La = W > 1 && !outgoing ? img_layout(B, Np, W, W) : Lb;
     const int nib = W > 1 ? (N / W) / 128 : (Np + 127) / 128, ib0 = W > 1 ? c->shard_rank * nib : 0;
     const unsigned cgrid = (unsigned)B * 128 * nib * ((Np + NJ - 1) / NJ);
+    static const int k5pers = [] { const char* e = getenv("GB_K5_PERS"); return e ? atoi(e) : 1; }();
+    if (k5pers) {
+      const unsigned pgrid = cgrid < (unsigned)s->num_sms ? cgrid : (unsigned)s->num_sms;
+      launch_pdl_cls(2, trimul_contract_pers_tc_kernel, pgrid, K5P_THREADS, K5P_SMEM, st, s->a, s->b, s->x, N, Np, NJ, La, Lb, ib0, nib, (uint32_t)cgrid);
+    } else
     launch_pdl_cls(2, trimul_contract_tc_kernel, cgrid, 256, K5_SMEM, st, s->a, s->b, s->x, N, Np, NJ, La, Lb, ib0, nib);
     GB_LAUNCH_CHECK(c, "trimul_contract_tc");
   }
