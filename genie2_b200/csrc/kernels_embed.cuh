@@ -94,7 +94,7 @@ __device__ __forceinline__ void soft_bins(float d, float dmin, float dstep, floa
 }
 
 template <int NBIN>
-__global__ void __launch_bounds__(128, 5) pair_embed_kernel(
+__global__ void __launch_bounds__(128, 4) pair_embed_kernel(
     float* __restrict__ p, const float* __restrict__ PiPj /*[B*N, 256]: Pi | Pj*/, const float* __restrict__ rots,
     const float* __restrict__ trans, const int* __restrict__ residue_index, const int* __restrict__ chain_index,
     const int* __restrict__ mask, const uint8_t* __restrict__ fsm, const uint8_t* __restrict__ fst,
@@ -114,9 +114,9 @@ __global__ void __launch_bounds__(128, 5) pair_embed_kernel(
   const int ri = residue_index[row_i], ci = chain_index[row_i], mi = mask[row_i];
   const int fsi = fsm[row_i];
   // per-thread weight columns
-  float wt[NBIN + 4];
+  float2 wt2[NBIN + 4];      // each weight twice: the second operand of the packed FMAs
 #pragma unroll
-  for (int k = 0; k < nbin + 4; ++k) wt[k] = WtT[k * 128 + c];
+  for (int k = 0; k < nbin + 4; ++k) { const float w = WtT[k * 128 + c]; wt2[k] = make_float2(w, w); }
   const float wt_fst = WtT[(nbin + 4) * 128 + c] + WtT[(nbin + 5) * 128 + c];
   const float wm_fst = WmT[nbin * 128 + c] + WmT[(nbin + 1) * 128 + c];
   const float w_same = WrelT[(2 * relpos_k + 2) * 128 + c];
@@ -163,42 +163,43 @@ __global__ void __launch_bounds__(128, 5) pair_embed_kernel(
     }
     __syncthreads();
     const int jn = min(PE_TJ, N - j0);
-    for (int jj = 0; jj < jn; jj += 4) {
-      // global operands of the four pixels first: their latency hides behind the 41 x 4 FMAs below
-      const float4 rel4 = *reinterpret_cast<const float4*>(&feat[nbin + 5][jj]);
-      const float relv[4] = {rel4.x, rel4.y, rel4.z, rel4.w};
-      float pj[4], wr[4];
+    for (int jj = 0; jj < jn; jj += 8) {
+      // global operands of the eight pixels first: their latency hides behind the 41 x 8 FMAs below
+      const float4 rela = *reinterpret_cast<const float4*>(&feat[nbin + 5][jj]), relb = *reinterpret_cast<const float4*>(&feat[nbin + 5][jj + 4]);
+      const float relv[8] = {rela.x, rela.y, rela.z, rela.w, relb.x, relb.y, relb.z, relb.w};
+      float pj[8], wr[8];
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
+      for (int u = 0; u < 8; ++u) {
         const int jc = min(j0 + jj + u, N - 1);
         pj[u] = PiPj[((size_t)b * N + jc) * 256 + 128 + c];
         wr[u] = WrelT[__float_as_int(relv[u]) * 128 + c];
       }
-      float t[4] = {0.f, 0.f, 0.f, 0.f};
+      // packed fp32x2 FMAs (two pixels per instruction, each lane an exact IEEE fma in the same k order as before)
+      float2 t[4] = {make_float2(0.f, 0.f), make_float2(0.f, 0.f), make_float2(0.f, 0.f), make_float2(0.f, 0.f)};
 #pragma unroll
       for (int k = 0; k < nbin + 4; ++k) {
-        const float4 f = *reinterpret_cast<const float4*>(&feat[k][jj]);
-        t[0] = fmaf(wt[k], f.x, t[0]); t[1] = fmaf(wt[k], f.y, t[1]); t[2] = fmaf(wt[k], f.z, t[2]); t[3] = fmaf(wt[k], f.w, t[3]);
+        const float4 f = *reinterpret_cast<const float4*>(&feat[k][jj]), g = *reinterpret_cast<const float4*>(&feat[k][jj + 4]);
+        t[0] = __ffma2_rn(wt2[k], make_float2(f.x, f.y), t[0]);
+        t[1] = __ffma2_rn(wt2[k], make_float2(f.z, f.w), t[1]);
+        t[2] = __ffma2_rn(wt2[k], make_float2(g.x, g.y), t[2]);
+        t[3] = __ffma2_rn(wt2[k], make_float2(g.z, g.w), t[3]);
       }
-      const float4 fs4 = *reinterpret_cast<const float4*>(&feat[nbin + 4][jj]);
-      const float4 same4 = *reinterpret_cast<const float4*>(&feat[nbin + 6][jj]);
-      const float4 pm4 = *reinterpret_cast<const float4*>(&feat[nbin + 7][jj]);
-      const float fsv[4] = {fs4.x, fs4.y, fs4.z, fs4.w};
-      const float samev[4] = {same4.x, same4.y, same4.z, same4.w}, pmv[4] = {pm4.x, pm4.y, pm4.z, pm4.w};
+      const float tv[8] = {t[0].x, t[0].y, t[1].x, t[1].y, t[2].x, t[2].y, t[3].x, t[3].y};
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
+      for (int u = 0; u < 8; ++u) {
         if (jj + u >= jn) break;
+        const float fsv = feat[nbin + 4][jj + u], samev = feat[nbin + 6][jj + u], pmv = feat[nbin + 7][jj + u];
         float acc = pi_c + pj[u];
         acc += wr[u];
-        acc = fmaf(samev[u], w_same, acc);
-        acc += t[u];
-        acc = fmaf(fsv[u], wt_fst, acc);
-        if (has_motif && fsv[u] != 0.f) {
+        acc = fmaf(samev, w_same, acc);
+        acc += tv[u];
+        acc = fmaf(fsv, wt_fst, acc);
+        if (has_motif && fsv != 0.f) {
           float m = 0.f;
           for (int k = 0; k < nbin; ++k) m = fmaf(WmT[k * 128 + c], mfeat[k][jj + u], m);
           acc += m + wm_fst;
         }
-        p[(row_i * N + j0 + jj + u) * 128 + c] = acc * pmv[u];
+        p[(row_i * N + j0 + jj + u) * 128 + c] = acc * pmv;
       }
     }
     __syncthreads();

@@ -536,28 +536,35 @@ __global__ void __launch_bounds__(IA_THREADS, 1) ipa_attention_tc_kernel(
 #pragma unroll
         for (int g = 0; g < G; ++g) out[g] = -3.0e38f;
         if (kv) {
-          float k[28];
+          // packed fp32x2 arithmetic: kk[0..7] = k (two components per register pair), kk[8..13] = -k_pts
+          float2 kk[14];
 #pragma unroll
           for (int e = 0; e < 7; ++e) {       // planes 0..3 = k, 4..6 = k_pts x / y / z: consecutive keys, consecutive 16-byte words
             const float4 t = kpl[(size_t)(h * IPA_PLANES_PER_HEAD + e) * N];
-            k[4 * e] = t.x; k[4 * e + 1] = t.y; k[4 * e + 2] = t.z; k[4 * e + 3] = t.w;
+            kk[2 * e] = e < 4 ? make_float2(t.x, t.y) : make_float2(-t.x, -t.y);
+            kk[2 * e + 1] = e < 4 ? make_float2(t.z, t.w) : make_float2(-t.z, -t.w);
           }
           const float gam = -0.5f * hw[h];
 #pragma unroll
           for (int g = 0; g < G; ++g) {
             const float4* q4 = reinterpret_cast<const float4*>(qs + (g * 12 + h) * 28);
-            float qk = 0.f, d2 = 0.f;
+            float2 qk = make_float2(0.f, 0.f), d2 = make_float2(0.f, 0.f);
 #pragma unroll
-            for (int e = 0; e < 4; ++e) { const float4 t = q4[e]; qk = fmaf(t.x, k[4 * e], qk); qk = fmaf(t.y, k[4 * e + 1], qk); qk = fmaf(t.z, k[4 * e + 2], qk); qk = fmaf(t.w, k[4 * e + 3], qk); }
+            for (int e = 0; e < 4; ++e) {
+              const float4 t = q4[e];
+              qk = __ffma2_rn(make_float2(t.x, t.y), kk[2 * e], qk);
+              qk = __ffma2_rn(make_float2(t.z, t.w), kk[2 * e + 1], qk);
+            }
 #pragma unroll
             for (int e = 4; e < 7; ++e) {
               const float4 t = q4[e];
-              const float dx = t.x - k[4 * e], dy = t.y - k[4 * e + 1], dz = t.z - k[4 * e + 2], dw = t.w - k[4 * e + 3];
-              d2 = fmaf(dx, dx, d2); d2 = fmaf(dy, dy, d2); d2 = fmaf(dz, dz, d2); d2 = fmaf(dw, dw, d2);
+              const float2 da = __fadd2_rn(make_float2(t.x, t.y), kk[2 * e]), db = __fadd2_rn(make_float2(t.z, t.w), kk[2 * e + 1]);
+              d2 = __ffma2_rn(da, da, d2);
+              d2 = __ffma2_rn(db, db, d2);
             }
             float pb = 0.f;
             if (g < ng) pb = pbias[((rowb + i0 + g) * 12 + h) * Np + j];
-            out[g] = qk + pb + gam * d2;
+            out[g] = (qk.x + qk.y) + pb + gam * (d2.x + d2.y);
           }
         }
         p_store<G>(P + ((size_t)h * Np + j) * G, out);
@@ -640,9 +647,9 @@ __global__ void __launch_bounds__(IA_THREADS, 1) ipa_attention_tc_kernel(
     for (int t = warp - 2; t < 120; t += IA_THREADS / 32 - 2) {       // one value plane per pass, 8 key loads in flight together
       const int h = t / 10, ev = t - h * 10;
       const float4* src = vpl + (size_t)(h * IPA_PLANES_PER_HEAD + 7 + ev) * N;
-      float acc[G][4];
+      float2 acc[G / 2][4];        // {query 2 gp, query 2 gp + 1} x value component e
 #pragma unroll
-      for (int g = 0; g < G; ++g) acc[g][0] = acc[g][1] = acc[g][2] = acc[g][3] = 0.f;
+      for (int gp = 0; gp < G / 2; ++gp) acc[gp][0] = acc[gp][1] = acc[gp][2] = acc[gp][3] = make_float2(0.f, 0.f);
       for (int j0 = 0; j0 < N; j0 += 256) {
         float4 vv[8];
 #pragma unroll
@@ -657,10 +664,12 @@ __global__ void __launch_bounds__(IA_THREADS, 1) ipa_attention_tc_kernel(
             float av[G];
             p_load<G>(P + ((size_t)h * Np + j) * G, av);
             const float4 v = vv[u];
+            const float2 vx = make_float2(v.x, v.x), vy = make_float2(v.y, v.y), vz = make_float2(v.z, v.z), vw = make_float2(v.w, v.w);
 #pragma unroll
-            for (int g = 0; g < G; ++g) {
-              acc[g][0] = fmaf(av[g], v.x, acc[g][0]); acc[g][1] = fmaf(av[g], v.y, acc[g][1]);
-              acc[g][2] = fmaf(av[g], v.z, acc[g][2]); acc[g][3] = fmaf(av[g], v.w, acc[g][3]);
+            for (int gp = 0; gp < G / 2; ++gp) {        // two queries per packed FMA: their probabilities are adjacent in P
+              const float2 a2 = make_float2(av[2 * gp], av[2 * gp + 1]);
+              acc[gp][0] = __ffma2_rn(a2, vx, acc[gp][0]); acc[gp][1] = __ffma2_rn(a2, vy, acc[gp][1]);
+              acc[gp][2] = __ffma2_rn(a2, vz, acc[gp][2]); acc[gp][3] = __ffma2_rn(a2, vw, acc[gp][3]);
             }
           }
         }
@@ -671,9 +680,9 @@ __global__ void __launch_bounds__(IA_THREADS, 1) ipa_attention_tc_kernel(
         constexpr int NV = 4 * G;
         float a[NV];
 #pragma unroll
-        for (int g = 0; g < G; ++g)
+        for (int gp = 0; gp < G / 2; ++gp)
 #pragma unroll
-          for (int e = 0; e < 4; ++e) a[4 * g + e] = acc[g][e];
+          for (int e = 0; e < 4; ++e) { a[8 * gp + e] = acc[gp][e].x; a[8 * gp + 4 + e] = acc[gp][e].y; }
         // lane distances 16 .. NV first (plain butterfly), then the trading steps NV / 2 .. 1: every value is summed over
         // the same tree (16, 8, 4, 2, 1) whatever G is, so the result does not depend on the queries-per-CTA choice
 #pragma unroll
