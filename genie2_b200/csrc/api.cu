@@ -267,6 +267,10 @@ extern "C" int gb_load_weights(gb_ctx* c, const gb_tensor* tensors, int n) {
   c->WtT = upload(c, transpose(wt, 128, d.template_dist_n_bin + 6));
   c->WmT = upload(c, transpose(wm, 128, d.template_dist_n_bin + 2));
   {
+    const int rc = tc_pack_pair_embed(c, wt, wm, d.template_dist_n_bin);
+    if (rc != GB_OK) return rc;
+  }
+  {
     const int T1 = d.n_timestep + 1, D = d.c_timestep_emb;
     float* X = nullptr;
     GB_CUDA(c, cudaMalloc(&X, (size_t)T1 * D * sizeof(float)));
@@ -689,11 +693,16 @@ extern "C" int gb_denoise(gb_ctx* c, const float* rots, const float* trans, cons
   sgemm_nt(st, c->s, cs, c->W_pipj, cs, nullptr, nullptr, 0, c->pipj, 256, R, 256, cs, false);
   GB_LAUNCH_CHECK(c, "pair_pipj");
   const int W = c->shard_world, rows_l = N / W, row0 = c->shard_rank * rows_l;   // W == 1: all rows
+  static const int pe_tc = [] { const char* e = getenv("GB_PE_TC"); return e ? atoi(e) : 1; }();
+  if (pe_tc && c->precision == GB_PREC_BF16 && tc_pair_embed_supported(c)) {
+    if ((rc = tc_pair_embed(c, aux ? aux->quat_follow : nullptr, rows_l, row0, st))) return rc;
+  } else {
   pair_embed_kernel<37><<<dim3(rows_l, B), 128, 0, st>>>(c->p, c->pipj, c->rots_w, c->trans_w, c->residue_index, c->chain_index, c->mask,
                                                     c->fsm, c->fst, c->motif_pos, c->WrelT, c->WtT, c->WmT,
                                                     aux ? aux->quat_follow : nullptr, N, d.relpos_k, d.template_dist_min,
                                                     d.template_dist_step, c->has_motif, row0);
   GB_LAUNCH_CHECK(c, "pair_embed");
+  }
   // PairTransformNet
   for (int l = 0; l < d.n_pair_transform_layer; ++l) {
     if (d.include_mul_update) {

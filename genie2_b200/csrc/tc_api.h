@@ -30,6 +30,11 @@ int tc_trimul_stage(gb_ctx* c, const TriMulW& w, bool outgoing, int stage, float
 // p = (p + PairTransition(p)) * mask
 int tc_pair_transition(gb_ctx* c, const TransitionW& w, float* p, cudaStream_t st);
 
+// ---- pair embedding on tensor cores (tc_embed.cu); wt [128][nbin + 6], wm [128][nbin + 2] as in the state dict
+int tc_pack_pair_embed(gb_ctx* c, const std::vector<float>& wt, const std::vector<float>& wm, int nbin);
+bool tc_pair_embed_supported(const gb_ctx* c);
+int tc_pair_embed(gb_ctx* c, const float* quat_follow, int rows, int row0, cudaStream_t st);
+
 // ---- structure network on tensor cores (tc_struct.cu)
 int tc_struct_init(gb_ctx* c);
 bool tc_struct_supported(const gb_ctx* c, int N);

@@ -24,6 +24,8 @@ struct TcState {
   bf16 *s_img = nullptr, *cat_img = nullptr, *ln1_img = nullptr, *h1_img = nullptr, *h2_img = nullptr;
   bf16* z_img = nullptr;             // [B][N][2][Np][64]
   float* pbias = nullptr;            // [L][B][N][12][Np]
+  bf16* Wfeat_img = nullptr;         // pair embedding: [2 kb][128 ch][64 k] (tc_embed.cu)
+  float* wfst = nullptr;             // [2][128]
   bf16* Wb_img = nullptr;            // [2][96][64]  rows l*12+h, scaled by sqrt(1/3)
   float* bias96 = nullptr;
   std::vector<TcStructW> st;
