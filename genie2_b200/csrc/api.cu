@@ -263,6 +263,10 @@ extern "C" int gb_load_weights(gb_ctx* c, const gb_tensor* tensors, int n) {
   if (!G.ok) return gb_fail(c, GB_ERR_MISSING, "gb_load_weights: missing tensor %s", G.missing.c_str());
   c->W_single = upload(c, ws);
   c->W_pipj = upload(c, concat({&wi, &wj}));
+  {
+    const int rc = tc_pack_pipj(c, concat({&wi, &wj}));
+    if (rc != GB_OK) return rc;
+  }
   c->WrelT = upload(c, transpose(wr, 128, 2 * d.relpos_k + 3));
   c->WtT = upload(c, transpose(wt, 128, d.template_dist_n_bin + 6));
   c->WmT = upload(c, transpose(wm, 128, d.template_dist_n_bin + 2));
@@ -690,8 +694,13 @@ extern "C" int gb_denoise(gb_ctx* c, const float* rots, const float* trans, cons
   if (aux && aux->s) GB_CUDA(c, cudaMemcpyAsync(aux->s, c->s, Rcs * 4, cudaMemcpyDeviceToDevice, st));
   if (aux && aux->states) GB_CUDA(c, cudaMemcpyAsync(aux->states, c->s, Rcs * 4, cudaMemcpyDeviceToDevice, st));
   // PairFeatureNet
-  sgemm_nt(st, c->s, cs, c->W_pipj, cs, nullptr, nullptr, 0, c->pipj, 256, R, 256, cs, false);
-  GB_LAUNCH_CHECK(c, "pair_pipj");
+  static const int pipj_tc = [] { const char* e = getenv("GB_PIPJ_TC"); return e ? atoi(e) : 1; }();
+  if (pipj_tc && c->precision == GB_PREC_BF16 && tc_struct_supported(c, N) && tc_pipj_supported(c)) {
+    if ((rc = tc_pair_pipj(c, st))) return rc;
+  } else {
+    sgemm_nt(st, c->s, cs, c->W_pipj, cs, nullptr, nullptr, 0, c->pipj, 256, R, 256, cs, false);
+    GB_LAUNCH_CHECK(c, "pair_pipj");
+  }
   const int W = c->shard_world, rows_l = N / W, row0 = c->shard_rank * rows_l;   // W == 1: all rows
   static const int pe_tc = [] { const char* e = getenv("GB_PE_TC"); return e ? atoi(e) : 1; }();
   if (pe_tc && c->precision == GB_PREC_BF16 && tc_pair_embed_supported(c)) {

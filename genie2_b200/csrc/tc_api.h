@@ -35,6 +35,11 @@ int tc_pack_pair_embed(gb_ctx* c, const std::vector<float>& wt, const std::vecto
 bool tc_pair_embed_supported(const gb_ctx* c);
 int tc_pair_embed(gb_ctx* c, const float* quat_follow, int rows, int row0, cudaStream_t st);
 
+// Pi | Pj = s . [W_i | W_j]^T on tensor cores (tc_struct.cu); leaves the operand image of s for the structure net
+int tc_pack_pipj(gb_ctx* c, const std::vector<float>& wij);
+bool tc_pipj_supported(const gb_ctx* c);
+int tc_pair_pipj(gb_ctx* c, cudaStream_t st);
+
 // ---- structure network on tensor cores (tc_struct.cu)
 int tc_struct_init(gb_ctx* c);
 bool tc_struct_supported(const gb_ctx* c, int N);

@@ -24,6 +24,8 @@ struct TcState {
   bf16 *s_img = nullptr, *cat_img = nullptr, *ln1_img = nullptr, *h1_img = nullptr, *h2_img = nullptr;
   bf16* z_img = nullptr;             // [B][N][2][Np][64]
   float* pbias = nullptr;            // [L][B][N][12][Np]
+  bf16* Wpipj_img = nullptr;         // [c_s/64][256][64]: [W_i | W_j] of the pair feature net
+  bool s_img_valid = false;          // s_img holds the image of the current single features (set by tc_pair_pipj)
   bf16* Wfeat_img = nullptr;         // pair embedding: [2 kb][128 ch][64 k] (tc_embed.cu)
   float* wfst = nullptr;             // [2][128]
   bf16* Wb_img = nullptr;            // [2][96][64]  rows l*12+h, scaled by sqrt(1/3)

@@ -244,6 +244,31 @@ __global__ void ln_img_kernel(const float* __restrict__ in, float* __restrict__ 
 }
 
 // ---------------------------------------------------------------------------------------------
+// split_img_kernel: fp32 rows [R, C] -> three bf16 operand images hi | lo | hi (hi = bf16(x), lo = bf16(x - hi)) in
+// three consecutive [C/64][Rp][64] buffers.  Against a weight image [W_hi | W_hi | W_lo] one GEMM of K = 3 C computes
+// x_hi W_hi + x_lo W_hi + x_hi W_lo: the product to ~2^-16 relative, from bf16 tensor-core passes.  One warp per row.
+// ---------------------------------------------------------------------------------------------
+__global__ void split_img_kernel(const float* __restrict__ in, bf16* __restrict__ img, int R, int C, int Rp, size_t stride /*elements between the three images*/) {
+  const int row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  pdl_wait();
+  pdl_launch();
+  if (row >= R) return;
+  for (int c = lane * 4; c < C; c += 128) {
+    const float4 v = ld4(in + (size_t)row * C + c);
+    uint2 hi, lo;
+    hi.x = pack_bf16(v.x, v.y);
+    hi.y = pack_bf16(v.z, v.w);
+    lo.x = pack_bf16(v.x - __uint_as_float(hi.x << 16), v.y - __uint_as_float(hi.x & 0xffff0000u));
+    lo.y = pack_bf16(v.z - __uint_as_float(hi.y << 16), v.w - __uint_as_float(hi.y & 0xffff0000u));
+    uint8_t* dst = reinterpret_cast<uint8_t*>(img + ((size_t)(c >> 6) * Rp + row) * 64) +
+                   (((uint32_t)((c & 63) >> 3) ^ ((uint32_t)row & 7u)) << 4) + ((c & 7) >> 2) * 8;
+    *reinterpret_cast<uint2*>(dst) = hi;
+    *reinterpret_cast<uint2*>(dst + stride * 2) = lo;
+    *reinterpret_cast<uint2*>(dst + stride * 4) = hi;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
 // ipa_prep_tc_kernel (once per denoiser eval, after the pair stack).  p does not change across the
 // structure layers, so for all layers l at once:
 //   pbias[l][b][i][h][j] = sqrt(1/3) * (linear_b_l(z_ij)[h]) + 1e5 * (m_i m_j - 1)
@@ -853,6 +878,47 @@ static int gemm_img(gb_ctx* c, cudaStream_t st, const bf16* A, int K, const bf16
   return GB_OK;
 }
 
+// PairFeatureNet's two projections of s (pair_feature_net.py:117-121): pipj[R][256] = s . [W_i | W_j]^T as one tensor-core
+// GEMM with split-bf16 operands (these two terms carry most of the embedding; plain bf16 operands cost 25 % more error in
+// p and pushed the L = 1024 z error past its gate).  Also leaves the bf16 operand image of s in s_img, which is what the structure net starts from (s does not
+// change through the pair stack), so tc_structure_net skips its own conversion.
+int tc_pack_pipj(gb_ctx* c, const std::vector<float>& wij /*[256][c_s]*/) {
+  TcState* s = static_cast<TcState*>(c->tc_state);
+  const int cs = c->d.c_s;
+  s->Wpipj_img = nullptr;
+  if (cs % 64 != 0) return GB_OK;
+  // [W_hi | W_hi | W_lo] along K (see split_img_kernel)
+  std::vector<uint16_t> img((size_t)256 * 3 * cs);
+  pack_image(img.data(), 256, 3 * cs, [&](int r, int k) -> float {
+    const float w = wij[(size_t)r * cs + k % cs];
+    if (k < 2 * cs) return w;
+    const uint32_t bits = (uint32_t)f2bf(w) << 16;
+    float hi;
+    memcpy(&hi, &bits, 4);
+    return w - hi;
+  });
+  s->Wpipj_img = (bf16*)upload_bytes(c, img.data(), img.size() * 2);
+  if (!s->Wpipj_img) return gb_fail(c, GB_ERR_CUDA, "tc_pack_pipj: device allocation failed");
+  return GB_OK;
+}
+
+bool tc_pipj_supported(const gb_ctx* c) {
+  const TcState* s = static_cast<const TcState*>(c->tc_state);
+  return s && s->Rp && s->Wpipj_img && s->s_img && (size_t)(s->ln1_img - s->s_img) == (size_t)(c->d.c_s / 64) * s->Rp * 64 &&
+         (size_t)(s->h1_img - s->ln1_img) == (size_t)(c->d.c_s / 64) * s->Rp * 64;
+}
+
+int tc_pair_pipj(gb_ctx* c, cudaStream_t st) {
+  TcState* s = static_cast<TcState*>(c->tc_state);
+  const int R = c->B * c->N, cs = c->d.c_s;
+  // s_img | ln1_img | h1_img are consecutive buffers of one image each and the last two are free at this point of the eval
+  const size_t stride = (size_t)(s->ln1_img - s->s_img);
+  launch_pdl(split_img_kernel, (unsigned)((R * 32 + 255) / 256), 256, 0, st, (const float*)c->s, s->s_img, R, cs, s->Rp, stride);
+  GB_LAUNCH_CHECK(c, "s_split_img");
+  s->s_img_valid = true;
+  return gemm_img(c, st, s->s_img, 3 * cs, s->Wpipj_img, 256, nullptr, nullptr, 0, c->pipj, 256, nullptr, false);
+}
+
 // StructureNet.forward (structure_net.py:189-243) on c->s / c->p / c->rots_w / c->trans_w, bf16 mode.
 int tc_structure_net(gb_ctx* c, float* states_out, cudaStream_t st) {
   TcState* s = static_cast<TcState*>(c->tc_state);
@@ -871,8 +937,11 @@ int tc_structure_net(gb_ctx* c, float* states_out, cudaStream_t st) {
                                                      d.n_structure_layer * IPA_H, tr);
   GB_LAUNCH_CHECK(c, "ipa_prep_tc");
   const unsigned lnb = (unsigned)((R * 32 + 255) / 256);
-  launch_pdl(ln_img_kernel, lnb, 256, 0, st, c->s, nullptr, nullptr, s->s_img, nullptr, nullptr, R, cs, Rp, 0, nullptr, nullptr, nullptr, nullptr);
-  GB_LAUNCH_CHECK(c, "s_to_img");
+  if (!s->s_img_valid) {      // already made by tc_pair_pipj of this eval
+    launch_pdl(ln_img_kernel, lnb, 256, 0, st, c->s, nullptr, nullptr, s->s_img, nullptr, nullptr, R, cs, Rp, 0, nullptr, nullptr, nullptr, nullptr);
+    GB_LAUNCH_CHECK(c, "s_to_img");
+  }
+  s->s_img_valid = false;
   int state_idx = 1;
   for (int blk = 0; blk < d.n_structure_block; ++blk)
     for (int l = 0; l < d.n_structure_layer; ++l) {
