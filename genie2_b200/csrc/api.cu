@@ -802,10 +802,14 @@ extern "C" int gb_sample_loop(gb_ctx* c, float* trans_inout, float* rots_inout, 
   // the legacy default stream, which cannot capture); replays go to the caller's stream.  GB_STEP_GRAPH=0 keeps the plain
   // launch loop (also used for row-sharded runs: NCCL calls stay outside graphs here).
   static const int graph_mode = [] { const char* e = getenv("GB_STEP_GRAPH"); return e ? atoi(e) : 1; }();
-  if (graph_mode && c->shard_world == 1 && t_start - t_end + 1 >= 3) {
-    gb_ctx::StepKey key;
-    key.trans = trans_inout; key.rots = rots_inout; key.tape = noise_tape; key.scale = scale; key.seed = seed;
-    key.epoch = c->epoch; key.precision = c->precision;
+  // Short calls (one step per call, as the host-buffer entry point gb_sample_host is typically driven) use the graph
+  // from the second call with the same arguments on: a capture costs about as much as launching the step once.
+  gb_ctx::StepKey key;
+  key.trans = trans_inout; key.rots = rots_inout; key.tape = noise_tape; key.scale = scale; key.seed = seed;
+  key.epoch = c->epoch; key.precision = c->precision;
+  const bool repeated = key == c->last_key;
+  c->last_key = key;
+  if (graph_mode && c->shard_world == 1 && (t_start - t_end + 1 >= 3 || repeated)) {
     if (!c->step_graph || !(key == c->step_key)) {
       if (c->step_graph) cudaGraphExecDestroy((cudaGraphExec_t)c->step_graph);
       c->step_graph = nullptr;

@@ -96,7 +96,7 @@ struct gb_ctx {
     bool operator==(const StepKey& o) const {
       return trans == o.trans && rots == o.rots && tape == o.tape && scale == o.scale && seed == o.seed && epoch == o.epoch && precision == o.precision;
     }
-  } step_key;
+  } step_key, last_key;                            // key of the captured graph / of the previous gb_sample_loop call
   uint64_t epoch = 0;                              // bumped by everything that invalidates a captured step (features, weights, schedule, sharding)
   void* tape_alloc = nullptr;
   size_t tape_bytes = 0;
