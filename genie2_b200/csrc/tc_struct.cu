@@ -279,7 +279,7 @@ __global__ void split_img_kernel(const float* __restrict__ in, bf16* __restrict_
 // ---------------------------------------------------------------------------------------------
 #define PREP_SMEM (32768 + 24576 + 1024 + 64)
 
-__global__ void __launch_bounds__(256, 2) ipa_prep_tc_kernel(const float* __restrict__ p, int B, int N, int Np,
+__global__ void __launch_bounds__(256, 3) ipa_prep_tc_kernel(const float* __restrict__ p, int B, int N, int Np,
                                                              const int* __restrict__ rmask, const bf16* __restrict__ Wimg,
                                                              const float* __restrict__ bias96, float* __restrict__ pbias,
                                                              bf16* __restrict__ z_img, int ncol, const TileRange tr) {
