@@ -132,8 +132,8 @@ def run_reference(args):
 
 # ------------------------------------------------------------------------------- clocks
 class ClockSampler:
-    """nvidia-smi clocks/throttle reasons sampled every 200 ms during the timed region."""
-    Q = ('clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,'
+    """nvidia-smi clocks/throttle reasons sampled every 25 ms during the warm-up and timed steps."""
+    Q = ('timestamp,clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,'
          'clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap')
 
     def __init__(self, index):
@@ -141,11 +141,13 @@ class ClockSampler:
         self.p = None
         try:
             self.p = subprocess.Popen(['nvidia-smi', '-i', str(index), '--query-gpu=' + self.Q,
-                                       '--format=csv,noheader,nounits', '-lms', '200'], stdout=self.f, stderr=subprocess.DEVNULL)
+                                       '--format=csv,noheader,nounits', '-lms', '25'], stdout=self.f, stderr=subprocess.DEVNULL)
         except OSError:
             pass
 
-    def stop(self):
+    def stop(self, t0=None, t1=None):
+        """Median SM clock and throttle reasons of the samples whose nvidia-smi timestamp lies inside [t0, t1]
+        (time.time() values bracketing the timed region); all samples if none does (said in 'window')."""
         if self.p is None:
             return {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': ['nvidia-smi unavailable']}
         self.p.terminate()
@@ -156,21 +158,23 @@ class ClockSampler:
         self.f.flush()
         rows = [r.strip().split(', ') for r in open(self.f.name) if r.strip()]
         os.unlink(self.f.name)
-        sm, mx, reasons = [], None, set()
+        import datetime
         names = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
+        parsed = []
         for r in rows:
-            if len(r) < 6:
+            if len(r) < 7:
                 continue
             try:
-                sm.append(float(r[0]))
-                mx = float(r[1])
+                ts = datetime.datetime.strptime(r[0].strip(), '%Y/%m/%d %H:%M:%S.%f').timestamp()
+                parsed.append((ts, float(r[1]), float(r[2]), [n for n, v in zip(names, r[3:7]) if v.strip().lower().startswith('active')]))
             except ValueError:
                 continue
-            for nme, v in zip(names, r[2:6]):
-                if v.strip().lower().startswith('active'):
-                    reasons.add(nme)
-        sm.sort()
-        return {'sm_mhz': sm[len(sm) // 2] if sm else None, 'sm_max_mhz': mx, 'reasons': sorted(reasons), 'samples': len(sm)}
+        inside = [q for q in parsed if t0 is not None and t1 is not None and t0 - 0.02 <= q[0] <= t1 + 0.02]
+        use, window = (inside, 'timed region') if inside else (parsed, 'whole run (no sample fell inside the timed region)')
+        sm = sorted(q[1] for q in use)
+        reasons = sorted({n for q in use for n in q[3]})
+        return {'sm_mhz': sm[len(sm) // 2] if sm else None, 'sm_max_mhz': use[-1][2] if use else None, 'reasons': reasons,
+                'samples': len(sm), 'window': window}
 
 
 # ------------------------------------------------------------------------------- B200 arm
@@ -287,6 +291,7 @@ def run_b200(args):
     if K + W_ > T_STEPS:
         raise SystemExit('steps + warmup must be <= %d' % T_STEPS)
 
+    clocks = ClockSampler(local)      # started now: nvidia-smi delivers its first line after a few hundred milliseconds
     lib = _lib.load()
     cfg = O.OracleConfig()
     sd = W.make_state_dict(cfg, 0, 'activated')
@@ -313,19 +318,20 @@ def run_b200(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    # ---- device-resident throughput
+    # ---- device-resident throughput (clock samples are kept by their timestamps: only those inside the timed region count)
     loop(T_STEPS, W_)
     barrier()
-    clocks = ClockSampler(local)
+    wall0 = time.time()
     l0 = genie.model.launch_count()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     loop(T_STEPS - W_, K)
     e1.record()
     barrier()
+    wall1 = time.time()
     launches = genie.model.launch_count() - l0
     ms = e0.elapsed_time(e1)
-    clk = clocks.stop()
+    clk = clocks.stop(wall0, wall1)
     finite = bool(torch.isfinite(x).all())
 
     # ---- end to end through host buffers: one gb_sample_host call per step
