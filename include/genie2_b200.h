@@ -137,7 +137,9 @@ int gb_p_sample(gb_ctx* ctx, float* trans_inout, float* rots_inout, const float*
 
 /* steps t_start, t_start-1, ..., t_end (inclusive) of the loop at base.py:236-282,
  * no host synchronisation inside.  noise_tape NULL or [n_timestep+1,B,N,3] with
- * tape[t] the draw used at step t. */
+ * tape[t] the draw used at step t.  Three or more steps, or a repeated call with the same
+ * arguments, replay ONE captured step as a CUDA graph on `stream` (the step index lives in
+ * device memory); results are bit-identical to launching kernel by kernel (GB_STEP_GRAPH=0). */
 int gb_sample_loop(gb_ctx* ctx, float* trans_inout, float* rots_inout, int t_start, int t_end,
                    float scale, const float* noise_tape, uint64_t seed, void* stream);
 
