@@ -9,8 +9,9 @@ import os
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, 'libgenie2_b200.so')
 
-GB_PREC_FP32, GB_PREC_TF32, GB_PREC_BF16 = 0, 1, 2
-PRECISIONS = {'fp32': GB_PREC_FP32, 'tf32': GB_PREC_TF32, 'bf16': GB_PREC_BF16}
+GB_PREC_FP32, GB_PREC_BF16X3, GB_PREC_BF16 = 0, 1, 2
+GB_PREC_TF32 = GB_PREC_BF16X3          # old name of the slot (include/genie2_b200.h)
+PRECISIONS = {'fp32': GB_PREC_FP32, 'bf16x3': GB_PREC_BF16X3, 'tf32': GB_PREC_BF16X3, 'bf16': GB_PREC_BF16}
 
 
 class gb_dims(C.Structure):

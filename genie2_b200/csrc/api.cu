@@ -19,6 +19,17 @@
 
 static std::string g_create_err;
 
+// Selects the context's device for the duration of an entry point and restores the caller's current device afterwards,
+// so that two contexts on different GPUs can be driven from one host thread.
+struct DeviceGuard {
+  int prev = -1;
+  bool changed = false;
+  explicit DeviceGuard(int dev) {
+    if (cudaGetDevice(&prev) == cudaSuccess && prev != dev) changed = cudaSetDevice(dev) == cudaSuccess;
+  }
+  ~DeviceGuard() { if (changed) cudaSetDevice(prev); }
+};
+
 int gb_fail(const gb_ctx* ctx, int code, const char* fmt, ...) {
   char buf[1024];
   va_list ap;
@@ -60,7 +71,7 @@ extern "C" int gb_create(gb_ctx** out, const gb_dims* d, int device) {
     return gb_fail(nullptr, GB_ERR_UNSUPPORTED, "triangle attention must be 4 heads x 32");
   if (d->c_s % 4 != 0 || d->c_s > 1024) return gb_fail(nullptr, GB_ERR_UNSUPPORTED, "c_s must be a multiple of 4, <= 1024");
   if (d->rescale == 0.f) return gb_fail(nullptr, GB_ERR_INVALID, "rescale must be non-zero");
-  if (cudaSetDevice(device) != cudaSuccess) return gb_fail(nullptr, GB_ERR_CUDA, "cudaSetDevice failed");
+  DeviceGuard dg(device);
   gb_ctx* c = new gb_ctx();
   c->d = *d;
   c->device = device;
@@ -96,7 +107,7 @@ static void free_features(gb_ctx* c) {
 
 extern "C" void gb_destroy(gb_ctx* c) {
   if (!c) return;
-  cudaSetDevice(c->device);
+  DeviceGuard dg(c->device);
   shard_destroy(c);
   tc_destroy(c);
   free_features(c);
@@ -233,11 +244,14 @@ static int pack_triatt(gb_ctx* c, Getter& G, const std::string& pre, TriAttW& w)
 
 extern "C" int gb_load_weights(gb_ctx* c, const gb_tensor* tensors, int n) {
   if (!c || !tensors || n <= 0) return gb_fail(c, GB_ERR_INVALID, "gb_load_weights: bad arguments");
-  GB_CUDA(c, cudaSetDevice(c->device));
+  DeviceGuard dg(c->device);
   for (void* p : c->weight_allocs) cudaFree(p);
   c->weight_allocs.clear();
   c->host.clear();
   c->weights_loaded = false;
+  // s_static (gb_set_features) is W_single . static features of the weights loaded at that time: a re-bind is required
+  c->features_set = false;
+  drop_step_graph(c);
   for (int i = 0; i < n; ++i) {
     const gb_tensor& t = tensors[i];
     if (!t.name || !t.data || t.ndim < 1 || t.ndim > 4) return gb_fail(c, GB_ERR_INVALID, "gb_load_weights: tensor %d malformed", i);
@@ -378,7 +392,7 @@ extern "C" int gb_load_weights(gb_ctx* c, const gb_tensor* tensors, int n) {
 extern "C" int gb_set_schedule(gb_ctx* c, const float* alphas, const float* sqrt_alphas, const float* sqrt_omac,
                                const float* sqrt_betas) {
   if (!c || !alphas || !sqrt_alphas || !sqrt_omac || !sqrt_betas) return gb_fail(c, GB_ERR_INVALID, "gb_set_schedule: NULL argument");
-  GB_CUDA(c, cudaSetDevice(c->device));
+  DeviceGuard dg(c->device);
   const size_t n = (size_t)c->d.n_timestep + 1;
   if (!c->alphas) {
     float* base = nullptr;
@@ -465,7 +479,7 @@ extern "C" int gb_set_features(gb_ctx* c, const gb_features* f) {
   if (c->shard_world > 1 && (f->B != 1 || f->N % (128 * c->shard_world) != 0))
     return gb_fail(c, GB_ERR_UNSUPPORTED, "row sharding over %d GPUs needs B == 1 and N a multiple of %d (got B = %d, N = %d)",
                    c->shard_world, 128 * c->shard_world, f->B, f->N);
-  GB_CUDA(c, cudaSetDevice(c->device));
+  DeviceGuard dg(c->device);
   const int B = f->B, N = f->N;
   if (!c->features_set || B != c->B || N != c->N) {
     GB_CUDA(c, cudaDeviceSynchronize());
@@ -657,6 +671,7 @@ extern "C" int gb_frenet(gb_ctx* c, const float* trans, float* rots_out, void* s
   int rc = check_ready(c, "gb_frenet");
   if (rc) return rc;
   if (!trans || !rots_out) return gb_fail(c, GB_ERR_INVALID, "gb_frenet: NULL pointer");
+  DeviceGuard dg(c->device);
   const size_t smem = (size_t)c->N * 13 * 4;
   frenet_kernel<<<c->B, 256, smem, (cudaStream_t)stream>>>(trans, c->chain_index, c->mask, c->N, rots_out);
   GB_LAUNCH_CHECK(c, "frenet");
@@ -682,6 +697,7 @@ extern "C" int gb_denoise(gb_ctx* c, const float* rots, const float* trans, cons
   if (!rots || !trans || !timesteps || !z_out) return gb_fail(c, GB_ERR_INVALID, "gb_denoise: NULL pointer");
   if (c->shard_world > 1 && c->precision != GB_PREC_BF16)
     return gb_fail(c, GB_ERR_UNSUPPORTED, "row sharding is built for the tensor-core (bf16) pair stack only");
+  DeviceGuard dg(c->device);
   cudaStream_t st = (cudaStream_t)stream;
   const gb_dims& d = c->d;
   const int B = c->B, N = c->N, R = B * N, cs = d.c_s;
@@ -783,6 +799,7 @@ extern "C" int gb_p_sample(gb_ctx* c, float* trans_inout, float* rots_inout, con
   if (!c->schedule_set) return gb_fail(c, GB_ERR_INVALID, "gb_p_sample: schedule not set");
   if (!trans_inout || !rots_inout || !z) return gb_fail(c, GB_ERR_INVALID, "gb_p_sample: NULL pointer");
   if (step < 1 || step > c->d.n_timestep) return gb_fail(c, GB_ERR_INVALID, "gb_p_sample: step %d outside [1, %d]", step, c->d.n_timestep);
+  DeviceGuard dg(c->device);
   return launch_ddpm(c, trans_inout, rots_inout, z, step, scale, noise, 0, seed, (cudaStream_t)stream);
 }
 
@@ -794,6 +811,7 @@ extern "C" int gb_sample_loop(gb_ctx* c, float* trans_inout, float* rots_inout, 
   if (!trans_inout || !rots_inout) return gb_fail(c, GB_ERR_INVALID, "gb_sample_loop: NULL pointer");
   if (t_end < 1 || t_start > c->d.n_timestep || t_start < t_end)
     return gb_fail(c, GB_ERR_INVALID, "gb_sample_loop: bad step range [%d, %d]", t_start, t_end);
+  DeviceGuard dg(c->device);
   cudaStream_t st = (cudaStream_t)stream;
   const size_t stride = (size_t)c->B * c->N * 3;
   // Three or more steps on one GPU: capture ONE step (its ~105 launches, programmatic-dependent-launch edges included) as
@@ -821,7 +839,7 @@ extern "C" int gb_sample_loop(gb_ctx* c, float* trans_inout, float* rots_inout, 
       }
       cudaStream_t cs = (cudaStream_t)c->cap_stream;
       GB_CUDA(c, cudaStreamBeginCapture(cs, cudaStreamCaptureModeThreadLocal));
-      step_begin_kernel<<<1, 256, 0, cs>>>(c->t_dev, c->step_dev, c->B);
+      step_begin_kernel<<<(c->B + 255) / 256, 256, 0, cs>>>(c->t_dev, c->step_dev, c->B);
       rc = cudaGetLastError() == cudaSuccess ? GB_OK : gb_fail(c, GB_ERR_CUDA, "step_begin launch failed during capture");
       c->launches++;
       if (rc == GB_OK) rc = gb_denoise(c, rots_inout, trans_inout, c->t_dev, c->z, nullptr, cs);
@@ -852,7 +870,7 @@ extern "C" int gb_sample_loop(gb_ctx* c, float* trans_inout, float* rots_inout, 
     return GB_OK;
   }
   for (int step = t_start; step >= t_end; --step) {
-    fill_int_kernel<<<1, 256, 0, st>>>(c->t_dev, step, c->B);
+    fill_int_kernel<<<(c->B + 255) / 256, 256, 0, st>>>(c->t_dev, step, c->B);
     GB_LAUNCH_CHECK(c, "fill_timesteps");
     if ((rc = gb_denoise(c, rots_inout, trans_inout, c->t_dev, c->z, nullptr, stream))) return rc;
     if ((rc = launch_ddpm(c, trans_inout, rots_inout, c->z, step, scale, noise_tape, noise_tape ? stride : 0, seed, st))) return rc;
@@ -865,7 +883,10 @@ extern "C" int gb_sample_host(gb_ctx* c, const float* x_T_host, float* x_out_hos
   int rc = check_ready(c, "gb_sample_host");
   if (rc) return rc;
   if (!x_T_host || !x_out_host) return gb_fail(c, GB_ERR_INVALID, "gb_sample_host: NULL pointer");
-  GB_CUDA(c, cudaSetDevice(c->device));
+  if (!c->schedule_set) return gb_fail(c, GB_ERR_INVALID, "gb_sample_host: schedule not set");
+  if (t_end < 1 || t_start > c->d.n_timestep || t_start < t_end)      // before any copy sized from the range
+    return gb_fail(c, GB_ERR_INVALID, "gb_sample_host: bad step range [%d, %d]", t_start, t_end);
+  DeviceGuard dg(c->device);
   const size_t stride = (size_t)c->B * c->N * 3;
   cudaStream_t st = 0;
   GB_CUDA(c, cudaMemcpyAsync(c->trans_io, x_T_host, stride * 4, cudaMemcpyHostToDevice, st));
@@ -894,6 +915,7 @@ extern "C" int gb_sample_host(gb_ctx* c, const float* x_T_host, float* x_out_hos
 extern "C" int gb_k_trimul(gb_ctx* c, int layer, int outgoing, float* p, void* stream) {
   int rc = check_ready(c, "gb_k_trimul");
   if (rc) return rc;
+  DeviceGuard dg(c->device);
   if (!p || layer < 0 || layer >= c->d.n_pair_transform_layer || !c->d.include_mul_update) return gb_fail(c, GB_ERR_INVALID, "gb_k_trimul: bad arguments");
   return run_trimul(c, outgoing ? c->pair[layer].mul_out : c->pair[layer].mul_in, outgoing != 0, p, (cudaStream_t)stream);
 }
@@ -901,6 +923,7 @@ extern "C" int gb_k_trimul(gb_ctx* c, int layer, int outgoing, float* p, void* s
 extern "C" int gb_k_trimul_stage(gb_ctx* c, int layer, int outgoing, int stage, float* p, void* stream) {
   int rc = check_ready(c, "gb_k_trimul_stage");
   if (rc) return rc;
+  DeviceGuard dg(c->device);
   if (!p || layer < 0 || layer >= c->d.n_pair_transform_layer || !c->d.include_mul_update || stage < 1 || stage > 3)
     return gb_fail(c, GB_ERR_INVALID, "gb_k_trimul_stage: bad arguments");
   if (c->precision != GB_PREC_BF16) return gb_fail(c, GB_ERR_UNSUPPORTED, "gb_k_trimul_stage: tensor-core (bf16) mode only");
@@ -910,6 +933,7 @@ extern "C" int gb_k_trimul_stage(gb_ctx* c, int layer, int outgoing, int stage, 
 extern "C" int gb_k_pair_transition(gb_ctx* c, int layer, float* p, void* stream) {
   int rc = check_ready(c, "gb_k_pair_transition");
   if (rc) return rc;
+  DeviceGuard dg(c->device);
   if (!p || layer < 0 || layer >= c->d.n_pair_transform_layer) return gb_fail(c, GB_ERR_INVALID, "gb_k_pair_transition: bad arguments");
   return run_transition(c, c->pair[layer].tr, p, (cudaStream_t)stream);
 }
@@ -917,6 +941,7 @@ extern "C" int gb_k_pair_transition(gb_ctx* c, int layer, float* p, void* stream
 extern "C" int gb_k_tri_attention(gb_ctx* c, int layer, int starting, float* p, void* stream) {
   int rc = check_ready(c, "gb_k_tri_attention");
   if (rc) return rc;
+  DeviceGuard dg(c->device);
   if (!c->d.include_tri_att) return gb_fail(c, GB_ERR_INVALID, "gb_k_tri_attention: include_tri_att is off in this context");
   if (!p || layer < 0 || layer >= c->d.n_pair_transform_layer) return gb_fail(c, GB_ERR_INVALID, "gb_k_tri_attention: bad arguments");
   return run_triatt(c, starting ? c->pair[layer].att_start : c->pair[layer].att_end, starting != 0, p, (cudaStream_t)stream);
@@ -926,6 +951,7 @@ extern "C" int gb_k_ipa(gb_ctx* c, int layer, const float* s, const float* p, co
                         float* out, void* stream) {
   int rc = check_ready(c, "gb_k_ipa");
   if (rc) return rc;
+  DeviceGuard dg(c->device);
   if (!s || !p || !rots || !trans || !out || layer < 0 || layer >= c->d.n_structure_layer) return gb_fail(c, GB_ERR_INVALID, "gb_k_ipa: bad arguments");
   return run_ipa(c, c->st[layer], s, p, rots, trans, out, nullptr, (cudaStream_t)stream);
 }

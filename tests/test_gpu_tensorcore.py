@@ -120,6 +120,7 @@ def test_forward_bf16_vs_oracle_and_fp32_path():
     print('bf16 forward errors', errs)
     assert errs['s'] < 1e-4                       # single features do not touch the bf16 path
     assert errs['p'] < 2e-2
+    assert errs['states'] < TOL_Z_BF16            # (computed but never asserted before round 2)
     assert errs['z'] < TOL_Z_BF16
     model.set_precision('fp32')
     o32, _ = run_cuda_forward(model, rots, trans, ts, feats, None)
