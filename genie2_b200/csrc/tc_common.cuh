@@ -228,6 +228,32 @@ __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
   return *reinterpret_cast<uint32_t*>(&v);
 }
 
+// Split of fp32 values into bf16 hi + bf16 lo (GB_PREC_BF16X3): hi = bf16(v), lo = bf16(v - hi); v - hi is exact in fp32, so
+// hi + lo carries 16 mantissa bits and  x w ~ x_hi w_hi + x_lo w_hi + x_hi w_lo  to ~2^-16 of |x w|.
+__device__ __forceinline__ void split_bf16x2(float a, float b, uint32_t& hi, uint32_t& lo) {
+  hi = pack_bf16(a, b);
+  lo = pack_bf16(a - __uint_as_float(hi << 16), b - __uint_as_float(hi & 0xffff0000u));
+}
+// NS-way split (NS = 1, 2): component c = bf16 of what the components before it left over
+template <int NS>
+__device__ __forceinline__ void split_bf16x2_n(float a, float b, uint32_t (&c)[NS]) {
+#pragma unroll
+  for (int i = 0; i < NS; ++i) {
+    c[i] = pack_bf16(a, b);
+    a -= __uint_as_float(c[i] << 16);
+    b -= __uint_as_float(c[i] & 0xffff0000u);
+  }
+}
+// operand components (A, B) of pass i of an NS-way split product, largest terms first.  A third component was tried for the
+// structure net (six passes) and bought nothing: the fp32 accumulation of tcgen05.mma itself leaves ~1e-5 on a K = 2112
+// product, above the 2^-17 of the hi | lo operands.
+template <int NS> struct SplitPasses;
+template <> struct SplitPasses<1> { static constexpr int N = 1; __device__ static constexpr int a(int) { return 0; } __device__ static constexpr int b(int) { return 0; } };
+template <> struct SplitPasses<2> { static constexpr int N = 3; __device__ static constexpr int a(int i) { return i == 1 ? 1 : 0; } __device__ static constexpr int b(int i) { return i == 2 ? 1 : 0; } };
+__device__ __forceinline__ float2 unpack_bf16x2(uint32_t v) { return make_float2(__uint_as_float(v << 16), __uint_as_float(v & 0xffff0000u)); }
+// sigmoid to ~1e-6 relative (ex2.approx + rcp.approx): the split mode cannot use the 2^-11 tanh.approx of the bf16 mode
+__device__ __forceinline__ float sigmoid_acc(float x) { return __fdividef(1.f, 1.f + __expf(-x)); }
+
 // ------------------------------------------------------------------ kernel-side conveniences
 // dynamic shared memory base rounded up to 1024 bytes (SWIZZLE_128B atoms)
 __device__ __forceinline__ uint8_t* smem_base_1024(uint8_t* raw) {

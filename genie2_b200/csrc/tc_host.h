@@ -14,6 +14,15 @@ static uint16_t f2bf(float f) {   // round to nearest even
   return (uint16_t)(u >> 16);
 }
 
+static float bf_round(float f) {
+  const uint32_t b = (uint32_t)f2bf(f) << 16;
+  float r;
+  memcpy(&r, &b, 4);
+  return r;
+}
+// the part of f a bf16 cannot hold: f = bf_round(f) + bf_lo(f) to 16 mantissa bits (GB_PREC_BF16X3 weight images)
+static float bf_lo(float f) { return f - bf_round(f); }
+
 // rows x K (K % 64 == 0) fp32 matrix given by at(r, k) -> tile images [K/64][rows][64]
 template <typename F>
 static void pack_image(uint16_t* dst, int rows, int K, F at) {

@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define GB_VERSION 100
+#define GB_VERSION 200
 
 typedef struct gb_ctx gb_ctx;
 
@@ -40,12 +40,21 @@ typedef enum gb_status {
   GB_ERR_MISSING = -4       /* a required weight tensor was not supplied */
 } gb_status;
 
-/* Precision of the pair-stack GEMMs (embeddings, LayerNorm statistics, softmax,
- * residual adds, frames and the structure net are always fp32). */
+/* Arithmetic of the GEMM-shaped work (pair stack, IPA projections / o_pair, structure transitions).  LayerNorm
+ * statistics, softmax, gating, residual adds, frames and the posterior step are fp32 in every mode, and the residual
+ * stream p is stored in fp32 in every mode.
+ *   FP32    fp32 FFMA on CUDA cores: the exact-parity path (1e-4 on every tensor Denoiser.forward returns).
+ *   BF16X3  tcgen05.mma kind::f16 with SPLIT operands: every operand v is carried as hi = bf16(v), lo = bf16(v - hi)
+ *           and every product is the three passes hi*hi + lo*hi + hi*lo accumulated in fp32 tensor memory (~2^-16
+ *           per product); intermediates between kernels (a, b, x, H, activations) are stored as hi | lo image pairs
+ *           or fp32.  This is the tensor-core mode that meets the 1e-3 per-eval / 0.1 A trajectory gates.
+ *   BF16    tcgen05.mma kind::f16, plain bf16 operands and bf16 intermediates: fastest, ~1.6e-2 per eval.
+ * GB_PREC_TF32 is the former name of slot 1 (declared, never built, in revision 100); it selects BF16X3. */
 typedef enum gb_precision {
-  GB_PREC_FP32 = 0,  /* fp32 FFMA on CUDA cores -- the exact-parity path            */
-  GB_PREC_TF32 = 1,  /* tcgen05.mma kind::tf32, fp32 storage, fp32 TMEM accumulation */
-  GB_PREC_BF16 = 2   /* tcgen05.mma kind::f16 (bf16 operands), fp32 accumulation     */
+  GB_PREC_FP32 = 0,
+  GB_PREC_BF16X3 = 1,
+  GB_PREC_TF32 = 1,
+  GB_PREC_BF16 = 2
 } gb_precision;
 
 /* Model dimensions: the keyword arguments of Denoiser.__init__ (genie/model/model.py:20-61)

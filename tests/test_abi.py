@@ -27,7 +27,7 @@ def test_library_exports_every_declared_symbol():
     for n in names:
         assert hasattr(lib, n), n
     assert sorted(_lib.SYMBOLS) == names          # the ctypes table binds all of them, nothing else
-    assert _lib.load().gb_version() == 100
+    assert _lib.load().gb_version() == 200
 
 
 def test_no_cpu_fallback():
