@@ -230,16 +230,24 @@ __global__ void __launch_bounds__(256, 2) trimul_contract_tc_kernel(const bf16* 
 // TMEM accumulators, warps 2-9 drain the other one -- load, MMA and drain of consecutive units overlap instead of
 // relying on a second resident CTA.  Same operands, same k order, same stores as the kernel above: bit-identical x.
 // ---------------------------------------------------------------------------------------------
-#define K5P_STAGES 4
+// SPLIT (GB_PREC_BF16X3): a, b and x are hi | lo image pairs (lo plane `lo_ab` / `lo_x` elements behind the hi plane).  A
+// stage holds [A_hi 16K | B_hi 32K | A_lo 16K | B_lo 32K] (two stages instead of four) and every k step issues the three
+// passes A_hi B_hi + A_lo B_hi + A_hi B_lo into the same fp32 accumulator; x is written as bf16(x) and bf16(x - bf16(x)).
 #define K5P_THREADS 320
-#define K5P_SMEM (K5P_STAGES * K5_STAGE_BYTES + 1024 + 128)
+template <bool SPLIT> struct K5P {
+  static constexpr uint32_t STAGES = SPLIT ? 2 : 4;
+  static constexpr uint32_t STAGE_BYTES = SPLIT ? 2 * K5_STAGE_BYTES : K5_STAGE_BYTES;
+  static constexpr uint32_t SMEM = STAGES * STAGE_BYTES + 1024 + 128;
+};
 
+template <bool SPLIT>
 __global__ void __launch_bounds__(K5P_THREADS, 1) trimul_contract_pers_tc_kernel(
     const bf16* __restrict__ a, const bf16* __restrict__ b, bf16* __restrict__ x, int N, int Np, int NJ, const ImgLayout La,
-    const ImgLayout Lb, int ib0, int nib, uint32_t nunits) {
+    const ImgLayout Lb, int ib0, int nib, uint32_t nunits, size_t lo_ab, size_t lo_x) {
+  constexpr uint32_t K5P_STAGES = K5P<SPLIT>::STAGES, STAGE_BYTES = K5P<SPLIT>::STAGE_BYTES;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* sm = smem_base_1024(smem_raw);
-  uint64_t* full = reinterpret_cast<uint64_t*>(sm + K5P_STAGES * K5_STAGE_BYTES);
+  uint64_t* full = reinterpret_cast<uint64_t*>(sm + K5P_STAGES * STAGE_BYTES);
   uint64_t* empty = full + K5P_STAGES;
   uint64_t* acc_full = empty + K5P_STAGES;      // [2] MMAs of a unit complete
   uint64_t* acc_empty = acc_full + 2;           // [2] the 8 epilogue warps have read the accumulator
@@ -274,11 +282,16 @@ __global__ void __launch_bounds__(K5P_THREADS, 1) trimul_contract_pers_tc_kernel
         for (uint32_t kb = 0; kb < nkb; ++kb, ++it) {
           const uint32_t s = it % K5P_STAGES;
           if (it >= K5P_STAGES) mbar_wait(empty + s, ((it / K5P_STAGES) - 1) & 1);
-          uint8_t* st = sm + s * K5_STAGE_BYTES;
-          mbar_expect_tx(full + s, (a_rows + nj) * 128u);
-          bulk_g2s(st, a + img_off(La, bb, cch, kb, ib * 128u), a_rows * 128u, full + s);
-          for (uint32_t r = 0; r < nj; r += bpiece)
-            bulk_g2s(st + 16384 + r * 128u, b + img_off(Lb, bb, cch, kb, jb * NJ + r), min(bpiece, nj - r) * 128u, full + s);
+          uint8_t* st = sm + s * STAGE_BYTES;
+          mbar_expect_tx(full + s, (SPLIT ? 2u : 1u) * (a_rows + nj) * 128u);
+          const size_t ao = img_off(La, bb, cch, kb, ib * 128u);
+          bulk_g2s(st, a + ao, a_rows * 128u, full + s);
+          if (SPLIT) bulk_g2s(st + K5_STAGE_BYTES, a + lo_ab + ao, a_rows * 128u, full + s);
+          for (uint32_t r = 0; r < nj; r += bpiece) {
+            const size_t bo = img_off(Lb, bb, cch, kb, jb * NJ + r);
+            bulk_g2s(st + 16384 + r * 128u, b + bo, min(bpiece, nj - r) * 128u, full + s);
+            if (SPLIT) bulk_g2s(st + K5_STAGE_BYTES + 16384 + r * 128u, b + lo_ab + bo, min(bpiece, nj - r) * 128u, full + s);
+          }
         }
       }
     }
@@ -298,10 +311,16 @@ __global__ void __launch_bounds__(K5P_THREADS, 1) trimul_contract_pers_tc_kernel
         const uint32_t s = it % K5P_STAGES;
         mbar_wait(full + s, (it / K5P_STAGES) & 1);
         tc_fence_after();
-        const uint32_t sa = smem_u32(sm + s * K5_STAGE_BYTES), sb = sa + 16384;
+        const uint32_t sa = smem_u32(sm + s * STAGE_BYTES), sb = sa + 16384;
         if (elect_one()) {
 #pragma unroll
-          for (int k = 0; k < 4; ++k) umma(acc, umma_desc(sa + k * 32), umma_desc(sb + k * 32), idesc, (kb | k) ? 1u : 0u);
+          for (int k = 0; k < 4; ++k) {
+            umma(acc, umma_desc(sa + k * 32), umma_desc(sb + k * 32), idesc, (kb | k) ? 1u : 0u);
+            if (SPLIT) {
+              umma(acc, umma_desc(sa + K5_STAGE_BYTES + k * 32), umma_desc(sb + k * 32), idesc, 1u);
+              umma(acc, umma_desc(sa + k * 32), umma_desc(sb + K5_STAGE_BYTES + k * 32), idesc, 1u);
+            }
+          }
           umma_commit(empty + s);
           if (kb == nkb - 1) umma_commit(acc_full + slot);
         }
@@ -334,17 +353,26 @@ __global__ void __launch_bounds__(K5P_THREADS, 1) trimul_contract_pers_tc_kernel
           const uint32_t sw = cch & 7u;
 #pragma unroll
           for (int kp = 0; kp < 2; ++kp) {
-            uint4 o[2];
+            uint4 o[2], ol[2];
 #pragma unroll
             for (int k4 = 0; k4 < 2; ++k4) {
               const uint32_t* vv = v + 16 * kp + 8 * k4;
-              o[k4].x = pack_bf16(__uint_as_float(vv[0]), __uint_as_float(vv[1]));
-              o[k4].y = pack_bf16(__uint_as_float(vv[2]), __uint_as_float(vv[3]));
-              o[k4].z = pack_bf16(__uint_as_float(vv[4]), __uint_as_float(vv[5]));
-              o[k4].w = pack_bf16(__uint_as_float(vv[6]), __uint_as_float(vv[7]));
+              if (SPLIT) {
+                split_bf16x2(__uint_as_float(vv[0]), __uint_as_float(vv[1]), o[k4].x, ol[k4].x);
+                split_bf16x2(__uint_as_float(vv[2]), __uint_as_float(vv[3]), o[k4].y, ol[k4].y);
+                split_bf16x2(__uint_as_float(vv[4]), __uint_as_float(vv[5]), o[k4].z, ol[k4].z);
+                split_bf16x2(__uint_as_float(vv[6]), __uint_as_float(vv[7]), o[k4].w, ol[k4].w);
+              } else {
+                o[k4].x = pack_bf16(__uint_as_float(vv[0]), __uint_as_float(vv[1]));
+                o[k4].y = pack_bf16(__uint_as_float(vv[2]), __uint_as_float(vv[3]));
+                o[k4].z = pack_bf16(__uint_as_float(vv[4]), __uint_as_float(vv[5]));
+                o[k4].w = pack_bf16(__uint_as_float(vv[6]), __uint_as_float(vv[7]));
+              }
             }
             const bool swap = sw & 1u;
-            st_global_32B(dst + (((q0 + 2 * kp) ^ (sw & 6u)) << 4), swap ? o[1] : o[0], swap ? o[0] : o[1]);
+            uint8_t* d32 = dst + (((q0 + 2 * kp) ^ (sw & 6u)) << 4);
+            st_global_32B(d32, swap ? o[1] : o[0], swap ? o[0] : o[1]);
+            if (SPLIT) st_global_32B(d32 + lo_x * 2, swap ? ol[1] : ol[0], swap ? ol[0] : ol[1]);
           }
         }
       }
@@ -549,6 +577,221 @@ __global__ void __launch_bounds__(256, 3) trimul_out_tc_kernel(
       o.z += v.z * g23.x;
       o.w += v.w * g23.y;
       st4(p + px[u] * 128 + ((lane ^ (r & 31)) << 2), o);
+    }
+  }
+  if (warp == 1) tmem_dealloc(tmem, 128);
+}
+
+// ---------------------------------------------------------------------------------------------
+// K6, GB_PREC_BF16X3: the x tile arrives as a hi | lo image pair (two 32 KB bulk copies), the folded weight W' = W_z * gamma
+// as hi and lo images; D = x_hi W'_hi + x_lo W'_hi + x_hi W'_lo.  W'_lo takes W'_hi's place in shared memory once the first
+// two passes have completed (96 KB per CTA keeps two CTAs per SM); a ninth warp does the copies and the MMA issue so the
+// eight statistics warps never wait for it.  Statistics are taken from hi + lo (exact in fp32); u = row sums of
+// W'_hi + W'_lo; g is fp32.  Same staging / coalesced read-modify-write of p as the bf16 kernel.
+// ---------------------------------------------------------------------------------------------
+#define K6S_THREADS 288
+#define K6S_SMEM (98304 + 1024 + 64 + 5120)
+
+// per-pixel sum over the 128 channels of (hi + lo - mean)^POW of this thread's (8-pixel chunk, 8-channel group)
+template <bool SQ>
+__device__ __forceinline__ void k6s_partial(const uint8_t* base, uint32_t q8, const float (&mean)[8], float (&acc)[8]) {
+#pragma unroll
+  for (int i = 0; i < 8; ++i) acc[i] = 0.f;
+#pragma unroll
+  for (uint32_t k = 0; k < 8; ++k) {
+    const uint4 wh = *reinterpret_cast<const uint4*>(base + k * 128u + ((q8 ^ k) << 4));
+    const uint4 wl = *reinterpret_cast<const uint4*>(base + 32768u + k * 128u + ((q8 ^ k) << 4));
+    const uint32_t hh[4] = {wh.x, wh.y, wh.z, wh.w}, ll[4] = {wl.x, wl.y, wl.z, wl.w};
+#pragma unroll
+    for (int t = 0; t < 4; ++t) {
+      const float2 a = unpack_bf16x2(hh[t]), b = unpack_bf16x2(ll[t]);
+      if (SQ) {
+        const float d0 = (a.x + b.x) - mean[2 * t], d1 = (a.y + b.y) - mean[2 * t + 1];
+        acc[2 * t] = fmaf(d0, d0, acc[2 * t]);
+        acc[2 * t + 1] = fmaf(d1, d1, acc[2 * t + 1]);
+      } else {
+        acc[2 * t] += a.x + b.x;
+        acc[2 * t + 1] += a.y + b.y;
+      }
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < 8; ++i) acc[i] += __shfl_xor_sync(0xffffffffu, acc[i], 16);
+}
+
+__global__ void __launch_bounds__(K6S_THREADS, 2) trimul_out_x3_kernel(
+    const bf16* __restrict__ x, size_t lo_x, const float* __restrict__ g, float* __restrict__ p, int N, int Np,
+    const bf16* __restrict__ Wz_hi, const bf16* __restrict__ Wz_lo, const float* __restrict__ uvec, const float* __restrict__ vvec,
+    const TileRange tr) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* sm = smem_base_1024(smem_raw);
+  uint8_t* X = sm;                       // hi 32K | lo 32K
+  uint8_t* W = sm + 65536;
+  uint64_t* bar_w = reinterpret_cast<uint64_t*>(sm + 98304);
+  uint64_t* bar_w2 = bar_w + 1;
+  uint64_t* bar_mma1 = bar_w + 2;
+  uint64_t* bar_mma = bar_w + 3;
+  uint32_t* tslot = reinterpret_cast<uint32_t*>(bar_w + 4);
+  float* red = reinterpret_cast<float*>(sm + 98304 + 64);     // [8][128] partials, then mean [128], rstd [128]
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const PixTile T = pix_tile(blockIdx.x, tr);
+  if (tid == 0) {
+    mbar_init(bar_w, 1);
+    mbar_init(bar_w2, 1);
+    mbar_init(bar_mma1, 1);
+    mbar_init(bar_mma, 1);
+    fence_mbar_init();
+  }
+  if (warp == 1) tmem_alloc(tslot, 128);
+  if (tid >= 32 && tid < 36) {           // L2 prefetch of the tile's p and g rows (read last, few bytes in flight per warp)
+    const uint32_t ii = (tid >> 1) & 1, row = 2 * T.t2 + ii, col = 64 * T.jb;
+    if (row < (uint32_t)N && col < (uint32_t)N) {
+      const uint32_t npx = min(64u, (uint32_t)N - col);
+      const size_t px = ((size_t)T.b * N + row) * N + col;
+      l2_prefetch((tid & 1 ? g : p) + px * 128, npx * 512u);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tslot;
+  if (warp == 8) {
+    if (lane == 0) {
+      mbar_expect_tx(bar_w, 98304);
+      bulk_g2s(W, Wz_hi, 32768, bar_w);
+    }
+    pdl_wait();            // x comes from the contraction kernel
+    pdl_launch();
+    if (lane == 0) {
+      const size_t off = (((size_t)T.b * (Np >> 1) + T.t2) * (Np >> 6) + T.jb) * 16384;
+      bulk_g2s(X, x + off, 32768, bar_w);
+      bulk_g2s(X + 32768, x + lo_x + off, 32768, bar_w);
+    }
+    __syncwarp();
+    mbar_wait(bar_w, 0);
+    tc_fence_after();
+    const uint32_t idesc = umma_idesc(128, 128) | (1u << 15);      // A (x tile) is MN-major
+    const uint32_t xs = smem_u32(X), ws = smem_u32(W), tm = warp_uniform(tmem);
+    if (elect_one()) {
+#pragma unroll
+      for (int k = 0; k < 8; ++k)
+        umma(tm, umma_desc_mn(xs + k * 2048, 16384), umma_desc(ws + (k >> 2) * 16384 + (k & 3) * 32), idesc, k ? 1u : 0u);
+#pragma unroll
+      for (int k = 0; k < 8; ++k)
+        umma(tm, umma_desc_mn(xs + 32768 + k * 2048, 16384), umma_desc(ws + (k >> 2) * 16384 + (k & 3) * 32), idesc, 1u);
+      umma_commit(bar_mma1);
+    }
+    __syncwarp();
+    mbar_wait(bar_mma1, 0);          // W'_hi has been read: W'_lo takes its place
+    if (lane == 0) {
+      mbar_expect_tx(bar_w2, 32768);
+      bulk_g2s(W, Wz_lo, 32768, bar_w2);
+    }
+    __syncwarp();
+    mbar_wait(bar_w2, 0);
+    tc_fence_after();
+    if (elect_one()) {
+#pragma unroll
+      for (int k = 0; k < 8; ++k)
+        umma(tm, umma_desc_mn(xs + k * 2048, 16384), umma_desc(ws + (k >> 2) * 16384 + (k & 3) * 32), idesc, 1u);
+      umma_commit(bar_mma);
+    }
+    __syncwarp();
+  } else {
+    pdl_wait();
+    pdl_launch();
+    // per-pixel statistics over the 128 channels of hi + lo, two passes; thread = (8-pixel chunk, 8-channel group)
+    mbar_wait(bar_w, 0);
+    const uint32_t pc = tid & 15, cg = tid >> 4, q8 = pc & 7;
+    const uint8_t* base = X + (pc >> 3) * 16384u + cg * 1024u;
+    float acc[8], mean[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    k6s_partial<false>(base, q8, mean, acc);
+    float* part = red + (cg >> 1) * 128 + pc * 8;
+    if ((lane & 16) == 0) {
+      st4(part, make_float4(acc[0], acc[1], acc[2], acc[3]));
+      st4(part + 4, make_float4(acc[4], acc[5], acc[6], acc[7]));
+    }
+    asm volatile("bar.sync 1, 256;" ::: "memory");
+    if (tid < 128) {
+      float t = 0.f;
+#pragma unroll
+      for (int r = 0; r < 8; ++r) t += red[r * 128 + tid];
+      red[1024 + tid] = t * (1.f / 128.f);
+    }
+    asm volatile("bar.sync 1, 256;" ::: "memory");
+    {
+      const float4 m0 = ld4(red + 1024 + pc * 8), m1 = ld4(red + 1024 + pc * 8 + 4);
+      mean[0] = m0.x; mean[1] = m0.y; mean[2] = m0.z; mean[3] = m0.w; mean[4] = m1.x; mean[5] = m1.y; mean[6] = m1.z; mean[7] = m1.w;
+    }
+    k6s_partial<true>(base, q8, mean, acc);
+    if ((lane & 16) == 0) {
+      st4(part, make_float4(acc[0], acc[1], acc[2], acc[3]));
+      st4(part + 4, make_float4(acc[4], acc[5], acc[6], acc[7]));
+    }
+    asm volatile("bar.sync 1, 256;" ::: "memory");
+    if (tid < 128) {
+      float t = 0.f;
+#pragma unroll
+      for (int r = 0; r < 8; ++r) t += red[r * 128 + tid];
+      red[1152 + tid] = rsqrtf(t * (1.f / 128.f) + 1e-5f);
+    }
+  }
+  mbar_wait(bar_mma, 0);
+  tc_fence_after();
+  __syncthreads();                                               // stats visible; X / W dead -> staging
+  uint8_t* S = sm;
+  if (warp < 8) {
+    const uint32_t q = warp & 3, h = warp >> 2, m = q * 32 + lane;
+    const uint32_t t_lane = tmem + ((q * 32u) << 16);
+    const float mean = red[1024 + m], rstd = red[1152 + m];
+#pragma unroll 1
+    for (int cc = 0; cc < 2; ++cc) {
+      const uint32_t col0 = h * 64 + cc * 32;
+      uint32_t v[32];
+      tmem_ld32(t_lane + col0, v);
+      tmem_ld_wait();
+#pragma unroll
+      for (int k4 = 0; k4 < 8; ++k4) {
+        const float4 u4 = ld4(uvec + col0 + 4 * k4), v4 = ld4(vvec + col0 + 4 * k4);
+        float4 o;
+        o.x = rstd * (__uint_as_float(v[4 * k4 + 0]) - mean * u4.x) + v4.x;
+        o.y = rstd * (__uint_as_float(v[4 * k4 + 1]) - mean * u4.y) + v4.y;
+        o.z = rstd * (__uint_as_float(v[4 * k4 + 2]) - mean * u4.z) + v4.z;
+        o.w = rstd * (__uint_as_float(v[4 * k4 + 3]) - mean * u4.w) + v4.w;
+        *stage_ptr(S, m, (col0 >> 2) + k4) = o;
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp < 8) {
+    for (int r0 = warp * 16; r0 < warp * 16 + 16; r0 += 4) {     // 4 pixels in flight per warp
+      float4 pv[4], gv[4];
+      size_t px[4];
+      bool ok[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const uint32_t r = r0 + u, row = 2 * T.t2 + (r >> 6), col = 64 * T.jb + (r & 63);
+        ok[u] = row < (uint32_t)N && col < (uint32_t)N;
+        px[u] = ((size_t)T.b * N + row) * N + col;
+        if (ok[u]) {
+          const uint32_t cl = lane ^ (r & 31);
+          pv[u] = ld4(p + px[u] * 128 + cl * 4);
+          gv[u] = ld4(g + px[u] * 128 + cl * 4);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const uint32_t r = r0 + u;
+        if (!ok[u]) continue;
+        const float4 v = *reinterpret_cast<const float4*>(S + r * 512u + (lane << 4));
+        float4 o = pv[u];
+        o.x = fmaf(v.x, gv[u].x, o.x);
+        o.y = fmaf(v.y, gv[u].y, o.y);
+        o.z = fmaf(v.z, gv[u].z, o.z);
+        o.w = fmaf(v.w, gv[u].w, o.w);
+        st4(p + px[u] * 128 + ((lane ^ (r & 31)) << 2), o);
+      }
     }
   }
   if (warp == 1) tmem_dealloc(tmem, 128);
