@@ -409,7 +409,7 @@ extern "C" int gb_set_schedule(gb_ctx* c, const float* alphas, const float* sqrt
 
 extern "C" int gb_set_precision(gb_ctx* c, int precision) {
   if (!c) return GB_ERR_INVALID;
-  if (precision != GB_PREC_FP32 && precision != GB_PREC_TF32 && precision != GB_PREC_BF16)
+  if (precision != GB_PREC_FP32 && precision != GB_PREC_BF16X3 && precision != GB_PREC_BF16)
     return gb_fail(c, GB_ERR_INVALID, "gb_set_precision: unknown precision %d", precision);
   c->precision = precision;
   return GB_OK;
@@ -926,7 +926,7 @@ extern "C" int gb_k_trimul_stage(gb_ctx* c, int layer, int outgoing, int stage, 
   DeviceGuard dg(c->device);
   if (!p || layer < 0 || layer >= c->d.n_pair_transform_layer || !c->d.include_mul_update || stage < 1 || stage > 3)
     return gb_fail(c, GB_ERR_INVALID, "gb_k_trimul_stage: bad arguments");
-  if (c->precision != GB_PREC_BF16) return gb_fail(c, GB_ERR_UNSUPPORTED, "gb_k_trimul_stage: tensor-core (bf16) mode only");
+  if (c->precision == GB_PREC_FP32) return gb_fail(c, GB_ERR_UNSUPPORTED, "gb_k_trimul_stage: tensor-core modes (bf16, bf16x3) only");
   return tc_trimul_stage(c, outgoing ? c->pair[layer].mul_out : c->pair[layer].mul_in, outgoing != 0, stage, p, (cudaStream_t)stream);
 }
 

@@ -21,11 +21,15 @@ struct TriMulW {
   // tensor-core packings (K-major [n][k] rows, i.e. nn.Linear layout), filled by tc_pack
   void *tc_Wproj, *tc_Wz;
   float *tc_bproj, *tc_uv;   // tc_uv: [128] u | [128] v of the LayerNorm-folded output projection
+  // GB_PREC_BF16X3: hi | lo images of the same (unscaled) weights, see tc_proj_x3.cu / tc_pair.cu
+  void *x3_Wproj_hi, *x3_Wproj_lo, *x3_Wz_hi, *x3_Wz_lo;
+  float *x3_bproj, *x3_uv;
 };
 struct TransitionW {
   float *ln_g, *ln_b, *W1T, *b1, *W2T, *b2;
   void *tc_W1, *tc_W2;   // bf16 chunk images; W1 carries the LayerNorm gamma
   float* tc_b1;          // b1 + W1 beta
+  void *x3_W1, *x3_W2;   // GB_PREC_BF16X3: 64-wide hidden chunks, each block hi 16K | lo 16K (tc_transition_x3.cu)
 };
 struct TriAttW {
   float *ln_g, *ln_b, *Wbias /*[H][128]*/, *Wqkvg /*[4*H*C][128]: q|k|v|g*/, *bg, *Wo /*[128][H*C]*/, *bo, *bqkvg /*[4*H*C]: 0|0|0|bg*/;

@@ -17,6 +17,15 @@ int tc_proj_init(gb_ctx* c);
 int tc_pack_trimul_proj(gb_ctx* c, TriMulW& w, const std::vector<float>* Wm[5], const std::vector<float>* bm[5],
                         const std::vector<float>& ln_g, const std::vector<float>& ln_b);
 int tc_launch_trimul_proj(gb_ctx* c, const TriMulW& w, bool outgoing, const float* p, cudaStream_t st);
+// GB_PREC_BF16X3 (split-bf16, three passes per product): tc_proj_x3.cu, tc_transition_x3.cu
+int tc_proj_x3_init(gb_ctx* c);
+int tc_pack_trimul_proj_x3(gb_ctx* c, TriMulW& w, const std::vector<float>* Wm[5], const std::vector<float>* bm[5],
+                           const std::vector<float>& ln_g, const std::vector<float>& ln_b);
+int tc_launch_trimul_proj_x3(gb_ctx* c, const TriMulW& w, bool outgoing, const float* p, cudaStream_t st);
+int tc_transition_x3_init(gb_ctx* c);
+int tc_pack_transition_x3(gb_ctx* c, TransitionW& w, const std::vector<float>& w1, const std::vector<float>& w2,
+                          const std::vector<float>& ln_g);
+int tc_pair_transition_x3(gb_ctx* c, const TransitionW& w, float* p, cudaStream_t st);
 int tc_transition_init(gb_ctx* c);
 int tc_pack_transition(gb_ctx* c, TransitionW& w, const std::vector<float>& w1, const std::vector<float>& b1,
                        const std::vector<float>& w2, const std::vector<float>& ln_g, const std::vector<float>& ln_b);

@@ -803,7 +803,9 @@ __global__ void __launch_bounds__(K6S_THREADS, 2) trimul_out_x3_kernel(
 int tc_init(gb_ctx* c) {
   cudaError_t e;
   if ((e = cudaFuncSetAttribute(trimul_contract_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, K5_SMEM)) != cudaSuccess ||
-      (e = cudaFuncSetAttribute(trimul_contract_pers_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, K5P_SMEM)) != cudaSuccess ||
+      (e = cudaFuncSetAttribute(trimul_contract_pers_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, K5P<false>::SMEM)) != cudaSuccess ||
+      (e = cudaFuncSetAttribute(trimul_contract_pers_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, K5P<true>::SMEM)) != cudaSuccess ||
+      (e = cudaFuncSetAttribute(trimul_out_x3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, K6S_SMEM)) != cudaSuccess ||
       (e = cudaFuncSetAttribute(trimul_out_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, K6_SMEM)) != cudaSuccess)
     return gb_fail(c, GB_ERR_CUDA, "tc_init: cudaFuncSetAttribute failed: %s", cudaGetErrorString(e));
   c->tc_state = new TcState();
@@ -848,6 +850,21 @@ int tc_pack_trimul(gb_ctx* c, TriMulW& w, const std::vector<float>& ap, const st
   }
   w.tc_uv = (float*)upload_bytes(c, uv.data(), uv.size() * 4);
   if (!w.tc_Wz || !w.tc_uv) return gb_fail(c, GB_ERR_CUDA, "tc_pack_trimul: device allocation failed");
+  // GB_PREC_BF16X3: W' as hi | lo images, u = row sums of W'_hi + W'_lo (what the three passes multiply the mean with)
+  std::vector<uint16_t> wl(128 * 128);
+  pack_image(wl.data(), 128, 128, [&](int r, int k) { return bf_lo(lz[(size_t)r * 128 + k] * lno_g[k]); });
+  w.x3_Wz_hi = w.tc_Wz;
+  w.x3_Wz_lo = upload_bytes(c, wl.data(), wl.size() * 2);
+  for (int n = 0; n < 128; ++n) {
+    double u = 0.0;
+    for (int k = 0; k < 128; ++k) {
+      const float wf = lz[(size_t)n * 128 + k] * lno_g[k];
+      u += (double)bf_round(wf) + (double)bf_round(bf_lo(wf));
+    }
+    uv[n] = (float)u;
+  }
+  w.x3_uv = (float*)upload_bytes(c, uv.data(), uv.size() * 4);
+  if (!w.x3_Wz_lo || !w.x3_uv) return gb_fail(c, GB_ERR_CUDA, "tc_pack_trimul: device allocation failed");
   return GB_OK;
 }
 
@@ -856,14 +873,15 @@ static size_t align256(size_t v) { return (v + 255) & ~(size_t)255; }
 size_t tc_workspace_bytes(const gb_ctx* c, int B, int N) {
   const size_t Np = (size_t)((N + 63) / 64) * 64;
   const size_t plane = (size_t)B * 128 * Np * Np * 2;
-  return 3 * align256(plane) + align256((size_t)B * N * N * 128 * 2) + 1024 + tc_struct_workspace_bytes(c, B, N);
+  return 6 * align256(plane) + align256((size_t)B * N * N * 128 * 2) + 1024 + tc_struct_workspace_bytes(c, B, N);
 }
 
 int tc_bind_workspace(gb_ctx* c, void* base, size_t bytes, int B, int N) {
   TcState* s = static_cast<TcState*>(c->tc_state);
   const size_t Np = (size_t)((N + 63) / 64) * 64;
   const size_t plane = align256((size_t)B * 128 * Np * Np * 2);
-  if (bytes < 3 * plane + align256((size_t)B * N * N * 128 * 2)) return gb_fail(c, GB_ERR_INVALID, "tc_bind_workspace: too small");
+  const size_t gbytes = align256((size_t)B * N * N * 128 * 2);
+  if (bytes < 6 * plane + gbytes) return gb_fail(c, GB_ERR_INVALID, "tc_bind_workspace: too small");
   char* q = static_cast<char*>(base);
   s->Np = (int)Np;
   s->a = reinterpret_cast<bf16*>(q);
@@ -871,18 +889,22 @@ int tc_bind_workspace(gb_ctx* c, void* base, size_t bytes, int B, int N) {
   s->x = reinterpret_cast<bf16*>(q + 2 * plane);
   s->g = reinterpret_cast<bf16*>(q + 3 * plane);
   s->ab_bytes = 2 * plane;
+  // [a | b | x | g (bf16)] [a_lo | b_lo | x_lo]: the lo planes of GB_PREC_BF16X3 sit at one common offset behind their hi planes
+  s->lo_plane = (3 * plane + gbytes) / 2;
   // the k-padding (N <= k < Np) of the operand images is never written by K4 and must read as zero
-  if (cudaMemset(q, 0, 3 * plane) != cudaSuccess) return gb_fail(c, GB_ERR_CUDA, "tc_bind_workspace: memset failed");
-  const size_t used = 3 * plane + align256((size_t)B * N * N * 128 * 2);
+  if (cudaMemset(q, 0, 3 * plane) != cudaSuccess || cudaMemset(q + 3 * plane + gbytes, 0, 3 * plane) != cudaSuccess)
+    return gb_fail(c, GB_ERR_CUDA, "tc_bind_workspace: memset failed");
+  const size_t used = 6 * plane + gbytes;
   return tc_struct_bind(c, q + used, bytes - used, B, N);
 }
 
 int tc_trimul_stage(gb_ctx* c, const TriMulW& w, bool outgoing, int stage, float* p, cudaStream_t st) {
-  if (c->precision != GB_PREC_BF16) return gb_fail(c, GB_ERR_UNSUPPORTED, "tensor-core path: tf32 kernels are not built in this revision (use bf16 or fp32)");
   TcState* s = static_cast<TcState*>(c->tc_state);
   const int B = c->B, N = c->N, Np = s->Np, W = c->shard_world;
+  const bool x3 = c->precision == GB_PREC_BF16X3;
+  if (x3 && W > 1) return gb_fail(c, GB_ERR_UNSUPPORTED, "row sharding is built for the bf16 pair stack only");
   if (stage == 0 || stage == 1) {
-    int rc = tc_launch_trimul_proj(c, w, outgoing, p, st);
+    int rc = x3 ? tc_launch_trimul_proj_x3(c, w, outgoing, p, st) : tc_launch_trimul_proj(c, w, outgoing, p, st);
     if (rc != GB_OK) return rc;
     if (W > 1) {
       // each rank wrote its block of the operand images.  K5 needs every row of b: in-place all-gather over NVLink.
@@ -901,9 +923,10 @@ int tc_trimul_stage(gb_ctx* c, const TriMulW& w, bool outgoing, int stage, float
     const int nib = W > 1 ? (N / W) / 128 : (Np + 127) / 128, ib0 = W > 1 ? c->shard_rank * nib : 0;
     const unsigned cgrid = (unsigned)B * 128 * nib * ((Np + NJ - 1) / NJ);
     static const int k5pers = [] { const char* e = getenv("GB_K5_PERS"); return e ? atoi(e) : 1; }();
-    if (k5pers) {
+    if (k5pers || x3) {
       const unsigned pgrid = cgrid < (unsigned)s->num_sms ? cgrid : (unsigned)s->num_sms;
-      launch_pdl_cls(2, trimul_contract_pers_tc_kernel, pgrid, K5P_THREADS, K5P_SMEM, st, s->a, s->b, s->x, N, Np, NJ, La, Lb, ib0, nib, (uint32_t)cgrid);
+      if (x3) launch_pdl_cls(2, trimul_contract_pers_tc_kernel<true>, pgrid, K5P_THREADS, K5P<true>::SMEM, st, s->a, s->b, s->x, N, Np, NJ, La, Lb, ib0, nib, (uint32_t)cgrid, s->lo_plane, s->lo_plane);
+      else launch_pdl_cls(2, trimul_contract_pers_tc_kernel<false>, pgrid, K5P_THREADS, K5P<false>::SMEM, st, s->a, s->b, s->x, N, Np, NJ, La, Lb, ib0, nib, (uint32_t)cgrid, (size_t)0, (size_t)0);
     } else
     launch_pdl_cls(2, trimul_contract_tc_kernel, cgrid, 256, K5_SMEM, st, s->a, s->b, s->x, N, Np, NJ, La, Lb, ib0, nib);
     GB_LAUNCH_CHECK(c, "trimul_contract_tc");
@@ -912,7 +935,8 @@ int tc_trimul_stage(gb_ctx* c, const TriMulW& w, bool outgoing, int stage, float
     TileRange tr = full_tile_range(N, Np);
     if (W > 1) { tr.nt2 = (uint32_t)(N / W) >> 1; tr.t2_0 = c->shard_rank * tr.nt2; }
     const unsigned tiles = (unsigned)B * tr.nt2 * tr.njb;
-    launch_pdl_cls(3, trimul_out_tc_kernel, tiles, 256, K6_SMEM, st, s->x, s->g, p, N, Np, (const bf16*)w.tc_Wz, w.tc_uv, w.tc_uv + 128, tr);
+    if (x3) launch_pdl_cls(3, trimul_out_x3_kernel, tiles, K6S_THREADS, K6S_SMEM, st, s->x, s->lo_plane, c->g, p, N, Np, (const bf16*)w.x3_Wz_hi, (const bf16*)w.x3_Wz_lo, w.x3_uv, w.x3_uv + 128, tr);
+    else launch_pdl_cls(3, trimul_out_tc_kernel, tiles, 256, K6_SMEM, st, s->x, s->g, p, N, Np, (const bf16*)w.tc_Wz, w.tc_uv, w.tc_uv + 128, tr);
     GB_LAUNCH_CHECK(c, "trimul_out_tc");
   }
   return GB_OK;
@@ -925,8 +949,11 @@ extern "C" int gb_dbg_tc_copy(gb_ctx* c, int which, void* dst, int64_t bytes) {
   TcState* s = static_cast<TcState*>(c->tc_state);
   if (!dst) return s->Np;
   const size_t plane = (size_t)c->B * 128 * s->Np * s->Np * 2, gb = (size_t)c->B * c->N * c->N * 128 * 2;
-  const void* src = which == 0 ? (void*)s->a : which == 1 ? (void*)s->b : which == 2 ? (void*)s->x : which == 3 ? (void*)s->g : nullptr;
-  const size_t have = which == 3 ? gb : plane;
+  // 0..3: a, b, x, g (bf16); 4..6: lo planes of a, b, x (GB_PREC_BF16X3); 7: fp32 g of that mode
+  const void* src = which == 0 ? (void*)s->a : which == 1 ? (void*)s->b : which == 2 ? (void*)s->x : which == 3 ? (void*)s->g
+                  : which == 4 ? (void*)(s->a + s->lo_plane) : which == 5 ? (void*)(s->b + s->lo_plane)
+                  : which == 6 ? (void*)(s->x + s->lo_plane) : which == 7 ? (void*)c->g : nullptr;
+  const size_t have = which == 3 ? gb : which == 7 ? 2 * gb : plane;
   if (!src || bytes < 0 || (size_t)bytes > have) return gb_fail(c, GB_ERR_INVALID, "gb_dbg_tc_copy: bad arguments");
   GB_CUDA(c, cudaMemcpy(dst, src, (size_t)bytes, cudaMemcpyDeviceToDevice));
   return s->Np;

@@ -323,7 +323,7 @@ int tc_proj_init(gb_ctx* c) {
   TcState* s = static_cast<TcState*>(c->tc_state);
   if (cudaDeviceGetAttribute(&s->num_sms, cudaDevAttrMultiProcessorCount, c->device) != cudaSuccess || s->num_sms < 1)
     return gb_fail(c, GB_ERR_CUDA, "tc_proj_init: cannot read the SM count");
-  return GB_OK;
+  return tc_proj_x3_init(c);
 }
 
 // Weight images with LayerNorm_in's gamma folded in and everything scaled by 1/2 (exact in bf16):
@@ -347,7 +347,7 @@ int tc_pack_trimul_proj(gb_ctx* c, TriMulW& w, const std::vector<float>* Wm[5], 
     }
   w.tc_bproj = (float*)upload_bytes(c, bias.data(), bias.size() * 4);
   if (!w.tc_Wproj || !w.tc_bproj) return gb_fail(c, GB_ERR_CUDA, "tc_pack_trimul_proj: device allocation failed");
-  return GB_OK;
+  return tc_pack_trimul_proj_x3(c, w, Wm, bm, ln_g, ln_b);
 }
 
 int tc_launch_trimul_proj(gb_ctx* c, const TriMulW& w, bool outgoing, const float* p, cudaStream_t st) {

@@ -18,11 +18,13 @@ struct TcState {
   bf16 *x = nullptr;                 // [B][128][Np][Np]
   bf16 *g = nullptr;                 // [B*N*N][128]
   size_t ab_bytes = 0;
+  size_t lo_plane = 0;               // GB_PREC_BF16X3: elements from a / b / x (the hi planes) to their lo planes
   int num_sms = 0;
   // structure net
   int Rp = 0;                        // B*N rounded up to a multiple of 128
   bf16 *s_img = nullptr, *cat_img = nullptr, *ln1_img = nullptr, *h1_img = nullptr, *h2_img = nullptr;
   bf16* z_img = nullptr;             // [B][N][2][Np][64]
+  size_t img_lo = 0;                 // GB_PREC_BF16X3: elements from any image above to its lo twin
   float* pbias = nullptr;            // [L][B][N][12][Np]
   bf16* Wpipj_img = nullptr;         // [c_s/64][256][64]: [W_i | W_j] of the pair feature net
   bool s_img_valid = false;          // s_img holds the image of the current single features (set by tc_pair_pipj)

@@ -321,7 +321,7 @@ __global__ void __launch_bounds__(K7_THREADS, 1) pair_transition_tc_kernel(
 int tc_transition_init(gb_ctx* c) {
   cudaError_t e = cudaFuncSetAttribute(pair_transition_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, K7_SMEM);
   if (e != cudaSuccess) return gb_fail(c, GB_ERR_CUDA, "tc_transition_init: cudaFuncSetAttribute failed: %s", cudaGetErrorString(e));
-  return GB_OK;
+  return tc_transition_x3_init(c);
 }
 
 // W1' = W1 * gamma (LayerNorm folded), b1' = b1 + W1 beta;  chunk images [chunk][2 kb][128 rows][64]
@@ -343,11 +343,11 @@ int tc_pack_transition(gb_ctx* c, TransitionW& w, const std::vector<float>& w1, 
   w.tc_W2 = upload_bytes(c, i2.data(), i2.size() * 2);
   w.tc_b1 = (float*)upload_bytes(c, bf.data(), bf.size() * 4);
   if (!w.tc_W1 || !w.tc_W2 || !w.tc_b1) return gb_fail(c, GB_ERR_CUDA, "tc_pack_transition: device allocation failed");
-  return GB_OK;
+  return tc_pack_transition_x3(c, w, w1, w2, ln_g);
 }
 
 int tc_pair_transition(gb_ctx* c, const TransitionW& w, float* p, cudaStream_t st) {
-  if (c->precision != GB_PREC_BF16) return gb_fail(c, GB_ERR_UNSUPPORTED, "tensor-core path: tf32 kernels are not built in this revision (use bf16 or fp32)");
+  if (c->precision == GB_PREC_BF16X3) return tc_pair_transition_x3(c, w, p, st);
   size_t M = (size_t)c->B * c->N * c->N, px0 = 0;
   if (M >= (1ull << 31)) return gb_fail(c, GB_ERR_UNSUPPORTED, "pair map too large");
   if (c->shard_world > 1) {                         // B == 1: this rank's rows are one contiguous pixel range

@@ -1,0 +1,105 @@
+"""Parity of the GB_PREC_BF16X3 mode: tcgen05 tensor cores with split-bf16 operands (hi = bf16(v),
+lo = bf16(v - hi), three passes hi*hi + lo*hi + hi*lo per product, fp32 accumulation in tensor memory).
+
+This is the tensor-core mode held to the north star's fp32 gates: every intermediate of the triangle update
+(a, b, g, x -- read back as hi + lo through the test-only accessor gb_dbg_tc_copy), the pair transition, and the
+whole denoiser are compared with a torch fp32 restatement / the CPU oracle at 1e-4 .. 1e-3, not at the bf16
+tolerances of test_gpu_tensorcore.py.
+Reference: modules/triangular_multiplicative_update.py:57-110, modules/pair_transition.py:48-87,
+model/model.py:125-192.
+"""
+import os
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+from common import GOLDEN, load_forward_case, make_denoiser, feats_to, run_cuda_forward, rel
+from oracle import genie_oracle as O, weights as W
+
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), 'scripts'))
+
+pytestmark = pytest.mark.gpu
+DEV = 'cuda:0'
+TOL_STAGE = 1e-4      # one split GEMM (+ fp32 gating) against torch fp32 on the same GPU
+TOL_Z = 1e-3          # north star: per-step noise prediction vs the reference fp32 path
+
+
+def _setup(B, N, seed=3):
+    torch.backends.cuda.matmul.allow_tf32 = False
+    cfg = O.OracleConfig(n_pair_transform_layer=1, n_structure_layer=1)
+    sd = W.make_state_dict(cfg, seed, 'activated')
+    model = make_denoiser(cfg, sd, precision='bf16x3')
+    lens = [[N]] + [[max(3, N - 5 - 3 * i)] for i in range(B - 1)]
+    feats = feats_to(O.make_features(lens), DEV)
+    ctx = model.bind_features(feats, torch.device(DEV))
+    g = torch.Generator().manual_seed(seed)
+    p = (torch.randn(B, N, N, 128, generator=g) * 1.5 + 0.3).to(DEV)
+    mask = feats['residue_mask'].float()
+    pm = (mask[:, :, None] * mask[:, None, :])[..., None]
+    return model, {k: v.to(DEV) for k, v in sd.items()}, ctx, p, pm
+
+
+@pytest.mark.parametrize('B,N', [(1, 64), (2, 50), (1, 131)])
+def test_pair_transition_x3(B, N):
+    import genie2_b200._lib as L
+    lib = L.load()
+    model, sd, ctx, p0, pm = _setup(B, N)
+    p = p0.clone()
+    L.check(lib.gb_k_pair_transition(ctx, 0, p.data_ptr(), None), ctx, 'gb_k_pair_transition')
+    torch.cuda.synchronize()
+    pre = 'pair_transform_net.net.0.pair_transition.'
+    z = torch.nn.functional.layer_norm(p0, (128,), sd[pre + 'layer_norm.weight'], sd[pre + 'layer_norm.bias'])
+    hid = torch.relu(z @ sd[pre + 'linear_1.weight'].T + sd[pre + 'linear_1.bias'])
+    upd = (hid @ sd[pre + 'linear_2.weight'].T + sd[pre + 'linear_2.bias']) * pm
+    ref = (p0 + upd) * pm
+    assert rel(p - p0 * pm, ref - p0 * pm) < TOL_STAGE
+    masked = pm.expand_as(p) == 0
+    if bool(masked.any()):
+        assert float(p[masked].abs().max()) == 0.0
+
+
+@pytest.mark.parametrize('outgoing', [1, 0])
+@pytest.mark.parametrize('B,N', [(1, 64), (2, 100), (1, 200)])
+def test_trimul_x3_every_stage(B, N, outgoing):
+    import genie2_b200._lib as L
+    from tc_diag import decode_image, decode_x
+    lib = L.load()
+    model, sd, ctx, p0, pm = _setup(B, N)
+    p = p0.clone()
+    L.check(lib.gb_k_trimul(ctx, 0, outgoing, p.data_ptr(), None), ctx, 'gb_k_trimul')
+    torch.cuda.synchronize()
+    pre = 'pair_transform_net.net.0.tri_mul_%s.' % ('out' if outgoing else 'in')
+    ln = torch.nn.functional.layer_norm
+    lin = lambda n, v: v @ sd[pre + n + '.weight'].T + sd[pre + n + '.bias']
+    z = ln(p0, (128,), sd[pre + 'layer_norm_in.weight'], sd[pre + 'layer_norm_in.bias'])
+    a = lin('linear_a_p', z) * torch.sigmoid(lin('linear_a_g', z)) * pm
+    b = lin('linear_b_p', z) * torch.sigmoid(lin('linear_b_g', z)) * pm
+    gate = torch.sigmoid(lin('linear_g', z))
+    x = torch.einsum('bikc,bjkc->bijc', a, b) if outgoing else torch.einsum('bkic,bkjc->bijc', a, b)
+    upd = lin('linear_z', ln(x, (128,), sd[pre + 'layer_norm_out.weight'], sd[pre + 'layer_norm_out.bias'])) * gate
+    Np = lib.gb_dbg_tc_copy(ctx, 0, None, 0)
+    assert Np == (N + 63) // 64 * 64
+
+    def grab(which, n, dtype=torch.bfloat16):
+        out = torch.empty(n, dtype=dtype, device=DEV)
+        assert lib.gb_dbg_tc_copy(ctx, which, out.data_ptr(), n * out.element_size()) == Np
+        return out
+    plane = B * 128 * Np * Np
+    a_img = decode_image(grab(0, plane), B, Np) + decode_image(grab(4, plane), B, Np)
+    b_img = decode_image(grab(1, plane), B, Np) + decode_image(grab(5, plane), B, Np)
+    # K-padding of the operand images must read as exact zeros (it multiplies into every output)
+    assert float(a_img[:, :, :N, N:].abs().max() if Np > N else 0.0) == 0.0
+    assert float(b_img[:, :, :N, N:].abs().max() if Np > N else 0.0) == 0.0
+    perm = (0, 3, 1, 2) if outgoing else (0, 3, 2, 1)
+    errs = {
+        'a': rel(a_img[:, :, :N, :N], a.permute(*perm)),
+        'b': rel(b_img[:, :, :N, :N], b.permute(*perm)),
+        'g': rel(grab(7, B * N * N * 128, torch.float32).view(B, N, N, 128) * pm, gate * pm),
+        'x': rel((decode_x(grab(2, plane), B, Np) + decode_x(grab(6, plane), B, Np))[:, :, :N, :N], x.permute(0, 3, 1, 2)),
+        'dp': rel(p - p0, upd),
+    }
+    print('x3 trimul stages', B, N, outgoing, {k: '%.1e' % v for k, v in errs.items()})
+    for k, v in errs.items():
+        assert v < TOL_STAGE, (k, v)
