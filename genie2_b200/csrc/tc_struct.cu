@@ -25,9 +25,14 @@ using namespace tc;
 // gemm_img_tc_kernel: one CTA = 128 rows x 64 output columns; warp 0 streams k-blocks of A (16 KB)
 // and W (8 KB) through an 8-stage mbarrier ring, warp 1 issues the MMAs, all warps run the epilogue.
 // ---------------------------------------------------------------------------------------------
-#define GI_STAGES 8
+// NS = 2 (GB_PREC_BF16X3): A, W (and the image output O) are hi | lo split components, component c `A_lo` / `W_lo` / `O_lo`
+// elements behind component c - 1; a stage holds NS x [A_c 16K | W_c 8K] and every k step issues the passes of SplitPasses.
 #define GI_STAGE_BYTES (16384 + 8192)
-#define GI_SMEM (GI_STAGES * GI_STAGE_BYTES + 1024 + 256)
+template <int NS> struct GI {
+  static constexpr int STAGES = NS == 1 ? 8 : 4;
+  static constexpr uint32_t STAGE = NS * GI_STAGE_BYTES;
+  static constexpr uint32_t SMEM = STAGES * STAGE + 1024 + 256;
+};
 
 struct GemmImgArgs {
   const bf16* A;      // [nkb][Rp][64]
@@ -40,12 +45,16 @@ struct GemmImgArgs {
   int mblk0;          // first 128-row block of this launch (row-sharded launches compute their own rows only)
   int kvsplit;        // > 0: IPA projection scatter, value = N (keys per sample): columns < IPA_QW go to rows [R][IPA_QW],
                       // the rest to key-major planes [B][IPA_NPLANE][N][4] behind them (see ipa_dims.h)
+  size_t A_lo, W_lo, O_lo;   // NS > 1 only
 };
 
+template <int NS>
 __global__ void __launch_bounds__(256, 1) gemm_img_tc_kernel(const GemmImgArgs g) {
+  constexpr int GI_STAGES = GI<NS>::STAGES;
+  constexpr uint32_t STAGE = GI<NS>::STAGE;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* sm = smem_base_1024(smem_raw);
-  uint64_t* full = reinterpret_cast<uint64_t*>(sm + GI_STAGES * GI_STAGE_BYTES);
+  uint64_t* full = reinterpret_cast<uint64_t*>(sm + GI_STAGES * STAGE);
   uint64_t* empty = full + GI_STAGES;
   uint64_t* done = empty + GI_STAGES;
   uint32_t* tslot = reinterpret_cast<uint32_t*>(done + 1);
@@ -66,20 +75,26 @@ __global__ void __launch_bounds__(256, 1) gemm_img_tc_kernel(const GemmImgArgs g
       // the weight halves of the first ring of stages do not depend on the previous kernel: in flight before pdl_wait
       const int npre = g.nkb < GI_STAGES ? g.nkb : GI_STAGES;
       for (int kb = 0; kb < npre; ++kb) {
-        mbar_expect_tx(full + kb, GI_STAGE_BYTES);
-        bulk_g2s(sm + kb * GI_STAGE_BYTES + 16384, g.W + ((size_t)kb * g.Nw + n0) * 64, 8192, full + kb);
+        mbar_expect_tx(full + kb, STAGE);
+        const bf16* wsrc = g.W + ((size_t)kb * g.Nw + n0) * 64;
+#pragma unroll
+        for (int c = 0; c < NS; ++c) bulk_g2s(sm + kb * STAGE + c * GI_STAGE_BYTES + 16384, wsrc + c * g.W_lo, 8192, full + kb);
       }
       pdl_wait();
       pdl_launch();
       for (int kb = 0; kb < g.nkb; ++kb) {
         const int s = kb % GI_STAGES;
-        uint8_t* st = sm + s * GI_STAGE_BYTES;
+        uint8_t* st = sm + s * STAGE;
         if (kb >= GI_STAGES) {
           mbar_wait(empty + s, ((kb / GI_STAGES) - 1) & 1);
-          mbar_expect_tx(full + s, GI_STAGE_BYTES);
-          bulk_g2s(st + 16384, g.W + ((size_t)kb * g.Nw + n0) * 64, 8192, full + s);
+          mbar_expect_tx(full + s, STAGE);
+          const bf16* wsrc = g.W + ((size_t)kb * g.Nw + n0) * 64;
+#pragma unroll
+          for (int c = 0; c < NS; ++c) bulk_g2s(st + c * GI_STAGE_BYTES + 16384, wsrc + c * g.W_lo, 8192, full + s);
         }
-        bulk_g2s(st, g.A + ((size_t)kb * g.Rp + m0) * 64, 16384, full + s);
+        const bf16* asrc = g.A + ((size_t)kb * g.Rp + m0) * 64;
+#pragma unroll
+        for (int c = 0; c < NS; ++c) bulk_g2s(st + c * GI_STAGE_BYTES, asrc + c * g.A_lo, 16384, full + s);
       }
     }
     __syncwarp();
@@ -89,10 +104,14 @@ __global__ void __launch_bounds__(256, 1) gemm_img_tc_kernel(const GemmImgArgs g
       const int s = kb % GI_STAGES;
       mbar_wait(full + s, (kb / GI_STAGES) & 1);
       tc_fence_after();
-      const uint32_t sa = smem_u32(sm + s * GI_STAGE_BYTES), sb = sa + 16384;
+      const uint32_t sa = smem_u32(sm + s * STAGE), sb = sa + 16384;
       if (elect_one()) {
 #pragma unroll
-        for (int k = 0; k < 4; ++k) umma(tm, umma_desc(sa + k * 32), umma_desc(sb + k * 32), idesc, (kb | k) ? 1u : 0u);
+        for (int k = 0; k < 4; ++k)
+#pragma unroll
+          for (int ps = 0; ps < SplitPasses<NS>::N; ++ps)
+            umma(tm, umma_desc(sa + SplitPasses<NS>::a(ps) * GI_STAGE_BYTES + k * 32), umma_desc(sb + SplitPasses<NS>::b(ps) * GI_STAGE_BYTES + k * 32),
+                 idesc, (kb | k | ps) ? 1u : 0u);
         umma_commit(empty + s);
         if (kb == g.nkb - 1) umma_commit(done);
       }
@@ -139,12 +158,14 @@ __global__ void __launch_bounds__(256, 1) gemm_img_tc_kernel(const GemmImgArgs g
       uint8_t* row = reinterpret_cast<uint8_t*>(g.O + ((size_t)blockIdx.x * g.Rp + m) * 64);
 #pragma unroll
       for (int ch = 0; ch < 4; ++ch) {
-        uint4 w;
-        w.x = pack_bf16(o[8 * ch + 0], o[8 * ch + 1]);
-        w.y = pack_bf16(o[8 * ch + 2], o[8 * ch + 3]);
-        w.z = pack_bf16(o[8 * ch + 4], o[8 * ch + 5]);
-        w.w = pack_bf16(o[8 * ch + 6], o[8 * ch + 7]);
-        *reinterpret_cast<uint4*>(row + (((h * 4 + ch) ^ (m & 7u)) << 4)) = w;
+        uint32_t c0[NS], c1[NS], c2[NS], c3[NS];
+        split_bf16x2_n<NS>(o[8 * ch + 0], o[8 * ch + 1], c0);
+        split_bf16x2_n<NS>(o[8 * ch + 2], o[8 * ch + 3], c1);
+        split_bf16x2_n<NS>(o[8 * ch + 4], o[8 * ch + 5], c2);
+        split_bf16x2_n<NS>(o[8 * ch + 6], o[8 * ch + 7], c3);
+#pragma unroll
+        for (int c = 0; c < NS; ++c)
+          *reinterpret_cast<uint4*>(row + (size_t)c * g.O_lo * 2 + (((h * 4 + ch) ^ (m & 7u)) << 4)) = make_uint4(c0[c], c1[c], c2[c], c3[c]);
       }
     }
   }
@@ -159,9 +180,9 @@ __global__ void __launch_bounds__(256, 1) gemm_img_tc_kernel(const GemmImgArgs g
 // ---------------------------------------------------------------------------------------------
 __global__ void ln_img_kernel(const float* __restrict__ in, float* __restrict__ out, float* __restrict__ out2,
                               bf16* __restrict__ img, const float* __restrict__ gamma, const float* __restrict__ beta,
-                              int R, int C, int Rp, int normalize, const float* __restrict__ Wbb = nullptr,
-                              const float* __restrict__ bbb = nullptr, float* __restrict__ rots = nullptr,
-                              float* __restrict__ trans = nullptr) {
+                              int R, int C, int Rp, int normalize, const float* __restrict__ Wbb,
+                              const float* __restrict__ bbb, float* __restrict__ rots,
+                              float* __restrict__ trans, size_t img_lo, int ns /* split components of the image, img_lo elements apart */) {
   const int row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   pdl_wait();
   pdl_launch();
@@ -199,11 +220,13 @@ __global__ void ln_img_kernel(const float* __restrict__ in, float* __restrict__ 
     if (out) st4(out + (size_t)row * C + c, v[q]);
     if (out2) st4(out2 + (size_t)row * C + c, v[q]);
     if (img) {
-      uint2 o;
-      o.x = pack_bf16(v[q].x, v[q].y);
-      o.y = pack_bf16(v[q].z, v[q].w);
-      uint8_t* dst = reinterpret_cast<uint8_t*>(img + ((size_t)(c >> 6) * Rp + row) * 64);
-      *reinterpret_cast<uint2*>(dst + (((uint32_t)((c & 63) >> 3) ^ (row & 7u)) << 4) + ((c & 7) >> 2) * 8) = o;
+      uint2 o, ol;
+      split_bf16x2(v[q].x, v[q].y, o.x, ol.x);
+      split_bf16x2(v[q].z, v[q].w, o.y, ol.y);
+      uint8_t* dst = reinterpret_cast<uint8_t*>(img + ((size_t)(c >> 6) * Rp + row) * 64) +
+                     (((uint32_t)((c & 63) >> 3) ^ (row & 7u)) << 4) + ((c & 7) >> 2) * 8;
+      *reinterpret_cast<uint2*>(dst) = o;
+      if (ns > 1) *reinterpret_cast<uint2*>(dst + img_lo * 2) = ol;
     }
   }
   if (Wbb) {
@@ -271,23 +294,29 @@ __global__ void split_img_kernel(const float* __restrict__ in, bf16* __restrict_
 // ---------------------------------------------------------------------------------------------
 // ipa_prep_tc_kernel (once per denoiser eval, after the pair stack).  p does not change across the
 // structure layers, so for all layers l at once:
-//   pbias[l][b][i][h][j] = sqrt(1/3) * (linear_b_l(z_ij)[h]) + 1e5 * (m_i m_j - 1)
-//                                          (invariant_point_attention.py:184-190,206-212)
+//   pbias[l][b][i][h][j] = sqrt(1/3) * (linear_b_l(z_ij)[h])      (invariant_point_attention.py:184-190)
+// (the mask term 1e5 (m_i m_j - 1) of :206-212 is added by the attention kernel, last, as the reference does: on a masked
+//  query row every logit sits at -1e5 where fp32 has 7 fractional bits, so the ORDER of the additions decides the result)
 //   z_img[b][i][mb][j][64]  bf16 copy of z_ij[64 mb ..], chunk-swizzled by j & 7: for a fixed query
 //                           row i this is the MN-major (channel-contiguous) A operand of o_pair.
 // One CTA = 128 pixels (2 rows x 64 cols); Wb image [2 kb][96 rows = l*12+h][64]; bias96 pre-scaled.
 // ---------------------------------------------------------------------------------------------
-#define PREP_SMEM (32768 + 24576 + 1024 + 64)
+// NS = 2 (GB_PREC_BF16X3): A, the Wb image (components directly behind each other) and z_img (`z_lo` elements apart) are
+// hi | lo split components and the pair-bias GEMM runs the passes of SplitPasses<NS>; two CTAs per SM instead of three.
+template <int NS> struct PrepSmem {
+  static constexpr uint32_t A = NS * 32768, W = NS * 24576, TOTAL = A + W + 1024 + 64;
+};
 
-__global__ void __launch_bounds__(256, 3) ipa_prep_tc_kernel(const float* __restrict__ p, int B, int N, int Np,
-                                                             const int* __restrict__ rmask, const bf16* __restrict__ Wimg,
+template <int NS>
+__global__ void __launch_bounds__(256, NS == 1 ? 3 : 2) ipa_prep_tc_kernel(const float* __restrict__ p, int B, int N, int Np,
+                                                             const bf16* __restrict__ Wimg,
                                                              const float* __restrict__ bias96, float* __restrict__ pbias,
-                                                             bf16* __restrict__ z_img, int ncol, const TileRange tr) {
+                                                             bf16* __restrict__ z_img, int ncol, const TileRange tr, size_t z_lo) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* sm = smem_base_1024(smem_raw);
   uint8_t* A = sm;
-  uint8_t* W = sm + 32768;
-  uint64_t* bar_w = reinterpret_cast<uint64_t*>(sm + 32768 + 24576);
+  uint8_t* W = sm + PrepSmem<NS>::A;
+  uint64_t* bar_w = reinterpret_cast<uint64_t*>(sm + PrepSmem<NS>::A + PrepSmem<NS>::W);
   uint64_t* bar_mma = bar_w + 1;
   uint32_t* tslot = reinterpret_cast<uint32_t*>(bar_w + 2);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -296,8 +325,8 @@ __global__ void __launch_bounds__(256, 3) ipa_prep_tc_kernel(const float* __rest
     mbar_init(bar_w, 1);
     mbar_init(bar_mma, 1);
     fence_mbar_init();
-    mbar_expect_tx(bar_w, 24576);
-    bulk_g2s(W, Wimg, 24576, bar_w);
+    mbar_expect_tx(bar_w, PrepSmem<NS>::W);
+    bulk_g2s(W, Wimg, PrepSmem<NS>::W, bar_w);
   }
   if (warp == 1) tmem_alloc(tslot, 128);
   pdl_wait();            // p comes from the last pair-transition kernel
@@ -316,14 +345,16 @@ __global__ void __launch_bounds__(256, 3) ipa_prep_tc_kernel(const float* __rest
 #pragma unroll
       for (int u = 0; u < 4; ++u) {
         const uint32_t m = warp * 16 + it * 4 + u, i = 2 * T.t2 + (m >> 6), j = 64 * T.jb + (m & 63);
-        uint2 o;
-        o.x = pack_bf16(v[u].x, v[u].y);
-        o.y = pack_bf16(v[u].z, v[u].w);
+        uint32_t cx[NS], cy[NS];
+        split_bf16x2_n<NS>(v[u].x, v[u].y, cx);
+        split_bf16x2_n<NS>(v[u].z, v[u].w, cy);
         const uint32_t inrow = ((chunk ^ (m & 7u)) << 4) + half * 8u;
-        *reinterpret_cast<uint2*>(A + kb * 16384u + m * 128u + inrow) = o;
+#pragma unroll
+        for (int c = 0; c < NS; ++c) *reinterpret_cast<uint2*>(A + c * 32768u + kb * 16384u + m * 128u + inrow) = make_uint2(cx[c], cy[c]);
         if (ok[u]) {
           uint8_t* zr = reinterpret_cast<uint8_t*>(z_img) + ((((size_t)T.b * N + i) * 2 + kb) * Np + j) * 128;
-          *reinterpret_cast<uint2*>(zr + inrow) = o;
+#pragma unroll
+          for (int c = 0; c < NS; ++c) *reinterpret_cast<uint2*>(zr + (size_t)c * z_lo * 2 + inrow) = make_uint2(cx[c], cy[c]);
         }
       }
     }
@@ -337,7 +368,9 @@ __global__ void __launch_bounds__(256, 3) ipa_prep_tc_kernel(const float* __rest
   if (tid == 0) {
     mbar_wait(bar_w, 0);
     tc_fence_after();
-    umma_tile(tmem, smem_u32(A), smem_u32(W), 96, 2, false);
+#pragma unroll
+    for (int ps = 0; ps < SplitPasses<NS>::N; ++ps)
+      umma_tile(tmem, smem_u32(A) + SplitPasses<NS>::a(ps) * 32768u, smem_u32(W) + SplitPasses<NS>::b(ps) * 24576u, 96, 2, ps > 0);
     umma_commit(bar_mma);
   }
   __syncwarp();
@@ -346,8 +379,6 @@ __global__ void __launch_bounds__(256, 3) ipa_prep_tc_kernel(const float* __rest
   const uint32_t q = warp & 3, h = warp >> 2, m = q * 32 + lane;
   const uint32_t i = 2 * T.t2 + (m >> 6), j = 64 * T.jb + (m & 63);
   const bool valid = i < (uint32_t)N && j < (uint32_t)N;
-  float mterm = 0.f;
-  if (valid) mterm = 1e5f * ((float)(rmask[T.b * N + i] * rmask[T.b * N + j]) - 1.f);
   for (int cc = h; cc < 3; cc += 2) {          // warps 0-3: column chunks 0 and 2; warps 4-7: chunk 1
     uint32_t v[32];
     tmem_ld32(tmem + ((q * 32u) << 16) + cc * 32, v);
@@ -358,7 +389,7 @@ __global__ void __launch_bounds__(256, 3) ipa_prep_tc_kernel(const float* __rest
         const int n = cc * 32 + e;
         if (n < ncol) {
           const int l = n / 12, hh = n - l * 12;
-          pbias[((((size_t)l * B + T.b) * N + i) * 12 + hh) * Np + j] = __uint_as_float(v[e]) + bias96[n] + mterm;
+          pbias[((((size_t)l * B + T.b) * N + i) * 12 + hh) * Np + j] = __uint_as_float(v[e]) + bias96[n];
         }
       }
     }
@@ -430,11 +461,13 @@ __global__ void ipa_points_planes_kernel(float* __restrict__ qkv, const float* _
 // Queries per CTA (template parameter G): every CTA streams the whole K / V of its sample from L2, so that traffic
 // per query is 1 / G; the fp32 logits [12][Np][G] and the probability images must fit in shared memory:
 // G = 8 up to 256 keys, 4 up to 512, 2 up to 1024.
+// ns = 2 (GB_PREC_BF16X3): ring slots hold the hi | lo components of a z chunk (2 x 16 KB), the probability images exist as
+// a hi and a lo set
 struct IaSmem { uint32_t aimg, P, qs, red, fr, bar, total; };
-__host__ __device__ inline IaSmem ia_smem(int G, int Np) {
+__host__ __device__ inline IaSmem ia_smem(int G, int Np, int ns = 1) {
   IaSmem o;
-  o.aimg = IA_ZRING * 16384;
-  o.P = o.aimg + G * (Np >> 6) * 2048;
+  o.aimg = IA_ZRING * ns * 16384;
+  o.P = o.aimg + ns * G * (Np >> 6) * 2048;
   o.qs = o.P + 12 * Np * G * 4;
   o.red = o.qs + G * 12 * 28 * 4;
   o.fr = o.red + G * 480 * 4;
@@ -444,8 +477,10 @@ __host__ __device__ inline IaSmem ia_smem(int G, int Np) {
 }
 // Short chains and small batches: a CTA's fixed cost (prologue, 120 reductions, epilogue) dominates, so take the smallest
 // G that still fits all CTAs in one wave (B * ceil(N / G) <= SMs); otherwise the largest the shared memory allows.
-static inline int ia_queries_per_cta(int Np, int B = 0, int N = 0, int num_sms = 0) {
-  const int gmax = Np <= 256 ? 8 : Np <= 512 ? 4 : 2;
+static inline int ia_queries_per_cta(int Np, int B = 0, int N = 0, int num_sms = 0, int ns = 1) {
+  int gmax = Np <= 256 ? 8 : Np <= 512 ? 4 : 2;
+  if (ns == 2) gmax = gmax > 2 ? gmax / 2 : 0;     // hi | lo probability images: half the queries; Np > 512 does not fit
+  if (gmax == 0) return 0;
   for (int g = 2; g < gmax && num_sms > 0; g *= 2)
     if (B * ((N + g - 1) / g) <= num_sms) return g;
   return gmax;
@@ -478,19 +513,26 @@ template <int G> __device__ __forceinline__ void p_store(float* pp, const float 
 }
 
 // 2-byte store of element k of row r of a [.][Rp][64] operand image
-__device__ __forceinline__ void img_store(bf16* img, int Rp, uint32_t r, uint32_t k, float v) {
-  uint8_t* base = reinterpret_cast<uint8_t*>(img + ((size_t)(k >> 6) * Rp + r) * 64);
-  *reinterpret_cast<bf16*>(base + ((((k & 63) >> 3) ^ (r & 7u)) << 4) + ((k & 7) << 1)) = __float2bfloat16_rn(v);
+template <int NS = 1>
+__device__ __forceinline__ void img_store(bf16* img, int Rp, uint32_t r, uint32_t k, float v, size_t lo = 0) {
+  uint8_t* dst = reinterpret_cast<uint8_t*>(img + ((size_t)(k >> 6) * Rp + r) * 64) + ((((k & 63) >> 3) ^ (r & 7u)) << 4) + ((k & 7) << 1);
+#pragma unroll
+  for (int c = 0; c < NS; ++c) {
+    const bf16 hc = __float2bfloat16_rn(v);
+    *reinterpret_cast<bf16*>(dst + (size_t)c * lo * 2) = hc;
+    v -= __bfloat162float(hc);
+  }
 }
 
-template <int G>
+template <int G, int NS>
 __global__ void __launch_bounds__(IA_THREADS, 1) ipa_attention_tc_kernel(
     const float* __restrict__ qkv, const float* __restrict__ pbias, const bf16* __restrict__ z_img,
     const float* __restrict__ rots, const float* __restrict__ trans, const float* __restrict__ hw,
-    bf16* __restrict__ cat_img, int N, int Np, int Rp, int row0) {
+    bf16* __restrict__ cat_img, int N, int Np, int Rp, int row0, const int* __restrict__ rmask, size_t z_lo, size_t cat_lo) {
+  constexpr uint32_t ZSLOT = NS * 16384u;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* sm = smem_base_1024(smem_raw);
-  const IaSmem L = ia_smem(G, Np);
+  const IaSmem L = ia_smem(G, Np, NS);
   uint8_t* zring = sm;
   uint8_t* aimg = sm + L.aimg;                                 // [g][Np/64 kb][16 rows = head][64 j]
   float* P = reinterpret_cast<float*>(sm + L.P);               // [12 h][Np j][G]
@@ -517,9 +559,12 @@ __global__ void __launch_bounds__(IA_THREADS, 1) ipa_attention_tc_kernel(
     for (int it = 0; it < min(tot, IA_ZRING); ++it) {
       const int g = it / nch, ch = it - g * nch;
       const uint8_t* src = reinterpret_cast<const uint8_t*>(z_img) + ((rowb + i0 + g) * 2 * Np + ch * 64) * 128;
-      mbar_expect_tx(full + it, 16384);
-      bulk_g2s(zring + it * 16384, src, 8192, full + it);
-      bulk_g2s(zring + it * 16384 + 8192, src + (size_t)Np * 128, 8192, full + it);
+      mbar_expect_tx(full + it, ZSLOT);
+#pragma unroll
+      for (int c = 0; c < NS; ++c) {
+        bulk_g2s(zring + it * ZSLOT + c * 16384, src + (size_t)c * z_lo * 2, 8192, full + it);
+        bulk_g2s(zring + it * ZSLOT + c * 16384 + 8192, src + (size_t)c * z_lo * 2 + (size_t)Np * 128, 8192, full + it);
+      }
     }
   }
   if (warp == 2) tmem_alloc(tslot, TCOLS);
@@ -535,7 +580,7 @@ __global__ void __launch_bounds__(IA_THREADS, 1) ipa_attention_tc_kernel(
     }
     qs[e] = v;
   }
-  for (int e = tid; e < (int)(G * aimg_g / 16); e += IA_THREADS) reinterpret_cast<uint4*>(aimg)[e] = make_uint4(0, 0, 0, 0);
+  for (int e = tid; e < (int)(NS * G * aimg_g / 16); e += IA_THREADS) reinterpret_cast<uint4*>(aimg)[e] = make_uint4(0, 0, 0, 0);
   for (int e = tid; e < G * 480; e += IA_THREADS) oacc[e] = 0.f;
   if (tid < G * 12) {
     const int g = tid / 12, x = tid - g * 12;
@@ -551,8 +596,12 @@ __global__ void __launch_bounds__(IA_THREADS, 1) ipa_attention_tc_kernel(
   {
     constexpr int HPG = 12 / (IA_THREADS / 256);   // heads per thread group
     const int hg = tid >> 8;
+    float mq[G];                                  // residue masks of the G queries
+#pragma unroll
+    for (int g = 0; g < G; ++g) mq[g] = g < ng ? (float)rmask[rowb + i0 + g] : 0.f;
     for (int j = tid & 255; j < Np; j += 256) {
       const bool kv = j < N;
+      const float mk = kv ? (float)rmask[rowb + j] : 0.f;
       const float4* kpl = reinterpret_cast<const float4*>(qkv + (size_t)gridDim.y * N * IPA_QW) + (size_t)b * IPA_NPLANE * N + (kv ? j : 0);
 #pragma unroll
       for (int hh = 0; hh < HPG; ++hh) {       // unrolled: the K planes and pair-bias words of later heads are in flight early
@@ -589,7 +638,8 @@ __global__ void __launch_bounds__(IA_THREADS, 1) ipa_attention_tc_kernel(
             }
             float pb = 0.f;
             if (g < ng) pb = pbias[((rowb + i0 + g) * 12 + h) * Np + j];
-            out[g] = (qk.x + qk.y) + pb + gam * (d2.x + d2.y);
+            // the reference's order (invariant_point_attention.py:181-212): q.k, + pair bias, + point term, + mask term LAST
+            out[g] = (((qk.x + qk.y) + pb) + gam * (d2.x + d2.y)) + 1e5f * (mq[g] * mk - 1.f);
           }
         }
         p_store<G>(P + ((size_t)h * Np + j) * G, out);
@@ -625,7 +675,13 @@ __global__ void __launch_bounds__(IA_THREADS, 1) ipa_attention_tc_kernel(
 #pragma unroll
       for (int g = 0; g < G; ++g) {
         t[g] *= sum[g];
-        *reinterpret_cast<bf16*>(aimg + g * aimg_g + off) = __float2bfloat16_rn(t[g]);
+        float rest = t[g];
+#pragma unroll
+        for (int c = 0; c < NS; ++c) {
+          const bf16 hc = __float2bfloat16_rn(rest);
+          *reinterpret_cast<bf16*>(aimg + (c * G + g) * aimg_g + off) = hc;
+          rest -= __bfloat162float(hc);
+        }
       }
       p_store<G>(pp, t);
     }
@@ -640,9 +696,12 @@ __global__ void __launch_bounds__(IA_THREADS, 1) ipa_attention_tc_kernel(
         const int s = it % IA_ZRING, g = it / nch, ch = it - g * nch;
         mbar_wait(empty + s, ((it / IA_ZRING) - 1) & 1);
         const uint8_t* src = reinterpret_cast<const uint8_t*>(z_img) + ((rowb + i0 + g) * 2 * Np + ch * 64) * 128;
-        mbar_expect_tx(full + s, 16384);
-        bulk_g2s(zring + s * 16384, src, 8192, full + s);
-        bulk_g2s(zring + s * 16384 + 8192, src + (size_t)Np * 128, 8192, full + s);
+        mbar_expect_tx(full + s, ZSLOT);
+#pragma unroll
+        for (int c = 0; c < NS; ++c) {
+          bulk_g2s(zring + s * ZSLOT + c * 16384, src + (size_t)c * z_lo * 2, 8192, full + s);
+          bulk_g2s(zring + s * ZSLOT + c * 16384 + 8192, src + (size_t)c * z_lo * 2 + (size_t)Np * 128, 8192, full + s);
+        }
       }
     }
     __syncwarp();
@@ -655,10 +714,13 @@ __global__ void __launch_bounds__(IA_THREADS, 1) ipa_attention_tc_kernel(
           const int s = it % IA_ZRING;
           mbar_wait(full + s, (it / IA_ZRING) & 1);
           tc_fence_after();
-          const uint32_t za = smem_u32(zring + s * 16384), ab = smem_u32(aimg + g * aimg_g + ch * 2048);
+          const uint32_t za = smem_u32(zring + s * ZSLOT), ab = smem_u32(aimg + g * aimg_g + ch * 2048);
 #pragma unroll
           for (int k = 0; k < 4; ++k)
-            umma(tmem + g * 16, umma_desc_mn(za + k * 2048, 8192), umma_desc(ab + k * 32), idesc, (ch | k) ? 1u : 0u);
+#pragma unroll
+            for (int ps = 0; ps < SplitPasses<NS>::N; ++ps)
+              umma(tmem + g * 16, umma_desc_mn(za + SplitPasses<NS>::a(ps) * 16384 + k * 2048, 8192),
+                   umma_desc(ab + SplitPasses<NS>::b(ps) * G * aimg_g + k * 32), idesc, (ch | k | ps) ? 1u : 0u);
           umma_commit(empty + s);
         }
         umma_commit(done + g);
@@ -731,7 +793,7 @@ __global__ void __launch_bounds__(IA_THREADS, 1) ipa_attention_tc_kernel(
   // ---- 4. inverse frame + norm (invariant_point_attention.py:227-240)
   for (int e = tid; e < ng * 192; e += IA_THREADS) {
     const int g = e / 192, x = e - g * 192;
-    img_store(cat_img, Rp, (uint32_t)(rowb + i0 + g), x, oacc[g * 480 + (x >> 4) * 40 + (x & 15)]);
+    img_store<NS>(cat_img, Rp, (uint32_t)(rowb + i0 + g), x, oacc[g * 480 + (x >> 4) * 40 + (x & 15)], cat_lo);
   }
   for (int e = tid; e < ng * 96; e += IA_THREADS) {
     const int g = e / 96, pt = e - g * 96;
@@ -740,10 +802,10 @@ __global__ void __launch_bounds__(IA_THREADS, 1) ipa_attention_tc_kernel(
     const float x = op[0] - R[9], y = op[8] - R[10], zc = op[16] - R[11];
     const float lx = R[0] * x + R[3] * y + R[6] * zc, ly = R[1] * x + R[4] * y + R[7] * zc, lz = R[2] * x + R[5] * y + R[8] * zc;
     const uint32_t r = (uint32_t)(rowb + i0 + g);
-    img_store(cat_img, Rp, r, 192 + pt, lx);
-    img_store(cat_img, Rp, r, 288 + pt, ly);
-    img_store(cat_img, Rp, r, 384 + pt, lz);
-    img_store(cat_img, Rp, r, 480 + pt, sqrtf(lx * lx + ly * ly + lz * lz + 1e-8f));
+    img_store<NS>(cat_img, Rp, r, 192 + pt, lx, cat_lo);
+    img_store<NS>(cat_img, Rp, r, 288 + pt, ly, cat_lo);
+    img_store<NS>(cat_img, Rp, r, 384 + pt, lz, cat_lo);
+    img_store<NS>(cat_img, Rp, r, 480 + pt, sqrtf(lx * lx + ly * ly + lz * lz + 1e-8f), cat_lo);
   }
   // o_pair: TMEM lane = channel c, columns 16 g + h
   {
@@ -757,7 +819,7 @@ __global__ void __launch_bounds__(IA_THREADS, 1) ipa_attention_tc_kernel(
       tmem_ld_wait();
       const uint32_t r = (uint32_t)(rowb + i0 + g);
 #pragma unroll
-      for (int h = 0; h < 12; ++h) img_store(cat_img, Rp, r, 576 + h * 128 + c, __uint_as_float(v[h]));
+      for (int h = 0; h < 12; ++h) img_store<NS>(cat_img, Rp, r, 576 + h * 128 + c, __uint_as_float(v[h]), cat_lo);
     }
   }
   tc_fence_before();
