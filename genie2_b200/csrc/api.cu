@@ -709,9 +709,14 @@ extern "C" int gb_denoise(gb_ctx* c, const float* rots, const float* trans, cons
   GB_LAUNCH_CHECK(c, "single_combine");
   if (aux && aux->s) GB_CUDA(c, cudaMemcpyAsync(aux->s, c->s, Rcs * 4, cudaMemcpyDeviceToDevice, st));
   if (aux && aux->states) GB_CUDA(c, cudaMemcpyAsync(aux->states, c->s, Rcs * 4, cudaMemcpyDeviceToDevice, st));
-  // PairFeatureNet
+  // PairFeatureNet.  Tensor-core modes never drop to the CUDA-core kernels silently: a shape the tensor-core structure
+  // path does not cover is an error (use GB_PREC_FP32).  GB_PIPJ_TC=0 / GB_PE_TC=0 are explicit debugging switches.
+  const bool tcmode = c->precision != GB_PREC_FP32;
+  if (tcmode && !(tc_struct_supported(c, N) && tc_pipj_supported(c)))
+    return gb_fail(c, GB_ERR_UNSUPPORTED, "tensor-core modes need c_s %% 128 == 0, c_s <= 512, N <= 1024 and n_structure_layer <= 8 (got c_s = %d, N = %d); use fp32",
+                   cs, N);
   static const int pipj_tc = [] { const char* e = getenv("GB_PIPJ_TC"); return e ? atoi(e) : 1; }();
-  if (pipj_tc && c->precision == GB_PREC_BF16 && tc_struct_supported(c, N) && tc_pipj_supported(c)) {
+  if (pipj_tc && tcmode) {
     if ((rc = tc_pair_pipj(c, st))) return rc;
   } else {
     sgemm_nt(st, c->s, cs, c->W_pipj, cs, nullptr, nullptr, 0, c->pipj, 256, R, 256, cs, false);
@@ -719,9 +724,12 @@ extern "C" int gb_denoise(gb_ctx* c, const float* rots, const float* trans, cons
   }
   const int W = c->shard_world, rows_l = N / W, row0 = c->shard_rank * rows_l;   // W == 1: all rows
   static const int pe_tc = [] { const char* e = getenv("GB_PE_TC"); return e ? atoi(e) : 1; }();
-  if (pe_tc && c->precision == GB_PREC_BF16 && tc_pair_embed_supported(c)) {
+  if (c->precision == GB_PREC_BF16 && !tc_pair_embed_supported(c))
+    return gb_fail(c, GB_ERR_UNSUPPORTED, "bf16 pair embedding: packed feature weights missing (template_dist_n_bin must be 37)");
+  if (pe_tc && c->precision == GB_PREC_BF16) {
     if ((rc = tc_pair_embed(c, aux ? aux->quat_follow : nullptr, rows_l, row0, st))) return rc;
   } else {
+    // fp32 and bf16x3: the 41- / 78-term feature dot on CUDA cores in fp32 (one launch per eval)
   pair_embed_kernel<37><<<dim3(rows_l, B), 128, 0, st>>>(c->p, c->pipj, c->rots_w, c->trans_w, c->residue_index, c->chain_index, c->mask,
                                                     c->fsm, c->fst, c->motif_pos, c->WrelT, c->WtT, c->WmT,
                                                     aux ? aux->quat_follow : nullptr, N, d.relpos_k, d.template_dist_min,
@@ -748,8 +756,7 @@ extern "C" int gb_denoise(gb_ctx* c, const float* rots, const float* trans, cons
   // StructureNet
   float* s = c->s;
   int state_idx = 1;
-  const bool tc_struct = c->precision == GB_PREC_BF16 && tc_struct_supported(c, N);
-  if (tc_struct) {
+  if (tcmode) {
     if ((rc = tc_structure_net(c, aux ? aux->states : nullptr, st))) return rc;
   } else
   for (int blk = 0; blk < d.n_structure_block; ++blk)

@@ -834,11 +834,15 @@ static size_t al256(size_t v) { return (v + 255) & ~(size_t)255; }
 
 int tc_struct_init(gb_ctx* c) {
   cudaError_t e;
-  if ((e = cudaFuncSetAttribute(gemm_img_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, GI_SMEM)) != cudaSuccess ||
-      (e = cudaFuncSetAttribute(ipa_prep_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PREP_SMEM)) != cudaSuccess ||
-      (e = cudaFuncSetAttribute(ipa_attention_tc_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, ia_smem(8, 256).total)) != cudaSuccess ||
-      (e = cudaFuncSetAttribute(ipa_attention_tc_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, ia_smem(4, 512).total)) != cudaSuccess ||
-      (e = cudaFuncSetAttribute(ipa_attention_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, ia_smem(2, 1024).total)) != cudaSuccess)
+  if ((e = cudaFuncSetAttribute(gemm_img_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, GI<1>::SMEM)) != cudaSuccess ||
+      (e = cudaFuncSetAttribute(gemm_img_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, GI<2>::SMEM)) != cudaSuccess ||
+      (e = cudaFuncSetAttribute(ipa_prep_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, PrepSmem<1>::TOTAL)) != cudaSuccess ||
+      (e = cudaFuncSetAttribute(ipa_prep_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, PrepSmem<2>::TOTAL)) != cudaSuccess ||
+      (e = cudaFuncSetAttribute(ipa_attention_tc_kernel<8, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, ia_smem(8, 256).total)) != cudaSuccess ||
+      (e = cudaFuncSetAttribute(ipa_attention_tc_kernel<4, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, ia_smem(4, 512).total)) != cudaSuccess ||
+      (e = cudaFuncSetAttribute(ipa_attention_tc_kernel<2, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, ia_smem(2, 1024).total)) != cudaSuccess ||
+      (e = cudaFuncSetAttribute(ipa_attention_tc_kernel<4, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, ia_smem(4, 256, 2).total)) != cudaSuccess ||
+      (e = cudaFuncSetAttribute(ipa_attention_tc_kernel<2, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, ia_smem(2, 512, 2).total)) != cudaSuccess)
     return gb_fail(c, GB_ERR_CUDA, "tc_struct_init: cudaFuncSetAttribute failed: %s", cudaGetErrorString(e));
   return GB_OK;
 }
@@ -848,12 +852,18 @@ bool tc_struct_supported(const gb_ctx* c, int N) {
   return cs % 128 == 0 && cs <= 512 && N <= 1024 && c->d.n_structure_layer * IPA_H <= 96;
 }
 
-size_t tc_struct_workspace_bytes(const gb_ctx* c, int B, int N) {
-  if (!tc_struct_supported(c, N)) return 0;
+// bytes of the block of bf16 images [s | ln1 | h1 | h2 | cat | z]; GB_PREC_BF16X3 keeps the lo component of every image in a
+// second block of the same layout behind it
+static size_t struct_img_block(const gb_ctx* c, int B, int N) {
   const size_t Np = (size_t)((N + 63) / 64) * 64, Rp = ((size_t)B * N + 127) / 128 * 128;
   const size_t kcs = c->d.c_s / 64;
-  return 4 * al256(kcs * Rp * 128) + al256((size_t)(IPA_CAT / 64) * Rp * 128) + al256((size_t)B * N * 2 * Np * 128) +
-         al256((size_t)c->d.n_structure_layer * B * N * IPA_H * Np * 4) + 1024;
+  return 4 * al256(kcs * Rp * 128) + al256((size_t)(IPA_CAT / 64) * Rp * 128) + al256((size_t)B * N * 2 * Np * 128);
+}
+
+size_t tc_struct_workspace_bytes(const gb_ctx* c, int B, int N) {
+  if (!tc_struct_supported(c, N)) return 0;
+  const size_t Np = (size_t)((N + 63) / 64) * 64;
+  return 2 * struct_img_block(c, B, N) + al256((size_t)c->d.n_structure_layer * B * N * IPA_H * Np * 4) + 1024;
 }
 
 int tc_struct_bind(gb_ctx* c, void* base, size_t bytes, int B, int N) {
@@ -861,9 +871,9 @@ int tc_struct_bind(gb_ctx* c, void* base, size_t bytes, int B, int N) {
   s->Rp = 0;
   if (!tc_struct_supported(c, N)) return GB_OK;
   if (bytes < tc_struct_workspace_bytes(c, B, N) - 1024) return gb_fail(c, GB_ERR_INVALID, "tc_struct_bind: too small");
-  const size_t Np = (size_t)((N + 63) / 64) * 64, Rp = ((size_t)B * N + 127) / 128 * 128;
+  const size_t Rp = ((size_t)B * N + 127) / 128 * 128;
   const size_t kcs = c->d.c_s / 64, act = al256(kcs * Rp * 128), cat = al256((size_t)(IPA_CAT / 64) * Rp * 128);
-  const size_t zb = al256((size_t)B * N * 2 * Np * 128);
+  const size_t blk = struct_img_block(c, B, N);
   char* q = static_cast<char*>(base);
   s->s_img = reinterpret_cast<bf16*>(q);
   s->ln1_img = reinterpret_cast<bf16*>(q + act);
@@ -871,18 +881,26 @@ int tc_struct_bind(gb_ctx* c, void* base, size_t bytes, int B, int N) {
   s->h2_img = reinterpret_cast<bf16*>(q + 3 * act);
   s->cat_img = reinterpret_cast<bf16*>(q + 4 * act);
   s->z_img = reinterpret_cast<bf16*>(q + 4 * act + cat);
-  s->pbias = reinterpret_cast<float*>(q + 4 * act + cat + zb);
+  s->img_lo = blk / 2;                      // elements from any of the images above to its lo twin
+  s->pbias = reinterpret_cast<float*>(q + 2 * blk);
   s->Rp = (int)Rp;
   // padded rows of the activation images and padded keys of z_img feed MMAs: keep them finite (zero)
-  if (cudaMemset(q, 0, 4 * act + cat + zb) != cudaSuccess) return gb_fail(c, GB_ERR_CUDA, "tc_struct_bind: memset failed");
+  if (cudaMemset(q, 0, 2 * blk) != cudaSuccess) return gb_fail(c, GB_ERR_CUDA, "tc_struct_bind: memset failed");
   return GB_OK;
 }
 
-// W [N][K] fp32 (nn.Linear layout) -> operand image [K/64][N][64]
-static bf16* pack_linear(gb_ctx* c, const std::vector<float>& w, int N, int K) {
-  std::vector<uint16_t> img((size_t)N * K);
-  pack_image(img.data(), N, K, [&](int r, int k) { return w[(size_t)r * K + k]; });
+// rows x K matrix at(r, k) -> two operand images [K/64][rows][64]: hi | lo split components (GB_PREC_BF16X3 reads both, the
+// bf16 mode the first)
+template <typename F>
+static bf16* pack_split2(gb_ctx* c, int rows, int K, F at) {
+  std::vector<uint16_t> img((size_t)2 * rows * K);
+  pack_image(img.data(), rows, K, at);
+  pack_image(img.data() + (size_t)rows * K, rows, K, [&](int r, int k) { return bf_lo(at(r, k)); });
   return (bf16*)upload_bytes(c, img.data(), img.size() * 2);
+}
+// W [N][K] fp32 (nn.Linear layout)
+static bf16* pack_linear(gb_ctx* c, const std::vector<float>& w, int N, int K) {
+  return pack_split2(c, N, K, [&](int r, int k) { return w[(size_t)r * K + k]; });
 }
 
 int tc_pack_struct_layer(gb_ctx* c, int l, const std::vector<float>& wqkv, const std::vector<float>& bqkv, const std::vector<float>& wout,
@@ -895,9 +913,7 @@ int tc_pack_struct_layer(gb_ctx* c, int l, const std::vector<float>& wqkv, const
   w = TcStructW();
   {
     // output columns reordered: q | q_pts | key-major planes (h, e) of 4 floats (ipa_dims.h)
-    std::vector<uint16_t> img((size_t)IPA_QKV * cs);
-    pack_image(img.data(), IPA_QKV, cs, [&](int r, int k) { return wqkv[(size_t)ipa_old_col(r) * cs + k]; });
-    w.Wqkv = (bf16*)upload_bytes(c, img.data(), img.size() * 2);
+    w.Wqkv = pack_split2(c, IPA_QKV, cs, [&](int r, int k) { return wqkv[(size_t)ipa_old_col(r) * cs + k]; });
     std::vector<float> bp(IPA_QKV);
     for (int r = 0; r < IPA_QKV; ++r) bp[r] = bqkv[ipa_old_col(r)];
     w.bqkv = (float*)upload_bytes(c, bp.data(), bp.size() * 4);
@@ -912,30 +928,34 @@ int tc_pack_struct_layer(gb_ctx* c, int l, const std::vector<float>& wqkv, const
   return GB_OK;
 }
 
-// linear_b of every structure layer stacked into one 128 -> 96 projection, sqrt(1/3) folded in
+// linear_b of every structure layer stacked into one 128 -> 96 projection, sqrt(1/3) folded in; hi | lo images
 int tc_pack_ipa_bias(gb_ctx* c, const std::vector<const std::vector<float>*>& wb, const std::vector<const std::vector<float>*>& bb) {
   TcState* s = static_cast<TcState*>(c->tc_state);
   const int L = (int)wb.size();
   if (L * IPA_H > 96) return GB_OK;
   const float sc = sqrtf(1.f / 3.f);
-  std::vector<uint16_t> img(96 * 128);
-  pack_image(img.data(), 96, 128, [&](int r, int k) { return r < L * IPA_H ? sc * (*wb[r / IPA_H])[(size_t)(r % IPA_H) * 128 + k] : 0.f; });
+  auto at = [&](int r, int k) { return r < L * IPA_H ? sc * (*wb[r / IPA_H])[(size_t)(r % IPA_H) * 128 + k] : 0.f; };
   std::vector<float> b96(96, 0.f);
   for (int r = 0; r < L * IPA_H; ++r) b96[r] = sc * (*bb[r / IPA_H])[r % IPA_H];
-  s->Wb_img = (bf16*)upload_bytes(c, img.data(), img.size() * 2);
+  s->Wb_img = pack_split2(c, 96, 128, at);
   s->bias96 = (float*)upload_bytes(c, b96.data(), b96.size() * 4);
   if (!s->Wb_img || !s->bias96) return gb_fail(c, GB_ERR_CUDA, "tc_pack_ipa_bias: device allocation failed");
   return GB_OK;
 }
 
+// x3: A / O are images with their lo twins `img_lo` elements behind, W is hi | lo images of K * Nw elements each
 static int gemm_img(gb_ctx* c, cudaStream_t st, const bf16* A, int K, const bf16* W, int Nw, const float* bias, const float* res,
-                    int ldr, float* C, int ldc, bf16* O, bool relu, int kvsplit = 0, int mblk0 = 0, int nmblk = 0) {
+                    int ldr, float* C, int ldc, bf16* O, bool relu, int kvsplit = 0, int mblk0 = 0, int nmblk = 0, bool x3 = false) {
   TcState* s = static_cast<TcState*>(c->tc_state);
   GemmImgArgs g;
   g.mblk0 = mblk0;
   g.A = A; g.W = W; g.bias = bias; g.res = res; g.C = C; g.O = O;
   g.Rp = s->Rp; g.Nw = Nw; g.nkb = K / 64; g.R = c->B * c->N; g.ldc = ldc; g.ldr = ldr; g.relu = relu ? 1 : 0; g.kvsplit = kvsplit;
-  launch_pdl(gemm_img_tc_kernel, dim3(Nw / 64, nmblk ? nmblk : s->Rp / 128), 256, GI_SMEM, st, g);
+  g.A_lo = g.O_lo = s->img_lo;
+  g.W_lo = (size_t)K * Nw;
+  const dim3 grid(Nw / 64, nmblk ? nmblk : s->Rp / 128);
+  if (x3) launch_pdl(gemm_img_tc_kernel<2>, grid, 256, GI<2>::SMEM, st, g);
+  else launch_pdl(gemm_img_tc_kernel<1>, grid, 256, GI<1>::SMEM, st, g);
   GB_LAUNCH_CHECK(c, "gemm_img_tc");
   return GB_OK;
 }
@@ -953,11 +973,7 @@ int tc_pack_pipj(gb_ctx* c, const std::vector<float>& wij /*[256][c_s]*/) {
   std::vector<uint16_t> img((size_t)256 * 3 * cs);
   pack_image(img.data(), 256, 3 * cs, [&](int r, int k) -> float {
     const float w = wij[(size_t)r * cs + k % cs];
-    if (k < 2 * cs) return w;
-    const uint32_t bits = (uint32_t)f2bf(w) << 16;
-    float hi;
-    memcpy(&hi, &bits, 4);
-    return w - hi;
+    return k < 2 * cs ? w : bf_lo(w);
   });
   s->Wpipj_img = (bf16*)upload_bytes(c, img.data(), img.size() * 2);
   if (!s->Wpipj_img) return gb_fail(c, GB_ERR_CUDA, "tc_pack_pipj: device allocation failed");
@@ -977,30 +993,43 @@ int tc_pair_pipj(gb_ctx* c, cudaStream_t st) {
   const size_t stride = (size_t)(s->ln1_img - s->s_img);
   launch_pdl(split_img_kernel, (unsigned)((R * 32 + 255) / 256), 256, 0, st, (const float*)c->s, s->s_img, R, cs, s->Rp, stride);
   GB_LAUNCH_CHECK(c, "s_split_img");
-  s->s_img_valid = true;
+  s->s_img_valid = c->precision == GB_PREC_BF16;      // (the split mode also needs the lo twin of s_img: tc_structure_net makes both)
   return gemm_img(c, st, s->s_img, 3 * cs, s->Wpipj_img, 256, nullptr, nullptr, 0, c->pipj, 256, nullptr, false);
 }
 
-// StructureNet.forward (structure_net.py:189-243) on c->s / c->p / c->rots_w / c->trans_w, bf16 mode.
+static void launch_ln(gb_ctx* c, cudaStream_t st, const float* in, float* out, float* out2, bf16* img, const float* gamma, const float* beta,
+                      int normalize, const StructLayerW* bb, bool x3) {
+  TcState* s = static_cast<TcState*>(c->tc_state);
+  const int R = c->B * c->N;
+  launch_pdl(ln_img_kernel, (unsigned)((R * 32 + 255) / 256), 256, 0, st, in, out, out2, img, gamma, beta, R, c->d.c_s, s->Rp, normalize,
+             bb ? (const float*)bb->Wbb : (const float*)nullptr, bb ? (const float*)bb->bbb : (const float*)nullptr,
+             bb ? c->rots_w : (float*)nullptr, bb ? c->trans_w : (float*)nullptr, s->img_lo, x3 ? 2 : 1);
+}
+
+// StructureNet.forward (structure_net.py:189-243) on c->s / c->p / c->rots_w / c->trans_w, tensor-core modes.
 int tc_structure_net(gb_ctx* c, float* states_out, cudaStream_t st) {
   TcState* s = static_cast<TcState*>(c->tc_state);
   const gb_dims& d = c->d;
   const int B = c->B, N = c->N, R = B * N, cs = d.c_s, Np = s->Np, Rp = s->Rp;
+  const bool x3 = c->precision == GB_PREC_BF16X3;
   if (!Rp || (int)s->st.size() < d.n_structure_layer || !s->Wb_img) return gb_fail(c, GB_ERR_INVALID, "tc_structure_net: not bound");
   const size_t Rcs = (size_t)R * cs;
   int rc;
   // row-sharded (B == 1): pair bias, z images, attention and the output projection for this rank's query rows only;
   // the [N, c_s] result of every layer is all-gathered and the O(N) rest runs replicated
   const int W = c->shard_world, rows = N / W, row0 = c->shard_rank * rows;
+  if (x3 && W > 1) return gb_fail(c, GB_ERR_UNSUPPORTED, "row sharding is built for the bf16 mode only");
+  if (x3 && Np > 512) return gb_fail(c, GB_ERR_UNSUPPORTED, "bf16x3 structure net: N = %d > 512 (the hi | lo probability images do not fit in shared memory); use bf16 or fp32", N);
   TileRange tr = full_tile_range(N, Np);
   if (W > 1) { tr.nt2 = (uint32_t)rows >> 1; tr.t2_0 = (uint32_t)row0 >> 1; }
   const unsigned ptiles = (unsigned)B * tr.nt2 * tr.njb;
-  launch_pdl_cls(5, ipa_prep_tc_kernel, ptiles, 256, PREP_SMEM, st, c->p, B, N, Np, c->mask, s->Wb_img, s->bias96, s->pbias, s->z_img,
-                                                     d.n_structure_layer * IPA_H, tr);
+  if (x3) launch_pdl_cls(5, ipa_prep_tc_kernel<2>, ptiles, 256, PrepSmem<2>::TOTAL, st, (const float*)c->p, B, N, Np, (const bf16*)s->Wb_img,
+                         (const float*)s->bias96, s->pbias, s->z_img, d.n_structure_layer * IPA_H, tr, s->img_lo);
+  else launch_pdl_cls(5, ipa_prep_tc_kernel<1>, ptiles, 256, PrepSmem<1>::TOTAL, st, (const float*)c->p, B, N, Np, (const bf16*)s->Wb_img,
+                      (const float*)s->bias96, s->pbias, s->z_img, d.n_structure_layer * IPA_H, tr, (size_t)0);
   GB_LAUNCH_CHECK(c, "ipa_prep_tc");
-  const unsigned lnb = (unsigned)((R * 32 + 255) / 256);
-  if (!s->s_img_valid) {      // already made by tc_pair_pipj of this eval
-    launch_pdl(ln_img_kernel, lnb, 256, 0, st, c->s, nullptr, nullptr, s->s_img, nullptr, nullptr, R, cs, Rp, 0, nullptr, nullptr, nullptr, nullptr);
+  if (!s->s_img_valid) {      // already made by tc_pair_pipj of this eval (bf16 mode)
+    launch_ln(c, st, c->s, nullptr, nullptr, s->s_img, nullptr, nullptr, 0, nullptr, x3);
     GB_LAUNCH_CHECK(c, "s_to_img");
   }
   s->s_img_valid = false;
@@ -1009,39 +1038,43 @@ int tc_structure_net(gb_ctx* c, float* states_out, cudaStream_t st) {
     for (int l = 0; l < d.n_structure_layer; ++l) {
       const StructLayerW& w = c->st[l];
       const TcStructW& t = s->st[l];
-      if ((rc = gemm_img(c, st, s->s_img, cs, t.Wqkv, IPA_QKV, t.bqkv, nullptr, 0, c->qkv, IPA_QKV, nullptr, false, N))) return rc;
+      if ((rc = gemm_img(c, st, s->s_img, cs, t.Wqkv, IPA_QKV, t.bqkv, nullptr, 0, c->qkv, IPA_QKV, nullptr, false, N, 0, 0, x3))) return rc;
       launch_pdl(ipa_points_planes_kernel, (R * IPA_H + 255) / 256, 256, 0, st, c->qkv, c->rots_w, c->trans_w, R, N);
       GB_LAUNCH_CHECK(c, "ipa_points_planes");
       {
-        const int nq = W > 1 ? rows : N, G = ia_queries_per_cta(Np, B, nq, s->num_sms);
+        const int nq = W > 1 ? rows : N, G = ia_queries_per_cta(Np, B, nq, s->num_sms, x3 ? 2 : 1);
         const dim3 grid((nq + G - 1) / G, B);
         const float* pb = s->pbias + (size_t)l * B * N * IPA_H * Np;
-        const size_t smem = ia_smem(G, Np).total;
-        if (G == 8) launch_pdl(ipa_attention_tc_kernel<8>, grid, IA_THREADS, smem, st, c->qkv, pb, s->z_img, c->rots_w, c->trans_w, w.hw, s->cat_img, N, Np, Rp, row0);
-        else if (G == 4) launch_pdl(ipa_attention_tc_kernel<4>, grid, IA_THREADS, smem, st, c->qkv, pb, s->z_img, c->rots_w, c->trans_w, w.hw, s->cat_img, N, Np, Rp, row0);
-        else launch_pdl(ipa_attention_tc_kernel<2>, grid, IA_THREADS, smem, st, c->qkv, pb, s->z_img, c->rots_w, c->trans_w, w.hw, s->cat_img, N, Np, Rp, row0);
+        const size_t smem = ia_smem(G, Np, x3 ? 2 : 1).total, zl = x3 ? s->img_lo : 0;
+#define IA_LAUNCH(GG, SP) launch_pdl(ipa_attention_tc_kernel<GG, SP>, grid, IA_THREADS, smem, st, (const float*)c->qkv, pb, (const bf16*)s->z_img, \
+                                     (const float*)c->rots_w, (const float*)c->trans_w, (const float*)w.hw, s->cat_img, N, Np, Rp, row0, (const int*)c->mask, zl, zl)
+        if (x3) { if (G == 4) IA_LAUNCH(4, 2); else IA_LAUNCH(2, 2); }
+        else if (G == 8) IA_LAUNCH(8, 1);
+        else if (G == 4) IA_LAUNCH(4, 1);
+        else IA_LAUNCH(2, 1);
+#undef IA_LAUNCH
       }
       GB_LAUNCH_CHECK(c, "ipa_attention_tc");
       if (W > 1) {
         if ((rc = gemm_img(c, st, s->cat_img, IPA_CAT, t.Wout, cs, w.bout, c->s, cs, c->sA, cs, nullptr, false, 0, row0 / 128, rows / 128))) return rc;
         if ((rc = shard_all_gather(c, c->sA, (size_t)rows * cs * sizeof(float), st))) return rc;
-      } else if ((rc = gemm_img(c, st, s->cat_img, IPA_CAT, t.Wout, cs, w.bout, c->s, cs, c->sA, cs, nullptr, false))) return rc;
-      launch_pdl(ln_img_kernel, lnb, 256, 0, st, c->sA, c->sB, nullptr, s->ln1_img, w.ln1_g, w.ln1_b, R, cs, Rp, 1, nullptr, nullptr, nullptr, nullptr);
+      } else if ((rc = gemm_img(c, st, s->cat_img, IPA_CAT, t.Wout, cs, w.bout, c->s, cs, c->sA, cs, nullptr, false, 0, 0, 0, x3))) return rc;
+      launch_ln(c, st, c->sA, c->sB, nullptr, s->ln1_img, w.ln1_g, w.ln1_b, 1, nullptr, x3);
       GB_LAUNCH_CHECK(c, "ipa_layer_norm");
       float* cur = c->sB;
       float* other = c->sA;
       for (int tl = 0; tl < d.n_structure_transition_layer; ++tl) {
         if (tl > 0) {
-          launch_pdl(ln_img_kernel, lnb, 256, 0, st, cur, nullptr, nullptr, s->ln1_img, nullptr, nullptr, R, cs, Rp, 0, nullptr, nullptr, nullptr, nullptr);
+          launch_ln(c, st, cur, nullptr, nullptr, s->ln1_img, nullptr, nullptr, 0, nullptr, x3);
           GB_LAUNCH_CHECK(c, "to_img");
         }
-        if ((rc = gemm_img(c, st, s->ln1_img, cs, t.W1[tl], cs, w.b1[tl], nullptr, 0, nullptr, 0, s->h1_img, true))) return rc;
-        if ((rc = gemm_img(c, st, s->h1_img, cs, t.W2[tl], cs, w.b2[tl], nullptr, 0, nullptr, 0, s->h2_img, true))) return rc;
-        if ((rc = gemm_img(c, st, s->h2_img, cs, t.W3[tl], cs, w.b3[tl], cur, cs, other, cs, nullptr, false))) return rc;
+        if ((rc = gemm_img(c, st, s->ln1_img, cs, t.W1[tl], cs, w.b1[tl], nullptr, 0, nullptr, 0, s->h1_img, true, 0, 0, 0, x3))) return rc;
+        if ((rc = gemm_img(c, st, s->h1_img, cs, t.W2[tl], cs, w.b2[tl], nullptr, 0, nullptr, 0, s->h2_img, true, 0, 0, 0, x3))) return rc;
+        if ((rc = gemm_img(c, st, s->h2_img, cs, t.W3[tl], cs, w.b3[tl], cur, cs, other, cs, nullptr, false, 0, 0, 0, x3))) return rc;
         float* tmp = cur; cur = other; other = tmp;
       }
       float* st_out = states_out ? states_out + (size_t)state_idx * Rcs : nullptr;
-      launch_pdl(ln_img_kernel, lnb, 256, 0, st, cur, c->s, st_out, s->s_img, w.ln2_g, w.ln2_b, R, cs, Rp, 1, w.Wbb, w.bbb, c->rots_w, c->trans_w);
+      launch_ln(c, st, cur, c->s, st_out, s->s_img, w.ln2_g, w.ln2_b, 1, &w, x3);
       GB_LAUNCH_CHECK(c, "transition_layer_norm_backbone_update");
       ++state_idx;
     }

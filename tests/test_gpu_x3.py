@@ -103,3 +103,89 @@ def test_trimul_x3_every_stage(B, N, outgoing):
     print('x3 trimul stages', B, N, outgoing, {k: '%.1e' % v for k, v in errs.items()})
     for k, v in errs.items():
         assert v < TOL_STAGE, (k, v)
+
+
+def _valid(t, mask, lead=0):
+    """rows of valid residues only ([.., B, N, C] -> [.., n_valid, C]).  On padded QUERY rows every IPA logit sits at -1e5,
+    where fp32 has 7 fractional bits (invariant_point_attention.py:206-212): their softmax is rounding noise in the reference
+    too, nothing reads them (padded keys are masked out of every valid row; the sampler multiplies by the mask), and they
+    are reproduced only as far as the summation order is (1e-3 .. 1e-2)."""
+    m = mask.bool()
+    return t[:, m] if lead else t[m]
+
+
+def test_forward_x3_vs_oracle_L64():
+    """Whole denoiser in bf16x3 mode (base config, activated weights, L=64 B=2 ragged) against the fp32 oracle, held to
+    the same gates as the fp32 CUDA-core path on the valid residues; padded rows at 1e-2."""
+    cfg = O.OracleConfig()
+    sd = W.make_state_dict(cfg, 5, 'activated')
+    g = torch.Generator().manual_seed(9)
+    feats = O.make_features([[64], [50]])
+    B, N = feats['residue_mask'].shape
+    trans = torch.randn(B, N, 3, generator=g) * 6
+    rots = O.compute_frenet_frames(trans, feats['chain_index'], feats['residue_mask'])
+    ts = torch.tensor([321, 7], dtype=torch.int32)
+    with torch.no_grad():
+        ref = O.denoiser_forward(sd, cfg, rots, trans, ts, feats, 'canonical')
+    model = make_denoiser(cfg, sd, precision='bf16x3')
+    o, _ = run_cuda_forward(model, rots, trans, ts, feats, None)
+    m = feats['residue_mask']
+    errs = {k: rel(o[k], ref[k]) for k in ('s', 'p', 'states', 'z')}
+    errs_v = {'states': rel(_valid(o['states'], m, 1), _valid(ref['states'], m, 1)), 'z': rel(_valid(o['z'], m), _valid(ref['z'], m))}
+    print('bf16x3 forward errors', errs, 'valid residues', errs_v)
+    assert errs['s'] < 1e-4
+    assert errs['p'] < 2e-4
+    assert errs_v['states'] < TOL_Z and errs_v['z'] < TOL_Z
+    assert errs['states'] < 1e-2 and errs['z'] < 1e-2
+
+
+@pytest.mark.parametrize('name', ['uncond_base_ragged', 'motif_base', 'multichain'])
+def test_forward_x3_matches_reference_fixture(name):
+    """bf16x3 forward vs the unmodified reference's recorded outputs (quaternion sign replayed), north-star gate."""
+    cfg, sd, feats, t = load_forward_case(name)
+    model = make_denoiser(cfg, sd, precision='bf16x3')
+    o, _ = run_cuda_forward(model, t['rots'], t['trans'], t['timesteps'], feats, t['quat'])
+    m = feats['residue_mask']
+    errs = {'s': rel(o['s'], t['s']), 'p': rel(o['p'], t['p']),
+            'states': rel(_valid(o['states'], m, 1), _valid(t['states'], m, 1)), 'z': rel(_valid(o['z'], m), _valid(t['z'], m))}
+    print('bf16x3 fixture', name, errs)
+    assert errs['s'] < 1e-4
+    assert errs['p'] < 2e-4
+    # motif_base is ill-conditioned in the structure net (the reference's own fp32 result is 3.6e-3 from an fp64 evaluation
+    # of the same graph, tests/test_gpu_parity.py): held to 3e-3 there
+    tol = 3e-3 if name == 'motif_base' else TOL_Z
+    assert errs['states'] < tol and errs['z'] < tol
+
+
+def test_c1_trajectory_x3():
+    """BASELINE configs[0] (L = 64, batch 1, 50 steps, full base config) in bf16x3 mode against the trajectory recorded
+    from the unmodified reference sampler: centred C-alpha RMSD within the north star's 0.1 A."""
+    import genie2_b200
+    from genie2_b200.sampler import _posterior, compute_frenet_frames
+    d = np.load(os.path.join(GOLDEN, 'traj_c1.npz'))
+    T_, L, B = int(d['T']), int(d['L']), int(d['B'])
+    sd = W.make_state_dict(O.OracleConfig(n_timestep=T_), int(d['seed']), 'activated')
+    gcfg = genie2_b200.Config()
+    gcfg.diffusion['n_timestep'] = T_
+    genie = genie2_b200.Genie(gcfg)
+    genie.model.load_state_dict(sd)
+    genie = genie.to(DEV)
+    genie.model.set_precision('bf16x3')
+    genie.setup_schedule()
+    feats = feats_to(O.make_features([[L]] * B), DEV)
+    tape = torch.from_numpy(d['tape']).to(DEV)
+    quats = torch.from_numpy(d['quats'].astype(np.float32)).to(DEV)
+    trans = tape[T_].clone()
+    ts = genie2_b200.T(compute_frenet_frames(genie.model, feats, trans), trans)
+    for step in range(T_, 0, -1):
+        tt = torch.full((B,), step, dtype=torch.int32, device=DEV)
+        z = genie.model(ts, tt, feats, quat_follow=quats[T_ - step])['z']
+        ts = _posterior(genie, ts, z, step, feats, float(d['scale']), tape[step])
+    torch.cuda.synchronize()
+    got, ref = ts.trans.cpu(), torch.from_numpy(d['final'])
+    assert torch.isfinite(got).all()
+    a = got[0] - got[0].mean(0, keepdim=True)
+    b = ref[0] - ref[0].mean(0, keepdim=True)
+    rmsd = float(((a - b) ** 2).sum(-1).mean().sqrt())
+    print('C1 bf16x3: centred C-alpha RMSD %.4f A' % rmsd)
+    assert rmsd < 0.1, rmsd
