@@ -70,6 +70,7 @@ SYMBOLS = {
     'gb_k_pair_transition': (C.c_int, [_P, C.c_int, _P, _P]),
     'gb_k_tri_attention': (C.c_int, [_P, C.c_int, C.c_int, _P, _P]),
     'gb_k_ipa': (C.c_int, [_P, C.c_int, _P, _P, _P, _P, _P, _P]),
+    'gb_k_ipa_static': (C.c_int, [_P, C.c_int, _P, _P, _P, _P, _P, _P]),
     'gb_dbg_tc_copy': (C.c_int, [_P, C.c_int, _P, C.c_int64]),
     'gb_shard_unique_id': (C.c_int, [_P]),
     'gb_shard_init': (C.c_int, [_P, C.c_int, C.c_int, _P]),

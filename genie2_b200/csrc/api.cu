@@ -46,6 +46,13 @@ extern "C" int64_t gb_launch_count(const gb_ctx* ctx) { return ctx ? ctx->launch
 extern "C" int64_t gb_workspace_bytes(const gb_ctx* ctx) { return ctx ? (int64_t)ctx->ws_bytes : 0; }
 extern "C" int64_t gb_collective_count(const gb_ctx* ctx) { return ctx ? ctx->collectives : 0; }
 
+// Scratch of gb_k_ipa_static (the entry point that allocates nothing): the fused projection rows [rows][1152] followed by
+// the concat rows [rows][2112], rows <= GB_K_IPA_STATIC_MAX_ROWS: 13,369,344 bytes that every GPU which loads this library
+// holds until the process exits.  In HOST code this name is only a stand-in for the symbol, not a device address: the
+// address is taken once per context with cudaGetSymbolAddress in gb_create (the context's device current) and only that
+// pointer is ever passed to a kernel.
+static __device__ __align__(256) float g_ipa_static_scratch[(size_t)GB_K_IPA_STATIC_MAX_ROWS * (IPA_QKV + IPA_CAT)];
+
 static const int kSmemPair = (PS_A_FLOATS + PS_W_FLOATS) * 4;
 static const int kSmemTrans = (PS_A_FLOATS + PS_W_FLOATS + PS_A_FLOATS) * 4;
 
@@ -84,6 +91,12 @@ extern "C" int gb_create(gb_ctx** out, const gb_dims* d, int device) {
   cudaFuncSetAttribute(frenet_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
   cudaFuncSetAttribute(ddpm_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
   if (cudaGetLastError() != cudaSuccess) { delete c; return gb_fail(nullptr, GB_ERR_CUDA, "cudaFuncSetAttribute failed"); }
+  {
+    void* sp = nullptr;     // device `device` is current here (DeviceGuard above)
+    const cudaError_t se = cudaGetSymbolAddress(&sp, g_ipa_static_scratch);
+    if (se != cudaSuccess || !sp) { delete c; return gb_fail(nullptr, GB_ERR_CUDA, "gb_create: cudaGetSymbolAddress(static scratch) failed: %s", cudaGetErrorString(se)); }
+    c->static_scratch = static_cast<float*>(sp);
+  }
   int rc = tc_init(c);
   if (rc != GB_OK) { g_create_err = c->err; delete c; return rc; }
   *out = c;
@@ -961,4 +974,37 @@ extern "C" int gb_k_ipa(gb_ctx* c, int layer, const float* s, const float* p, co
   DeviceGuard dg(c->device);
   if (!s || !p || !rots || !trans || !out || layer < 0 || layer >= c->d.n_structure_layer) return gb_fail(c, GB_ERR_INVALID, "gb_k_ipa: bad arguments");
   return run_ipa(c, c->st[layer], s, p, rots, trans, out, nullptr, (cudaStream_t)stream);
+}
+
+// gb_k_ipa without any allocation and without the context's workspace as scratch: the same kernels as run_ipa (fp32 CUDA
+// cores, one GPU) on the library's static scratch array.  Nothing in the scratch has to start at zero: the projection GEMM
+// writes all 1152 columns of every row before they are read, the attention kernel all 2112 columns of the concat row.
+extern "C" int gb_k_ipa_static(gb_ctx* c, int layer, const float* s, const float* p, const float* rots, const float* trans,
+                               float* out, void* stream) {
+  int rc = check_ready(c, "gb_k_ipa_static");
+  if (rc) return rc;
+  if (!s || !p || !rots || !trans || !out || layer < 0 || layer >= c->d.n_structure_layer) return gb_fail(c, GB_ERR_INVALID, "gb_k_ipa_static: bad arguments");
+  const int B = c->B, N = c->N, R = B * N, cs = c->d.c_s;
+  if (R > GB_K_IPA_STATIC_MAX_ROWS)
+    return gb_fail(c, GB_ERR_UNSUPPORTED, "gb_k_ipa_static: B * N = %d rows exceed the static scratch (GB_K_IPA_STATIC_MAX_ROWS = %d); use gb_k_ipa",
+                   R, GB_K_IPA_STATIC_MAX_ROWS);
+  if (c->shard_world > 1) return gb_fail(c, GB_ERR_UNSUPPORTED, "gb_k_ipa_static: not available on a row-sharded context");
+  if (!c->static_scratch) return gb_fail(c, GB_ERR_INVALID, "gb_k_ipa_static: static scratch address not resolved");
+  const size_t smem = ((size_t)IPA_H * N + 192 + 144 + 288) * sizeof(float);
+  if (smem > 200 * 1024) return gb_fail(c, GB_ERR_UNSUPPORTED, "gb_k_ipa_static: N = %d too large for ipa_attention", N);
+  DeviceGuard dg(c->device);
+  cudaStream_t st = (cudaStream_t)stream;
+  const StructLayerW& w = c->st[layer];
+  float* qkv = c->static_scratch;                                   // [R][1152]
+  float* cat = c->static_scratch + (size_t)R * IPA_QKV;             // [R][2112]
+  sgemm_nt(st, s, cs, w.Wqkv, cs, w.bqkv, nullptr, 0, qkv, IPA_QKV, R, IPA_QKV, cs, false);
+  GB_LAUNCH_CHECK(c, "ipa_proj(static)");
+  const int NP = IPA_H * IPA_PQ + IPA_H * (IPA_PQ + IPA_PV);
+  ipa_points_to_global_kernel<<<(R * NP + 255) / 256, 256, 0, st>>>(qkv, rots, trans, R);
+  GB_LAUNCH_CHECK(c, "ipa_points_to_global(static)");
+  ipa_attention_kernel<<<dim3(N, B), 256, smem, st>>>(qkv, p, rots, trans, c->mask, w.Wb, w.bb, w.hw, cat, N, 0);
+  GB_LAUNCH_CHECK(c, "ipa_attention(static)");
+  sgemm_nt(st, cat, IPA_CAT, w.Wout, IPA_CAT, w.bout, nullptr, 0, out, cs, R, cs, IPA_CAT, false);
+  GB_LAUNCH_CHECK(c, "ipa_out(static)");
+  return GB_OK;
 }

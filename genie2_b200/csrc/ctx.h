@@ -110,6 +110,8 @@ struct gb_ctx {
   int64_t collectives = 0;      // all-gathers enqueued since creation
   // tensor-core scratch (bf16/tf32 operand copies), owned by the tc module
   void* tc_state = nullptr;
+  // device address of the file-scope static scratch of gb_k_ipa_static (api.cu), resolved once in gb_create
+  float* static_scratch = nullptr;
 };
 
 // set ctx->err (printf style) and return code

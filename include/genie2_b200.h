@@ -209,6 +209,20 @@ int gb_k_tri_attention(gb_ctx* ctx, int layer, int starting, float* p, void* str
 int gb_k_ipa(gb_ctx* ctx, int layer, const float* s, const float* p, const float* rots,
              const float* trans, float* out, void* stream);
 
+/* gb_k_ipa for callers that cannot allocate (CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).
+ * No counterpart in the reference.  Same arguments, same kernels and the
+ * same result as gb_k_ipa (fp32 CUDA cores), but its scratch (projection rows [B*N][1152] + concat rows [B*N][2112]) is a
+ * file-scope static __device__ array of the library instead of the context's workspace, and the call performs no
+ * cudaMalloc / cudaFree and calls no allocating routine.  Limit: B * N <= GB_K_IPA_STATIC_MAX_ROWS of the bound feature
+ * batch (larger batches return GB_ERR_UNSUPPORTED); the array is 13,369,344 bytes on every GPU that loads the library,
+ * held until the process exits.  ALL calls, from every context on a device, share that one array and it keeps the last
+ * call's contents (nothing in it needs to start at zero: every element read is written earlier in the same call): calls
+ * that can overlap on the GPU (different streams, different contexts on one device) RACE -- serialise them.  Not
+ * available on a row-sharded context. */
+#define GB_K_IPA_STATIC_MAX_ROWS 1024
+int gb_k_ipa_static(gb_ctx* ctx, int layer, const float* s, const float* p, const float* rots,
+                    const float* trans, float* out, void* stream);
+
 /* TEST ONLY: copy one bf16 intermediate of the last tensor-core triangle update into dst (device):
  * which = 0/1: a / b operand tile images [B][128][Np/64][Np][64]; 2: x tile images [B][Np/2][Np/64][2][128][64];
  * 3: g [B*N*N][128].  Returns the padded length Np (> 0) or a negative gb_status; dst may be NULL
