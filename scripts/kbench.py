@@ -1,5 +1,6 @@
 """Short driver for per-kernel timing under `ncu --metrics gpu__time_duration.sum`: the pair-stack
-modules and whole forwards at the C2 shape (B=4, L=256), bf16 mode.  Also prints CUDA-event times."""
+modules and whole forwards at the C2 shape (B=4, L=256); precision from GB_KBENCH_PREC (default bf16x3, the headline
+mode).  Also prints CUDA-event times."""
 import os
 import sys
 
@@ -19,7 +20,7 @@ def main():
     lib = L.load()
     cfg = O.OracleConfig()
     sd = W.make_state_dict(cfg, 0, 'activated')
-    model = make_denoiser(cfg, sd, precision='bf16')
+    model = make_denoiser(cfg, sd, precision=os.environ.get('GB_KBENCH_PREC', 'bf16x3'))
     model.return_intermediates = False
     feats = feats_to(O.make_features([[N]] * B), 'cuda:0')
     ctx = model.bind_features(feats, torch.device('cuda:0'))
