@@ -70,11 +70,7 @@ def oracle_stepper(n_threads=None):
     # all the host cores this process may use: torchrun exports OMP_NUM_THREADS=1 to its workers, which would time the
     # reference on a single core
     if not n_threads:
-        try:
-            n_threads = len(os.sched_getaffinity(0))
-        except AttributeError:
-            n_threads = os.cpu_count() or 1
-        n_threads = min(n_threads, 32)     # beyond 32 threads the [1, 256, 256, 128]-sized eager ops stop scaling
+        n_threads = host_threads(32)       # beyond 32 threads the [1, 256, 256, 128]-sized eager ops stop scaling
     torch.set_num_threads(n_threads)
     cfg = O.OracleConfig()
     sd = W.make_state_dict(cfg, 0, 'activated')
@@ -93,39 +89,88 @@ def oracle_stepper(n_threads=None):
     return step, x, torch.get_num_threads()
 
 
+def host_threads(limit=64):
+    """All the host cores this process may use (torchrun exports OMP_NUM_THREADS=1 to its workers, which would time the
+    reference on a single core)."""
+    try:
+        n = len(os.sched_getaffinity(0))
+    except AttributeError:
+        n = os.cpu_count() or 1
+    return min(n, limit)
+
+
+def reference_sample_seconds(n_steps, threads):
+    """The UNMODIFIED reference (baseline/_ref, installed by oracle/install_reference.py) through its own public sampler,
+    UnconditionalSampler._sample (sampler/base.py:216-289): the whole workload -- L=256, batch 4, base configuration,
+    scale 0.6 -- with the schedule shortened to `n_steps` reverse steps (the work of a step does not depend on the
+    schedule length).  Chunked pair transition and the eigh quaternions intact.  Returns the seconds _sample took."""
+    import torch
+    from oracle import reference_bridge as R, genie_oracle as O, weights as W
+    torch.set_num_threads(threads)
+    sd = W.make_state_dict(O.OracleConfig(), 0, 'activated')
+    genie, sampler = R.load_installed_sampler(n_steps, sd)
+    params = {'length': L, 'scale': SCALE, 'num_samples': B, 'outdir': tempfile.gettempdir(), 'prefix': 'ref', 'offset': 0}
+    torch.manual_seed(1)
+    t0 = time.perf_counter()
+    out = sampler._sample(params)
+    dt = time.perf_counter() - t0
+    if not all(np.isfinite(o['atom_positions']).all() for o in out):
+        raise RuntimeError('reference arm produced non-finite coordinates')
+    return dt
+
+
+def reference_available():
+    from oracle import reference_bridge as R
+    return R.installed_available()
+
+
 def run_reference(args):
-    """--impl reference: the reference's CPU algorithm (oracle port; the Python reference itself
-    cannot travel to the GPU box) on the host cores.  One step = one reverse step of ONE sample
-    (L=256, batch 1) -- a bounded quarter of the batch-4 workload; evals/s is quoted for batch 4."""
+    """--impl reference: the reference's own CPU implementation of the path on the host cores.  With baseline/_ref
+    present (kind "reference"): the unmodified reference's sampler on the full batch-4 workload, W warm-up steps in one
+    _sample call and K timed steps in a second one.  Without it (kind "port"): the oracle port on ONE of the four
+    samples per step, evals/s quoted for batch 4."""
     rank = int(os.environ.get('RANK', '0'))
     if rank != 0:
         return
     import torch
     K = args.steps if args.steps is not None else 3
     W_ = args.warmup if args.warmup is not None else 1
-    step, x, threads = oracle_stepper()
-    with torch.no_grad():
-        t = T_STEPS
-        for _ in range(W_):
-            x = step(x, t)
-            t -= 1
-        t0 = time.perf_counter()
-        for _ in range(K):
-            x = step(x, t)
-            t -= 1
-        dt = time.perf_counter() - t0
-    per_sample = dt / K
-    value = 1.0 / (B * per_sample)
+    threads = host_threads()
+    if reference_available():
+        if W_ > 0:
+            reference_sample_seconds(W_, threads)
+        dt = reference_sample_seconds(K, threads)
+        per_step = dt / K
+        kind = 'reference'
+        sample = ('%d reverse steps of the whole workload (L=256, batch 4) through the unmodified reference '
+                  'UnconditionalSampler._sample from baseline/_ref, torch CPU fp32, %d threads' % (K, threads))
+        cfg_sample = 'the whole batch-4 workload, schedule shortened to the timed step count'
+    else:
+        step, x, threads = oracle_stepper(threads)
+        with torch.no_grad():
+            t = T_STEPS
+            for _ in range(W_):
+                x = step(x, t)
+                t -= 1
+            t0 = time.perf_counter()
+            for _ in range(K):
+                x = step(x, t)
+                t -= 1
+            dt = time.perf_counter() - t0
+        per_step = dt / K * B
+        kind = 'port'
+        sample = '%d reverse steps at L=256 batch 1 (oracle/genie_oracle.py, torch CPU fp32); batch-4 rate = 1/(4 t)' % K
+        cfg_sample = 'one reverse step of 1 of the 4 samples per step; batch-4 rate = 1/(4 t)'
+    value = 1.0 / per_step
     line = {
         'impl': 'reference', 'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': args.gpus, 'steps': K, 'warmup': W_,
-        'ms_per_step': per_sample * B * 1e3, 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None,
+        'ms_per_step': per_step * 1e3, 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None,
         'dtype': 'f32', 'data': 'synthetic',
-        'config': {'workload': 'unconditional L=256 batch 4, base config, 1000-step schedule, scale 0.6',
-                   'sample': 'one reverse step of 1 of the 4 samples per step; batch-4 rate = 1/(4 t)'},
-        'cpu_baseline': {'value': value, 'unit': UNIT, 'cores': threads, 'kind': 'port',
-                         'sample': '%d reverse steps at L=256 batch 1 (oracle/genie_oracle.py, torch CPU fp32)' % K},
+        'config': {'workload': 'unconditional L=256 batch 4, base config, 1000-step schedule, scale 0.6 (BASELINE configs[1])',
+                   'per_gpu_batch': B, 'length': L, 'sample': cfg_sample},
+        'cpu_baseline': {'value': value, 'unit': UNIT, 'cores': threads, 'kind': kind, 'sample': sample},
         'e2e': {'value': value, 'unit': UNIT, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
-        'seconds_per_1000_step_sample': 1000.0 * per_sample * B,
+        'seconds_per_1000_step_sample': 1000.0 * per_step,
         'gpu_launches': 0,
     }
     print(json.dumps(line), flush=True)
@@ -429,16 +474,24 @@ def run_b200(args):
                                'finite': bool(all(np.isfinite(o['atom_positions']).all() for o in outs))}
         line['seconds_per_1000_step_sample'] = dt
     if not args.no_cpu_baseline and world == 1:
-        step, xc, threads = oracle_stepper()
-        with torch.no_grad():
-            xc = step(xc, T_STEPS)
-            t0 = time.perf_counter()
-            n = 2
-            for i in range(n):
-                xc = step(xc, T_STEPS - 1 - i)
-            dt = (time.perf_counter() - t0) / n
-        line['cpu_baseline'] = {'value': 1.0 / (B * dt), 'unit': UNIT, 'cores': threads, 'kind': 'port',
-                                'sample': '%d reverse steps of one L=256 sample (oracle port, torch CPU fp32); batch-4 rate = 1/(4 t)' % n}
+        if reference_available():
+            threads, n = host_threads(), 3
+            reference_sample_seconds(1, threads)
+            dt = reference_sample_seconds(n, threads) / n
+            line['cpu_baseline'] = {'value': 1.0 / dt, 'unit': UNIT, 'cores': threads, 'kind': 'reference',
+                                    'sample': '%d reverse steps of the whole workload (L=256, batch 4) through the unmodified reference sampler '
+                                              'in baseline/_ref (torch CPU fp32, chunked pair transition, eigh quaternions)' % n}
+        else:
+            step, xc, threads = oracle_stepper()
+            with torch.no_grad():
+                xc = step(xc, T_STEPS)
+                t0 = time.perf_counter()
+                n = 2
+                for i in range(n):
+                    xc = step(xc, T_STEPS - 1 - i)
+                dt = (time.perf_counter() - t0) / n
+            line['cpu_baseline'] = {'value': 1.0 / (B * dt), 'unit': UNIT, 'cores': threads, 'kind': 'port',
+                                    'sample': '%d reverse steps of one L=256 sample (oracle port, torch CPU fp32); batch-4 rate = 1/(4 t)' % n}
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()

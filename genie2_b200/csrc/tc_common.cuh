@@ -44,12 +44,27 @@ __device__ __forceinline__ uint32_t mbar_try_wait(uint64_t* bar, uint32_t parity
       : "memory");
   return ok;
 }
-// Bounded wait: a protocol bug traps (launch error reported to the caller) instead of hanging the GPU.
+// try_wait with a suspend-time hint: the thread sleeps in hardware until the phase completes or `ns` nanoseconds pass (it
+// wakes at once on completion), so a waiting warp issues one instruction per wake-up instead of spinning.
+__device__ __forceinline__ uint32_t mbar_try_wait_hint(uint64_t* bar, uint32_t parity, uint32_t ns) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity), "r"(ns)
+      : "memory");
+  return ok;
+}
+// Bounded wait: a protocol bug traps (launch error reported to the caller) instead of hanging the GPU.  The bound is a count
+// of suspended waits (2^24 of them: a fraction of a second if the hardware ignores the hint, seconds if it honours it), not a clock64() poll: in round 1 the CS2R / ISETP / BRA of the polling
+// loop were a quarter of all instructions the persistent kernels issued, taken from the warps that had work.
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   if (mbar_try_wait(bar, parity)) return;
-  const long long t0 = clock64();
-  while (!mbar_try_wait(bar, parity)) {
-    if (clock64() - t0 > 4000000000LL) __trap();
+  uint32_t tries = 0;
+  while (!mbar_try_wait_hint(bar, parity, 1000000u)) {
+    if (++tries > (1u << 24)) __trap();
   }
 }
 

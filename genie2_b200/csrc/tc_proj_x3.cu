@@ -10,7 +10,8 @@
 // Tensor memory: [0,64) W_p hi | [64,128) W_g hi | [128,192) W_p lo | [192,256) W_g lo | two 128-column accumulator slots.
 // Shared memory: W_g hi 32K | W_g lo 32K | two X buffers of (hi 32K | lo 32K).
 // Outputs: a / b as hi | lo tile-image pairs (the lo plane `lo_ab` elements behind the hi plane, same ImgLayout), g fp32
-// [B*N*N][128].  The gate uses ex2 / rcp (1e-6) instead of the 2^-11 tanh.approx of the bf16 kernel.
+// [B*N*N][128].  The gate uses ex2 / rcp (1e-6) instead of the 2^-11 tanh.approx of the bf16 kernel; -log2(e) is folded into
+// the gate weights and biases when they are packed, so sigmoid(y) = rcp(1 + ex2(y')) is two MUFUs and one add.
 #include <vector>
 
 #include "common.cuh"
@@ -20,6 +21,14 @@
 #include "tc_state.h"
 
 using namespace tc;
+
+// 1 / (1 + 2^y): the logistic function of a pre-activation that was scaled by -log2(e) at pack time
+__device__ __forceinline__ float sigmoid_ex2(float y) {
+  float e, r;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(y));
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(1.f + e));
+  return r;
+}
 
 #define K4S_THREADS 544
 #define K4S_OFF_X 65536u
@@ -240,7 +249,7 @@ __global__ void __launch_bounds__(K4S_THREADS, 1) trimul_proj_x3_kernel(
             for (int e = 0; e < 8; ++e) {
               float u0 = __uint_as_float(vp[2 * e]) + b_p, u1 = __uint_as_float(vp[2 * e + 1]) + b_p;
               if (!cols_on) { u0 *= cm[hf * 16 + 2 * e]; u1 *= cm[hf * 16 + 2 * e + 1]; }
-              const float o0 = u0 * sigmoid_acc(__uint_as_float(vg[2 * e]) + b_g), o1 = u1 * sigmoid_acc(__uint_as_float(vg[2 * e + 1]) + b_g);
+              const float o0 = u0 * sigmoid_ex2(__uint_as_float(vg[2 * e]) + b_g), o1 = u1 * sigmoid_ex2(__uint_as_float(vg[2 * e + 1]) + b_g);
               split_bf16x2(o0, o1, w[e], wl[e]);
             }
           }
@@ -278,7 +287,7 @@ __global__ void __launch_bounds__(K4S_THREADS, 1) trimul_proj_x3_kernel(
           for (int k8 = 0; k8 < 4; ++k8) {
             uint32_t o[8];
 #pragma unroll
-            for (int e = 0; e < 8; ++e) o[e] = __float_as_uint(sigmoid_acc(__uint_as_float(v[8 * k8 + e]) + bg[8 * k8 + e]));
+            for (int e = 0; e < 8; ++e) o[e] = __float_as_uint(sigmoid_ex2(__uint_as_float(v[8 * k8 + e]) + bg[8 * k8 + e]));
             st_global_32B(dst + hf * 32 + k8 * 8, make_uint4(o[0], o[1], o[2], o[3]), make_uint4(o[4], o[5], o[6], o[7]));
           }
         }
@@ -303,12 +312,15 @@ int tc_proj_x3_init(gb_ctx* c) {
   return GB_OK;
 }
 
-// hi and lo weight images with LayerNorm_in's gamma folded in (no 1/2 scaling: the gate is a true sigmoid here):
-//   W' = W * gamma = W'_hi + W'_lo ;  bias' = b + W beta         order: a_p | a_g | b_p | b_g | g
+// hi and lo weight images with LayerNorm_in's gamma folded in; the three gates (a_g, b_g, g) also carry -log2(e), so that the
+// kernel's sigmoid is rcp(1 + ex2(.)):
+//   W' = sc * W * gamma = W'_hi + W'_lo ;  bias' = sc * (b + W beta)         order: a_p | a_g | b_p | b_g | g
 int tc_pack_trimul_proj_x3(gb_ctx* c, TriMulW& w, const std::vector<float>* Wm[5], const std::vector<float>* bm[5],
                            const std::vector<float>& ln_g, const std::vector<float>& ln_b) {
   std::vector<uint16_t> hi(5 * 128 * 128), lo(5 * 128 * 128);
-  auto wv = [&](int t, int r, int k) { return (*Wm[t])[(size_t)r * 128 + k] * ln_g[k]; };
+  const float NLOG2E = -1.4426950408889634f;
+  auto gate = [](int t) { return t == 1 || t == 3 || t == 4; };
+  auto wv = [&](int t, int r, int k) { return (gate(t) ? NLOG2E : 1.f) * ((*Wm[t])[(size_t)r * 128 + k] * ln_g[k]); };
   pack_image(hi.data(), 128, 128, [&](int r, int k) { return wv(4, r, k); });
   pack_image(lo.data(), 128, 128, [&](int r, int k) { return bf_lo(wv(4, r, k)); });
   for (int t = 0; t < 4; ++t)
@@ -324,7 +336,7 @@ int tc_pack_trimul_proj_x3(gb_ctx* c, TriMulW& w, const std::vector<float>* Wm[5
     for (int r = 0; r < 128; ++r) {
       double acc = (*bm[t])[r];
       for (int k = 0; k < 128; ++k) acc += (double)(*Wm[t])[(size_t)r * 128 + k] * ln_b[k];
-      bias[t * 128 + r] = (float)acc;
+      bias[t * 128 + r] = (float)(gate(t) ? (double)NLOG2E * acc : acc);
     }
   w.x3_bproj = (float*)upload_bytes(c, bias.data(), bias.size() * 4);
   if (!w.x3_Wproj_hi || !w.x3_Wproj_lo || !w.x3_bproj) return gb_fail(c, GB_ERR_CUDA, "tc_pack_trimul_proj_x3: device allocation failed");

@@ -94,6 +94,10 @@ class BaseSampler(ABC):
     def on_sample_end(self, params, list_np_features):
         raise NotImplementedError
 
+    def create_np_feature_list(self, params):
+        """The batch of base.py:218-222: ``create_np_features(params)`` once per sample."""
+        return [self.create_np_features(params) for _ in range(params['num_samples'])]
+
     def add_required_parameter(self, name):
         self.required.append(name)
 
@@ -111,9 +115,7 @@ class BaseSampler(ABC):
         ``randn_like`` per step as the reference), 'philox' (drawn in-kernel, whole loop in one
         library call)}, ``noise_tape`` [T+1,B,N,3] (tape[t] used at step t, tape[T] = x_T),
         ``seed``."""
-        features = convert_np_features_to_tensor(
-            batchify_np_features([self.create_np_features(params) for _ in range(params['num_samples'])]),
-            self.device)
+        features = convert_np_features_to_tensor(batchify_np_features(self.create_np_feature_list(params)), self.device)
         denoiser = self.model.model
         n_t = self.model.config.diffusion['n_timestep']
         tape = params.get('noise_tape', None)
@@ -154,9 +156,21 @@ class UnconditionalSampler(BaseSampler):
     def create_np_features(self, params):
         return create_empty_np_features([params['length']])
 
+    def create_np_feature_list(self, params):
+        """Extension: ``params['lengths']`` (with ``params['offsets']``) makes a ragged batch, sample i of length
+        lengths[i] written as ``{lengths[i]}_{offsets[i]}.pdb`` (genie2_b200.sample_unconditional.plan_batches)."""
+        if 'lengths' not in params:
+            return super().create_np_feature_list(params)
+        if len(params['lengths']) != params['num_samples'] or len(params.get('offsets', ())) != params['num_samples']:
+            raise ValueError("'lengths' and 'offsets' need one entry per sample")
+        return [create_empty_np_features([int(n)]) for n in params['lengths']]
+
     def on_sample_end(self, params, list_np_features):
         for i, f in enumerate(list_np_features):
-            name = '{}_{}'.format(params['prefix'], params['offset'] + i)
+            if 'lengths' in params:
+                name = '{}_{}'.format(params['lengths'][i], params['offsets'][i])
+            else:
+                name = '{}_{}'.format(params['prefix'], params['offset'] + i)
             save_np_features_to_pdb(f, os.path.join(params['outdir'], 'pdbs', '{}.pdb'.format(name)))
 
 

@@ -13,6 +13,35 @@ import types
 import torch
 
 REFERENCE_ROOT = os.environ.get('GENIE2_REFERENCE_ROOT', '/root/reference')
+INSTALLED_ROOT = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), 'baseline', '_ref')
+
+
+def installed_available():
+    """The unmodified reference as installed by oracle/install_reference.py (travels to the GPU box)."""
+    return os.path.isfile(os.path.join(INSTALLED_ROOT, 'genie', 'model', 'model.py'))
+
+
+def load_installed_sampler(n_timestep, state_dict=None, device='cpu'):
+    """Reference ``Genie`` + ``UnconditionalSampler`` (diffusion/genie.py, sampler/unconditional.py) built from the
+    base configuration shipped with the install, on ``device``; only the schedule length is overridden.  Used by the
+    baseline legs of bench.py and scripts/eager_gpu_baseline.py -- never by the product."""
+    if not installed_available():
+        raise RuntimeError('baseline/_ref is not installed (python oracle/install_reference.py)')
+    if INSTALLED_ROOT not in sys.path:
+        sys.path.insert(0, INSTALLED_ROOT)
+    _install_lightning_stub()
+    from genie.config import Config
+    from genie.diffusion.genie import Genie
+    from genie.sampler.unconditional import UnconditionalSampler
+    import genie.model.model as mm
+    assert os.path.abspath(mm.__file__).startswith(INSTALLED_ROOT), 'a different genie package is shadowing baseline/_ref'
+    config = Config(os.path.join(INSTALLED_ROOT, 'results', 'base', 'configuration'))
+    config.diffusion['n_timestep'] = int(n_timestep)
+    genie = Genie(config).eval()
+    if state_dict is not None:
+        genie.model.load_state_dict(state_dict)
+    genie = genie.to(device)
+    return genie, UnconditionalSampler(genie)
 
 
 def available():

@@ -20,7 +20,10 @@ SCALE = {'ns': 1e-3, 'us': 1.0, 'ms': 1e3, 'byte': 1e-6, 'Kbyte': 1e-3, 'Mbyte':
 S = 4 * 256 * 256 * 128      # C2: elements of the pair tensor
 ALG = {'trimul_proj_tc_kernel': 10 * S, 'trimul_contract_pers_tc_kernel': 6 * S, 'trimul_contract_tc_kernel': 6 * S,
        'trimul_out_tc_kernel': 12 * S, 'pair_transition_tc_kernel': 8 * S, 'ipa_attention_tc_kernel': 2 * S,
-       'pair_embed_tc_kernel': 4 * S, 'ipa_prep_tc_kernel': 4 * S + 2 * S + 8 * 4 * 256 * 12 * 256 * 4}
+       'pair_embed_tc_kernel': 4 * S, 'pair_embed_kernel': 4 * S, 'ipa_prep_tc_kernel': 4 * S + 2 * S + 8 * 4 * 256 * 12 * 256 * 4,
+       # GB_PREC_BF16X3: hi | lo operand images, fp32 g
+       'trimul_proj_x3_kernel': 10 * S, 'trimul_contract_pers_tc_kernel<1>': 12 * S, 'trimul_out_x3_kernel': 16 * S,
+       'pair_transition_x3_kernel': 8 * S}
 
 
 def val(r, m):
@@ -43,7 +46,7 @@ for name, rs in agg.items():
     d['dram_bytes_per_launch'] = round((d['dram_read_mb'] + d['dram_write_mb']) * 1e6)
     d['dram_gbs'] = round(d['dram_bytes_per_launch'] / d['gpu_time_us'] / 1e3, 1)
     for a, v in ALG.items():
-        if name.split('<')[0] == a:
+        if name.split('<')[0] == a or name.replace('(bool)', '') == a:
             d['algorithmic_bytes_per_launch'] = v
     out[name] = d
 json.dump(out, open(sys.argv[2], 'w'), indent=1)
