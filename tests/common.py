@@ -66,3 +66,19 @@ def run_cuda_forward(model, rots, trans, timesteps, feats, quat_follow=None, dev
     torch.cuda.synchronize()
     return {'z': out['z'].cpu(), 's': out['s'].cpu(), 'p': out['p'].cpu(), 'states': out['states'].cpu(),
             'trans': out['ts'].trans.cpu(), 'rots': out['ts'].rots.cpu()}, f
+
+
+# ------------------------------------------------------------------ 1000-step reference trajectory (tests/golden/traj_c1k.npz)
+def unpack_quat_signs(packed):
+    """uint8 [..] -> float [.., 4]: +-1 at the index of the reference quaternion's largest |component| (make_golden.py
+    pack_quat_signs).  Used as the 'follow' field: only the sign of its dot product with our quaternion is consumed."""
+    packed = torch.as_tensor(packed).long()
+    q = torch.zeros(*packed.shape, 4)
+    q.scatter_(-1, (packed & 3).unsqueeze(-1), 1.0)
+    return q * torch.where((packed & 4) != 0, -1.0, 1.0).unsqueeze(-1)
+
+
+def centred_rmsd(a, b):
+    a = a - a.mean(0, keepdim=True)
+    b = b - b.mean(0, keepdim=True)
+    return float(((a - b) ** 2).sum(-1).mean().sqrt())
