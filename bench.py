@@ -42,6 +42,8 @@ def parse():
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--single-mode', action='store_true', help='skip the block of the other tensor-core mode')
     ap.add_argument('--no-sample-1000', action='store_true', help='skip the measured whole 1000-step sample (about 4 s)')
+    ap.add_argument('--no-extra-blocks', action='store_true', help='skip the length_sweep (configs[2]) and c5 (configs[4]) blocks')
+    ap.add_argument('--sweep-steps', type=int, default=10, help='reverse steps per batch in the length_sweep block')
     ap.add_argument('--workload', default='c2', choices=['c2', 'c5'],
                     help="c2 (default, the contract's line): L=256 batch 4; c5: ONE L=1024 sample, row-sharded over the ranks")
     return ap.parse_args()
@@ -99,7 +101,7 @@ def host_threads(limit=64):
     return min(n, limit)
 
 
-def reference_sample_seconds(n_steps, threads):
+def reference_sample_seconds(n_steps, threads, batch=None):
     """The UNMODIFIED reference (baseline/_ref, installed by oracle/install_reference.py) through its own public sampler,
     UnconditionalSampler._sample (sampler/base.py:216-289): the whole workload -- L=256, batch 4, base configuration,
     scale 0.6 -- with the schedule shortened to `n_steps` reverse steps (the work of a step does not depend on the
@@ -109,7 +111,7 @@ def reference_sample_seconds(n_steps, threads):
     torch.set_num_threads(threads)
     sd = W.make_state_dict(O.OracleConfig(), 0, 'activated')
     genie, sampler = R.load_installed_sampler(n_steps, sd)
-    params = {'length': L, 'scale': SCALE, 'num_samples': B, 'outdir': tempfile.gettempdir(), 'prefix': 'ref', 'offset': 0}
+    params = {'length': L, 'scale': SCALE, 'num_samples': batch or B, 'outdir': tempfile.gettempdir(), 'prefix': 'ref', 'offset': 0}
     torch.manual_seed(1)
     t0 = time.perf_counter()
     out = sampler._sample(params)
@@ -137,14 +139,16 @@ def run_reference(args):
     W_ = args.warmup if args.warmup is not None else 1
     threads = host_threads()
     if reference_available():
-        if W_ > 0:
-            reference_sample_seconds(W_, threads)
-        dt = reference_sample_seconds(K, threads)
-        per_step = dt / K
+        # the warm-up call also sizes the timed one: the whole batch if K steps of it fit in ~4 minutes on this box's cores,
+        # otherwise one of the four samples per step (rate quoted for batch 4 = 1 / (4 t))
+        t_w = reference_sample_seconds(max(W_, 1), threads) / max(W_, 1)
+        nb = B if t_w * K <= 240.0 else 1
+        dt = reference_sample_seconds(K, threads, nb)
+        per_step = dt / K * (B / nb)
         kind = 'reference'
-        sample = ('%d reverse steps of the whole workload (L=256, batch 4) through the unmodified reference '
-                  'UnconditionalSampler._sample from baseline/_ref, torch CPU fp32, %d threads' % (K, threads))
-        cfg_sample = 'the whole batch-4 workload, schedule shortened to the timed step count'
+        sample = ('%d reverse steps of %s (L=256, batch %d) through the unmodified reference UnconditionalSampler._sample '
+                  'from baseline/_ref, torch CPU fp32, %d threads' % (K, 'the whole workload' if nb == B else 'one sample of four per step; batch-4 rate = 1/(4 t)', nb, threads))
+        cfg_sample = ('the whole batch-4 workload' if nb == B else 'one of the 4 samples per step') + ', schedule shortened to the timed step count'
     else:
         step, x, threads = oracle_stepper(threads)
         with torch.no_grad():
@@ -416,6 +420,20 @@ def run_b200(args):
     other = 'bf16' if prec != 'bf16' else 'bf16x3'
     m2 = measure(other) if not args.single_mode else None
     genie.model.set_precision(prec)
+    # ---- blocks of the other multi-GPU configurations, measured after the contract's timed region; every rank takes part
+    sweep = c5 = None
+    if not args.no_extra_blocks:
+        try:
+            sweep = measure_length_sweep(genie, dev, world, rank, barrier, args.sweep_steps, prec)
+        except Exception as e:      # never lose the contract line to an extra block
+            sweep = {'error': '%s: %s' % (type(e).__name__, e)}
+        genie.model.set_precision(prec)
+        ctx = genie.model.bind_features(feats, dev)      # the sweep re-bound the context to its own batches
+        genie.bind_schedule(ctx)
+        try:
+            c5 = measure_c5(5, 3, world, rank, local, barrier)
+        except Exception as e:
+            c5 = {'error': '%s: %s' % (type(e).__name__, e)}
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -449,6 +467,10 @@ def run_b200(args):
                        'frac_of_tensor_sustained': fl / (ms / K * 1e-3) / 1e12 / pk['tensor_sustained']},
         'finite': finite,
     }
+    if sweep is not None:
+        line['length_sweep'] = sweep
+    if c5 is not None:
+        line['c5'] = c5
     if m2 is not None:
         # the other tensor-core mode on the same workload, same K / W, timed right after the headline mode
         r2 = kernel_table(genie_with(genie, other), ctx, lib, other, pk)
@@ -497,23 +519,17 @@ def run_b200(args):
         dist.destroy_process_group()
 
 
-def run_c5(args):
-    """BASELINE configs[4]: one unconditional L=1024 sample.  With N > 1 (torchrun) the pair representation is sharded
-    by rows over the ranks (csrc/shard.cu: NCCL all-gather / all-to-all of the triangle operands inside gb_denoise);
-    every rank holds the same x_t and the same noise, so this is STRONG scaling of one sample."""
+def measure_c5(K, W_, world, rank, local, barrier):
+    """BASELINE configs[4]: ONE unconditional L=1024 sample, bf16 mode.  With world > 1 the pair representation is sharded
+    by rows over the ranks (csrc/shard.cu: NCCL all-gather / all-to-all of the triangle operands inside gb_denoise); every
+    rank holds the same x_t and the same noise, so this is STRONG scaling of one sample.  Returns the result dict on
+    rank 0 (None elsewhere).  Collective: every rank must call it."""
     import torch
     import torch.distributed as dist
     import genie2_b200
     from genie2_b200 import _lib, shard
     from oracle import genie_oracle as O, weights as W     # seeded weights / synthetic features (host side only)
-
-    world, rank, local = (int(os.environ.get(k, d)) for k, d in (('WORLD_SIZE', '1'), ('RANK', '0'), ('LOCAL_RANK', '0')))
-    torch.cuda.set_device(local)
     dev = torch.device('cuda', local)
-    if world > 1:
-        dist.init_process_group('nccl', device_id=dev)
-    K = args.steps if args.steps is not None else 20
-    W_ = max(args.warmup if args.warmup is not None else 3, 3)
     n = 1024
     lib = _lib.load()
     cfg = O.OracleConfig()
@@ -536,20 +552,17 @@ def run_c5(args):
         _lib.check(lib.gb_sample_loop(ctx, x.data_ptr(), rots.data_ptr(), t_start, t_start - cnt + 1, SCALE, None, 1234, stream),
                    ctx, 'gb_sample_loop')
 
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
+    clocks = ClockSampler(local)
     loop(T_STEPS, W_)
     barrier()
-    clocks = ClockSampler(local)
+    wall0 = time.time()
     l0, c0 = genie.model.launch_count(), genie.model.collective_count()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     loop(T_STEPS - W_, K)
     e1.record()
     barrier()
+    wall1 = time.time()
     ms = torch.tensor([e0.elapsed_time(e1)], device=dev, dtype=torch.float64)
     digest = x.double().sum().reshape(1)
     if world > 1:
@@ -560,12 +573,13 @@ def run_c5(args):
         same = bool(lo == hi)
     else:
         same = True
-    clk = clocks.stop()
+    clk = clocks.stop(wall0, wall1)
+    out = None
     if rank == 0:
         ms = float(ms)
         fl = flops_per_eval(n, 1)
         pk = peaks()
-        print(json.dumps({
+        out = {
             'metric': 'denoiser evals/sec at L=1024 batch 1', 'value': K / (ms * 1e-3), 'unit': UNIT, 'n_gpus': world, 'steps': K,
             'warmup': W_, 'ms_per_step': ms / K, 'higher_is_better': True, 'scaling': 'strong', 'vs_baseline': None, 'dtype': 'bf16',
             'data': 'synthetic',
@@ -578,9 +592,107 @@ def run_c5(args):
             'finite': bool(torch.isfinite(x).all()), 'clocks': clk,
             'whole_eval': {'algorithmic_tflop_per_eval': fl / 1e12, 'achieved_tflops': fl / (ms / K * 1e-3) / 1e12,
                            'frac_of_tensor_sustained': fl / (ms / K * 1e-3) / 1e12 / pk['tensor_sustained'] / world},
-        }), flush=True)
+        }
+    del genie
+    torch.cuda.empty_cache()
+    return out
+
+
+def run_c5(args):
+    """--workload c5: the c5 block alone, as its own JSON line."""
+    import torch
+    import torch.distributed as dist
+    world, rank, local = (int(os.environ.get(k, d)) for k, d in (('WORLD_SIZE', '1'), ('RANK', '0'), ('LOCAL_RANK', '0')))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group('nccl', device_id=torch.device('cuda', local))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    out = measure_c5(args.steps if args.steps is not None else 20, max(args.warmup if args.warmup is not None else 3, 3), world, rank, local, barrier)
+    if rank == 0:
+        print(json.dumps(out), flush=True)
     if world > 1:
         dist.destroy_process_group()
+
+
+def measure_length_sweep(genie, dev, world, rank, barrier, steps, prec):
+    """BASELINE configs[2]: the reference's length-sweep task list (sample_unconditional.py:33-42,101-120: lengths 256..50,
+    5 samples per length, batch size 4) through the package's own scheduler -- plan_batches (full batches + ragged packing
+    of the left-over samples) and the shared dynamic queue of multiprocessor.py (a TCPStore fetch-add between the ranks; no
+    tensor travels, no collective on the data path) -- with `steps` reverse steps per batch instead of 1000.  Wall time
+    from a barrier to the barrier after the last rank has finished; every rank must call it."""
+    import torch
+    import torch.distributed as dist
+    import genie2_b200
+    from genie2_b200 import _lib
+    from genie2_b200.feat_utils import batchify_np_features, convert_np_features_to_tensor, create_empty_np_features
+    from genie2_b200.multiprocessor import StoreQueue, TaskQueue
+    from genie2_b200.sample_unconditional import plan_batches
+    lib = _lib.load()
+    genie.model.set_precision(prec)
+    lengths = list(range(256, 49, -1))
+    units = plan_batches(lengths, 5, 4)
+    q = StoreQueue(world, rank, key='gb_sweep') if world > 1 else None
+    queue = TaskQueue(units, q.claim if q else iter(range(len(units) + 1)).__next__)
+    stream = torch.cuda.current_stream(dev).cuda_stream
+    barrier()
+    t0 = time.perf_counter()
+    l0 = genie.model.launch_count()
+    n_units = n_samples = 0
+    t_bind = t_feat = t_loop = 0.0
+    ok = True
+    for u in queue:
+        tb = time.perf_counter()
+        feats = convert_np_features_to_tensor(batchify_np_features([create_empty_np_features([n]) for n in u['lengths']]), dev)
+        t_feat += time.perf_counter() - tb
+        ctx = genie.model.bind_features(feats, dev)      # synchronous: features upload, workspace re-carve, static embedding
+        genie.bind_schedule(ctx)
+        t_bind += time.perf_counter() - tb
+        nb = len(u['lengths'])
+        x = torch.randn(nb, u['length'], 3, device=dev) * feats['residue_mask'].unsqueeze(-1)
+        rots = genie2_b200.compute_frenet_frames(genie.model, feats, x)
+        tl = time.perf_counter()
+        _lib.check(lib.gb_sample_loop(ctx, x.data_ptr(), rots.data_ptr(), T_STEPS, T_STEPS - steps + 1, SCALE, None, 77 + n_units, stream),
+                   ctx, 'gb_sample_loop')
+        ok = ok and bool(torch.isfinite(x).all())        # (also the per-batch download a real run does)
+        t_loop += time.perf_counter() - tl
+        n_units += 1
+        n_samples += nb
+    torch.cuda.synchronize()
+    busy = time.perf_counter() - t0
+    launches = genie.model.launch_count() - l0
+    if q:
+        q.close()
+    barrier()
+    total = time.perf_counter() - t0
+    stats = torch.tensor([busy, float(n_units), float(n_samples), float(launches), 1.0 if ok else 0.0, total, t_bind, t_feat, t_loop], device=dev, dtype=torch.float64)
+    if world > 1:
+        allst = [torch.zeros_like(stats) for _ in range(world)]
+        dist.all_gather(allst, stats)
+    else:
+        allst = [stats]
+    if rank != 0:
+        return None
+    rows = [[float(v) for v in t.cpu()] for t in allst]
+    total = max(r[5] for r in rows)
+    return {
+        'workload': 'length sweep L=50..256 (207 lengths), 5 samples per length, batch 4 (BASELINE configs[2]); %d reverse steps per batch '
+                    'instead of 1000' % steps,
+        'precision': prec, 'n_gpus': world, 'steps_per_batch': steps, 'batches': len(units),
+        'scheduler': 'plan_batches: 207 full batches + 52 ragged batches of left-over samples; shared dynamic queue, largest first',
+        'seconds': total, 'samples': int(sum(r[2] for r in rows)), 'sample_steps_per_s': sum(r[2] for r in rows) * steps / total,
+        'per_rank_busy_seconds': [r[0] for r in rows], 'per_rank_batches': [int(r[1]) for r in rows],
+        # once per batch whatever the step count (< 1 % of a 1000-step run): host feature build + upload + gb_set_features
+        'per_rank_bind_seconds': [r[6] for r in rows], 'per_rank_feature_build_seconds': [r[7] for r in rows],
+        'per_rank_sample_loop_seconds': [r[8] for r in rows],
+
+        'gpu_launches': int(sum(r[3] for r in rows)), 'finite': all(r[4] == 1.0 for r in rows),
+        'scaling': 'strong (fixed task list)',
+    }
 
 
 if __name__ == '__main__':

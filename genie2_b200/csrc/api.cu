@@ -115,6 +115,7 @@ static void free_features(gb_ctx* c) {
   if (c->feat_alloc) cudaFree(c->feat_alloc);
   if (c->ws_alloc) cudaFree(c->ws_alloc);
   c->feat_alloc = c->ws_alloc = nullptr;
+  c->feat_cap = c->ws_cap = 0;
   c->features_set = false;
 }
 
@@ -496,16 +497,25 @@ extern "C" int gb_set_features(gb_ctx* c, const gb_features* f) {
   const int B = f->B, N = f->N;
   if (!c->features_set || B != c->B || N != c->N) {
     GB_CUDA(c, cudaDeviceSynchronize());
-    free_features(c);
     Carver kf{nullptr}, kw{nullptr};
     carve_features(c, kf, B, N);
     carve_workspace(c, kw, B, N);
     const size_t tcb = tc_workspace_bytes(c, B, N);
-    GB_CUDA(c, cudaMalloc(&c->feat_alloc, kf.off + 256));
-    cudaError_t e = cudaMalloc(&c->ws_alloc, kw.off + 512 + tcb);
-    if (e != cudaSuccess) {
-      cudaFree(c->feat_alloc); c->feat_alloc = nullptr;
-      return gb_fail(c, GB_ERR_CUDA, "workspace allocation of %zu bytes failed: %s", kw.off + tcb, cudaGetErrorString(e));
+    // grow-only: a batch that fits in what an earlier, larger batch allocated is re-carved in place (a length sweep that
+    // runs its largest batches first allocates once)
+    if (kf.off + 256 > c->feat_cap || kw.off + 512 + tcb > c->ws_cap) {
+      free_features(c);
+      GB_CUDA(c, cudaMalloc(&c->feat_alloc, kf.off + 256));
+      cudaError_t e = cudaMalloc(&c->ws_alloc, kw.off + 512 + tcb);
+      if (e != cudaSuccess) {
+        cudaFree(c->feat_alloc); c->feat_alloc = nullptr;
+        return gb_fail(c, GB_ERR_CUDA, "workspace allocation of %zu bytes failed: %s", kw.off + tcb, cudaGetErrorString(e));
+      }
+      c->feat_cap = kf.off + 256;
+      c->ws_cap = kw.off + 512 + tcb;
+    } else {
+      drop_step_graph(c);
+      c->features_set = false;
     }
     c->ws_bytes = kf.off + kw.off + tcb + 768;
     // GB_DEBUG_POISON=1: fill the fresh workspace with NaN patterns so that any read of a never-written location shows

@@ -319,3 +319,7 @@ class Denoiser(nn.Module):
 
     def launch_count(self):
         return int(_lib.load().gb_launch_count(self._ctx)) if self._ctx is not None else 0
+
+    def workspace_bytes(self):
+        """Device bytes of the feature + workspace carve of the batch that is bound now."""
+        return int(_lib.load().gb_workspace_bytes(self._ctx)) if self._ctx is not None else 0
