@@ -253,7 +253,7 @@ static int pack_triatt(gb_ctx* c, Getter& G, const std::string& pre, TriAttW& w)
   std::copy(bg.begin(), bg.end(), bq.begin() + 3 * hc);
   w.bqkvg = upload(c, bq);
   w.Wo = upload(c, wo); w.bo = upload(c, bo);
-  return GB_OK;
+  return tc_pack_triatt(c, w, wq, wk, wv, wg, wo);
 }
 
 extern "C" int gb_load_weights(gb_ctx* c, const gb_tensor* tensors, int n) {
@@ -478,7 +478,7 @@ static void carve_workspace(gb_ctx* c, Carver& k, int B, int N) {
   c->g = k.take<float>(M * 128);
   if (c->d.include_tri_att) {   // a..g double as the [M][512] q|k|v|g buffer of K8
     c->ta_x = k.take<float>(M * 128);
-    c->ta_bias = k.take<float>(M * TA_H);
+    c->ta_bias = k.take<float>((size_t)B * N * (((size_t)N + 63) / 64 * 64) * TA_H);   // [B][4][N][Np] (tensor-core kernels) >= [M][4]
   }
 }
 
@@ -625,8 +625,11 @@ static int run_trimul(gb_ctx* c, const TriMulW& w, bool outgoing, float* p, cuda
   return GB_OK;
 }
 
-// K8: p += TriangleAttention(p) (pair_transform_net.py:109-119); fp32 CUDA cores in every precision mode.
+// K8: p += TriangleAttention(p) (pair_transform_net.py:109-119).  GB_PREC_BF16: tcgen05 kernels (tc_triatt.cu).  fp32 and
+// bf16x3: the fp32 CUDA-core kernels below (a three-pass split attention is not built; the fp32 path keeps the 1e-3 gate).
 static int run_triatt(gb_ctx* c, const TriAttW& w, bool starting, float* p, cudaStream_t st) {
+  static const int tri_tc = [] { const char* e = getenv("GB_TRIATT_TC"); return e ? atoi(e) : 0; }();   // until verified on the GPU
+  if (c->precision == GB_PREC_BF16 && tri_tc) return tc_tri_attention(c, w, starting, p, st);
   const int B = c->B, N = c->N;
   const size_t M = (size_t)B * N * N;
   if (M > (size_t)INT32_MAX) return gb_fail(c, GB_ERR_UNSUPPORTED, "triangle attention: B*N*N too large");

@@ -39,6 +39,12 @@ int tc_trimul_stage(gb_ctx* c, const TriMulW& w, bool outgoing, int stage, float
 // p = (p + PairTransition(p)) * mask
 int tc_pair_transition(gb_ctx* c, const TransitionW& w, float* p, cudaStream_t st);
 
+// ---- triangle attention on tensor cores (tc_triatt.cu, GB_PREC_BF16)
+int tc_triatt_init(gb_ctx* c);
+int tc_pack_triatt(gb_ctx* c, TriAttW& w, const std::vector<float>& wq, const std::vector<float>& wk, const std::vector<float>& wv,
+                   const std::vector<float>& wg, const std::vector<float>& wo);
+int tc_tri_attention(gb_ctx* c, const TriAttW& w, bool starting, float* p, cudaStream_t st);
+
 // ---- pair embedding on tensor cores (tc_embed.cu); wt [128][nbin + 6], wm [128][nbin + 2] as in the state dict
 int tc_pack_pair_embed(gb_ctx* c, const std::vector<float>& wt, const std::vector<float>& wm, int nbin);
 bool tc_pair_embed_supported(const gb_ctx* c);

@@ -57,14 +57,18 @@ __device__ __forceinline__ uint32_t mbar_try_wait_hint(uint64_t* bar, uint32_t p
       : "memory");
   return ok;
 }
-// Bounded wait: a protocol bug traps (launch error reported to the caller) instead of hanging the GPU.  The bound is a count
-// of suspended waits (2^24 of them: a fraction of a second if the hardware ignores the hint, seconds if it honours it), not a clock64() poll: in round 1 the CS2R / ISETP / BRA of the polling
-// loop were a quarter of all instructions the persistent kernels issued, taken from the warps that had work.
+// Bounded wait: a protocol bug traps (launch error reported to the caller) instead of hanging the GPU.  The wait suspends
+// in hardware (10 us hint per try) and only looks at the clock every 64th try after the first 64: in round 1 the CS2R /
+// ISETP / BRA of a clock64() polling loop were a quarter of all instructions the persistent kernels issued, taken from
+// the warps that had work.  Time-out ~2 s.
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   if (mbar_try_wait(bar, parity)) return;
   uint32_t tries = 0;
-  while (!mbar_try_wait_hint(bar, parity, 1000000u)) {
-    if (++tries > (1u << 24)) __trap();
+  long long t0 = 0;
+  while (!mbar_try_wait_hint(bar, parity, 10000u)) {
+    ++tries;
+    if (tries == 64u) t0 = clock64();
+    else if (tries > 64u && (tries & 63u) == 0u && clock64() - t0 > 4000000000LL) __trap();
   }
 }
 

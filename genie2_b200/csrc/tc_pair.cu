@@ -811,6 +811,7 @@ int tc_init(gb_ctx* c) {
   c->tc_state = new TcState();
   int rc = tc_proj_init(c);
   if (rc == GB_OK) rc = tc_transition_init(c);
+  if (rc == GB_OK) rc = tc_triatt_init(c);
   return rc != GB_OK ? rc : tc_struct_init(c);
 }
 

@@ -1,0 +1,482 @@
+// K8 on tensor cores (GB_PREC_BF16): triangle attention around the starting / ending node
+// (modules/triangular_attention.py:67-130, modules/primitives.py:222-281; 4 heads x 32).
+//   p += linear_o( softmax_k( q_ij . k_ik / sqrt(32) + 1e9 (mask_ik - 1) + b_jk ) v_ik * sigmoid(g_ij) )
+// "Row" i and positions j, k live in the ATTENTION frame: for the starting node that is the pair map itself, for the
+// ending node its transpose (triangular_attention.py:84-86,127-128); the transpose is an index mapping when p is read and
+// written, pix(i, j) = starting ? (i, j) : (j, i); every intermediate buffer is laid out in the attention frame.
+//
+//   triatt_proj_tc_kernel   one CTA = 128 consecutive positions j of one row (b, i): LayerNorm -> bf16 operand image X;
+//                           four 128 x 128 x 128 tcgen05 GEMMs into the 512 tensor-memory columns:
+//                             D_q [px][ch] | D_k [px][ch] | D_g [px][ch] | D_vT [ch][px] = W_v X^T (so V lands key-contiguous)
+//                           outputs: Q, K row images [b][i][2 kb][Np rows][64] (1/sqrt(32) folded into W_q), V^T images
+//                           [b][i][Np/64][128 ch][64 keys], gate sigmoid(.) bf16 [b][i][j][128], and the triangle bias
+//                           b_jk = linear(x_jk) [b][4][j][Np] in fp32 on CUDA cores from the normalised row (4 dot products).
+//   triatt_core_tc_kernel   one CTA = 128 queries j of one row (b, i), all four heads, keys in blocks of 256:
+//                             S = Q_h K_h^T            SS MMA, M = 128, N <= 256, K = 32 (two k steps inside a 64-wide image)
+//                             softmax                  256 threads: thread = (query row, half of the keys); bias and mask
+//                                                      added in the reference's order; running max / sum (flash style)
+//                             O_h += P V_h             TS MMA: P (bf16) from tensor memory, V^T rows of head h from shared
+//                           then og = O / l * gate as an operand image, D = og W_o^T, p[pix] += D + b_o.
+//   Tensor memory: S 256 | P 128 | O 4 x 32 columns.
+#include <vector>
+
+#include "common.cuh"
+#include "tc_api.h"
+#include "tc_common.cuh"
+#include "tc_host.h"
+#include "tc_state.h"
+
+using namespace tc;
+
+#define TA_HEADS 4
+#define TA_CH 32
+
+__device__ __forceinline__ float ex2_approx(float x) {
+  float r;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+}
+
+// 64 fp32 values of one thread -> one 128-byte row of an operand image (8 chunks of 8 bf16, chunk c at position c ^ (r & 7))
+__device__ __forceinline__ void store_image_row(uint8_t* row, uint32_t r, const uint32_t (&v)[64]) {
+  const bool swap = r & 1u;
+#pragma unroll
+  for (int cp = 0; cp < 4; ++cp) {     // chunk pairs share a 32-byte sector
+    uint4 o[2];
+#pragma unroll
+    for (int c = 0; c < 2; ++c) {
+      const uint32_t* s = v + (2 * cp + c) * 8;
+      o[c].x = pack_bf16(__uint_as_float(s[0]), __uint_as_float(s[1]));
+      o[c].y = pack_bf16(__uint_as_float(s[2]), __uint_as_float(s[3]));
+      o[c].z = pack_bf16(__uint_as_float(s[4]), __uint_as_float(s[5]));
+      o[c].w = pack_bf16(__uint_as_float(s[6]), __uint_as_float(s[7]));
+    }
+    st_global_32B(row + (((2u * cp) ^ (r & 6u)) << 4), swap ? o[1] : o[0], swap ? o[0] : o[1]);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// projections
+// ---------------------------------------------------------------------------------------------
+#define TAP_SMEM (32768 + 4 * 32768 + 2048 + 64 + 1024)
+
+__global__ void __launch_bounds__(256, 1) triatt_proj_tc_kernel(
+    const float* __restrict__ p, int N, int Np, const float* __restrict__ ln_g, const float* __restrict__ ln_b,
+    const bf16* __restrict__ Wimg /* q (scaled) | k | v | g */, const float* __restrict__ Wb /*[4][128]*/, const float* __restrict__ bg,
+    bf16* __restrict__ Qimg, bf16* __restrict__ Kimg, bf16* __restrict__ VTimg, bf16* __restrict__ G, float* __restrict__ tb,
+    int starting) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* sm = smem_base_1024(smem_raw);
+  uint8_t* X = sm;
+  uint8_t* W = sm + 32768;
+  float* tbs = reinterpret_cast<float*>(sm + 32768 + 4 * 32768);    // [4][128]
+  uint64_t* bar_w = reinterpret_cast<uint64_t*>(sm + 32768 + 4 * 32768 + 2048);
+  uint64_t* bar_mma = bar_w + 1;
+  uint32_t* tslot = reinterpret_cast<uint32_t*>(bar_w + 2);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int jt = blockIdx.x, i = blockIdx.y, b = blockIdx.z;
+  const size_t sample = (size_t)b * N * N;
+  if (tid == 0) {
+    mbar_init(bar_w, 1);
+    mbar_init(bar_mma, 1);
+    fence_mbar_init();
+    mbar_expect_tx(bar_w, 4 * 32768);
+    bulk_g2s(W, Wimg, 4 * 32768, bar_w);       // weights: nothing the previous kernel writes
+  }
+  if (warp == 1) tmem_alloc(tslot, 512);
+  pdl_wait();
+  {
+    // LayerNorm of the tile's rows -> bf16 image; the triangle bias from the normalised fp32 row.  Positions >= N
+    // (padding up to Np) become zero rows: q = k = v = 0 there.
+    const float4 g4 = ld4(ln_g + lane * 4), b4 = ld4(ln_b + lane * 4);
+    float4 wb[TA_HEADS];
+#pragma unroll
+    for (int h = 0; h < TA_HEADS; ++h) wb[h] = ld4(Wb + h * 128 + lane * 4);
+    const uint32_t kb = lane >> 4, chunk = (lane & 15) >> 1, half = lane & 1;
+#pragma unroll
+    for (int it = 0; it < 2; ++it) {
+      float4 v[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int m = warp * 16 + it * 8 + u, j = jt * 128 + m;
+        v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (j < N) v[u] = ld4(p + (sample + (starting ? (size_t)i * N + j : (size_t)j * N + i)) * 128 + lane * 4);
+      }
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const uint32_t m = warp * 16 + it * 8 + u;
+        const bool ok = jt * 128 + (int)m < N;
+        const float mean = warp_sum(v[u].x + v[u].y + v[u].z + v[u].w) * (1.f / 128.f);
+        const float dx = v[u].x - mean, dy = v[u].y - mean, dz = v[u].z - mean, dw = v[u].w - mean;
+        const float rstd = rsqrtf(warp_sum(dx * dx + dy * dy + dz * dz + dw * dw) * (1.f / 128.f) + 1e-5f);
+        float4 y = make_float4(dx * rstd * g4.x + b4.x, dy * rstd * g4.y + b4.y, dz * rstd * g4.z + b4.z, dw * rstd * g4.w + b4.w);
+        if (!ok) y = make_float4(0.f, 0.f, 0.f, 0.f);
+        uint2 o;
+        o.x = pack_bf16(y.x, y.y);
+        o.y = pack_bf16(y.z, y.w);
+        *reinterpret_cast<uint2*>(X + kb * 16384u + m * 128u + ((chunk ^ (m & 7u)) << 4) + half * 8u) = o;
+#pragma unroll
+        for (int h = 0; h < TA_HEADS; ++h) {
+          const float t = warp_sum(y.x * wb[h].x + y.y * wb[h].y + y.z * wb[h].z + y.w * wb[h].w);
+          if (lane == h) tbs[h * 128 + m] = t;
+        }
+      }
+    }
+  }
+  fence_proxy_async();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tslot;
+  pdl_launch();
+  if (warp == 0) {
+    mbar_wait(bar_w, 0);
+    tc_fence_after();
+    const uint32_t xs = smem_u32(X), ws = smem_u32(W), tm = warp_uniform(tmem);
+    if (elect_one()) {
+      umma_tile(tm, xs, ws, 128, 2, false);                    // D_q  [px][ch]
+      umma_tile(tm + 128u, xs, ws + 32768u, 128, 2, false);    // D_k
+      umma_tile(tm + 256u, xs, ws + 3 * 32768u, 128, 2, false);// D_g
+      umma_tile(tm + 384u, ws + 2 * 32768u, xs, 128, 2, false);// D_vT [ch][px]
+      umma_commit(bar_mma);
+    }
+    __syncwarp();
+  }
+  // triangle bias rows (coalesced over the positions of the tile)
+  for (int e = tid; e < TA_HEADS * 128; e += 256) {
+    const int h = e >> 7, m = e & 127, j = jt * 128 + m;
+    if (j < Np) tb[(((size_t)b * TA_HEADS + h) * N + i) * Np + j] = tbs[e];
+  }
+  mbar_wait(bar_mma, 0);
+  tc_fence_after();
+  const uint32_t q = warp & 3, hf = warp >> 2, m = q * 32 + lane;
+  const uint32_t t_lane = tmem + ((q * 32u) << 16);
+  const int j = jt * 128 + (int)m;
+  const size_t rowi = (size_t)b * N + i;
+  {
+    uint32_t v[64];
+    // q, k: this thread = position j, channels [64 hf, 64 hf + 64) = k-block hf of the row image
+    tmem_ld32(t_lane + hf * 64u, *reinterpret_cast<uint32_t(*)[32]>(v));
+    tmem_ld32(t_lane + hf * 64u + 32u, *reinterpret_cast<uint32_t(*)[32]>(v + 32));
+    tmem_ld_wait();
+    if (j < Np) store_image_row(reinterpret_cast<uint8_t*>(Qimg + ((rowi * 2 + hf) * Np + j) * 64), (uint32_t)j, v);
+    tmem_ld32(t_lane + 128u + hf * 64u, *reinterpret_cast<uint32_t(*)[32]>(v));
+    tmem_ld32(t_lane + 128u + hf * 64u + 32u, *reinterpret_cast<uint32_t(*)[32]>(v + 32));
+    tmem_ld_wait();
+    if (j < Np) store_image_row(reinterpret_cast<uint8_t*>(Kimg + ((rowi * 2 + hf) * Np + j) * 64), (uint32_t)j, v);
+    // gate: sigmoid(W_g x + b_g), plain row-major bf16 [b][i][j][128]
+    tmem_ld32(t_lane + 256u + hf * 64u, *reinterpret_cast<uint32_t(*)[32]>(v));
+    tmem_ld32(t_lane + 256u + hf * 64u + 32u, *reinterpret_cast<uint32_t(*)[32]>(v + 32));
+    tmem_ld_wait();
+    if (j < N) {
+      uint8_t* dst = reinterpret_cast<uint8_t*>(G + (rowi * N + j) * 128 + hf * 64);
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        uint32_t o[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          const int ch = c * 16 + 2 * e;
+          o[e] = pack_bf16(fast_sigmoid(__uint_as_float(v[ch]) + bg[hf * 64 + ch]), fast_sigmoid(__uint_as_float(v[ch + 1]) + bg[hf * 64 + ch + 1]));
+        }
+        st_global_32B(dst + c * 32, make_uint4(o[0], o[1], o[2], o[3]), make_uint4(o[4], o[5], o[6], o[7]));
+      }
+    }
+    // v^T: this thread = channel m, keys [64 hf, 64 hf + 64) of the tile = key block 2 jt + hf
+    tmem_ld32(t_lane + 384u + hf * 64u, *reinterpret_cast<uint32_t(*)[32]>(v));
+    tmem_ld32(t_lane + 384u + hf * 64u + 32u, *reinterpret_cast<uint32_t(*)[32]>(v + 32));
+    tmem_ld_wait();
+    const uint32_t kb64 = 2 * jt + hf;
+    if (kb64 < (uint32_t)(Np >> 6))
+      store_image_row(reinterpret_cast<uint8_t*>(VTimg + (((rowi * (Np >> 6)) + kb64) * 128 + m) * 64), m, v);
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem, 512);
+}
+
+// ---------------------------------------------------------------------------------------------
+// attention core + output projection + residual
+// ---------------------------------------------------------------------------------------------
+#define TAC_OFF_K 32768u
+#define TAC_OFF_VT (32768u + 65536u)
+#define TAC_OFF_WO (32768u + 2 * 65536u)
+#define TAC_OFF_MISC (32768u + 2 * 65536u + 32768u)
+#define TAC_SMEM (TAC_OFF_MISC + 2048 /*red*/ + 1024 /*mbs*/ + 128 + 1024)
+#define LOG2E 1.4426950408889634f
+
+__global__ void __launch_bounds__(256, 1) triatt_core_tc_kernel(
+    const bf16* __restrict__ Qimg, const bf16* __restrict__ Kimg, const bf16* __restrict__ VTimg, const bf16* __restrict__ G,
+    const float* __restrict__ tb, const int* __restrict__ rmask, const bf16* __restrict__ Woimg, const float* __restrict__ bo,
+    float* __restrict__ p, int N, int Np, int starting) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* sm = smem_base_1024(smem_raw);
+  uint8_t* Qs = sm;                       // [2 kb][128 rows][64]; later the og image
+  uint8_t* Ks = sm + TAC_OFF_K;           // [2 kb][nk rows][64]
+  uint8_t* VTs = sm + TAC_OFF_VT;         // [nk/64][128 ch][64 keys]
+  uint8_t* Wos = sm + TAC_OFF_WO;
+  float* red = reinterpret_cast<float*>(sm + TAC_OFF_MISC);           // [2 halves][128 rows] (+ [2][128] for the sums)
+  float* mbs = red + 512;                                               // [256] mask bias of the keys of the block
+  uint64_t* bar_q = reinterpret_cast<uint64_t*>(sm + TAC_OFF_MISC + 3072);
+  uint64_t *bar_ld = bar_q + 1, *bar_s = bar_q + 2, *bar_o = bar_q + 3, *bar_w = bar_q + 4;
+  uint32_t* tslot = reinterpret_cast<uint32_t*>(bar_q + 5);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int qt = blockIdx.x, i = blockIdx.y, b = blockIdx.z;
+  const size_t rowi = (size_t)b * N + i;
+  const int qrows = min(128, Np - qt * 128);
+  if (tid == 0) {
+    mbar_init(bar_q, 1); mbar_init(bar_ld, 1); mbar_init(bar_s, 1); mbar_init(bar_o, 1); mbar_init(bar_w, 1);
+    fence_mbar_init();
+    mbar_expect_tx(bar_w, 32768);
+    bulk_g2s(Wos, Woimg, 32768, bar_w);
+  }
+  if (warp == 1) tmem_alloc(tslot, 512);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tslot;
+  const uint32_t T_S = 0, T_P = 256, T_O = 384;
+  pdl_wait();
+  pdl_launch();
+  if (tid == 0) {
+    mbar_expect_tx(bar_q, 2u * qrows * 128u);
+    for (int kb = 0; kb < 2; ++kb)
+      bulk_g2s(Qs + kb * 16384, Qimg + ((rowi * 2 + kb) * Np + qt * 128) * 64, qrows * 128u, bar_q);
+  }
+  const uint32_t q = warp & 3, hf = warp >> 2, m = q * 32 + lane;
+  const uint32_t t_lane = tmem + ((q * 32u) << 16);
+  const int j = qt * 128 + (int)m, jc = j < N ? j : N - 1;     // padded query rows read a valid bias row (never written)
+  const int mi = rmask[b * N + i];
+  float mrun[TA_HEADS], lrun[TA_HEADS];
+#pragma unroll
+  for (int h = 0; h < TA_HEADS; ++h) { mrun[h] = -3.0e38f; lrun[h] = 0.f; }
+  const int nblk = (Np + 255) >> 8;
+  const uint32_t tm = warp_uniform(tmem), qs = smem_u32(Qs), ks = smem_u32(Ks), vts = smem_u32(VTs);
+  uint32_t ns = 0;                     // S commits so far (phase of bar_s)
+
+  auto issue_S = [&](int h, uint32_t nk) {      // warp 0, converged
+    tc_fence_after();
+    if (elect_one()) {
+      const uint32_t kb = h >> 1, off = (h & 1) * 64u;
+#pragma unroll
+      for (uint32_t s2 = 0; s2 < 2; ++s2)
+        umma(tm + T_S, umma_desc(qs + kb * 16384u + off + s2 * 32u), umma_desc(ks + kb * (nk * 128u) + off + s2 * 32u), umma_idesc(128, nk), s2);
+      umma_commit(bar_s);
+    }
+    __syncwarp();
+  };
+
+  for (int blk = 0; blk < nblk; ++blk) {
+    const int k0 = blk * 256;
+    const uint32_t nk = (uint32_t)min(256, Np - k0), hw = nk >> 1;      // keys of this block; per half
+    if (blk > 0) {
+      mbar_wait(bar_o, (blk - 1) & 1);    // the P V MMAs of the previous block have read K / V^T and updated O
+      tc_fence_after();
+      __syncthreads();
+    }
+    if (tid == 0) {
+      mbar_expect_tx(bar_ld, 2u * nk * 128u + nk * 256u);
+      for (int kb = 0; kb < 2; ++kb)
+        bulk_g2s(Ks + kb * (nk * 128u), Kimg + ((rowi * 2 + kb) * Np + k0) * 64, nk * 128u, bar_ld);
+      bulk_g2s(VTs, VTimg + ((rowi * (Np >> 6)) + (k0 >> 6)) * 8192, nk * 256u, bar_ld);
+    }
+    if (tid < (int)nk) {
+      const int k = k0 + tid;
+      mbs[tid] = k < N ? 1e9f * ((float)(mi * rmask[b * N + k]) - 1.f) : -3.0e38f;
+    }
+    if (blk == 0) mbar_wait(bar_q, 0);
+    mbar_wait(bar_ld, blk & 1);
+    __syncthreads();
+    if (warp == 0) issue_S(0, nk);
+    for (int h = 0; h < TA_HEADS; ++h) {
+      mbar_wait(bar_s, ns & 1);          // S_h complete (and every MMA issued before it: P V of the previous head)
+      ++ns;
+      tc_fence_after();
+      // ---- pass 1: s = q.k + mask bias + triangle bias (the reference's order), written back; row maximum
+      const float* tbr = tb + (((size_t)b * TA_HEADS + h) * N + jc) * Np + k0 + hf * hw;
+      float mx = -3.0e38f;
+      for (uint32_t c = 0; c < hw; c += 32) {
+        uint32_t v[32];
+        tmem_ld32(t_lane + T_S + hf * hw + c, v);
+        float4 t4[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) t4[e] = ld4(tbr + c + 4 * e);
+        tmem_ld_wait();
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          const float4 mb4 = *reinterpret_cast<const float4*>(mbs + hf * hw + c + 4 * e);
+          const float s0 = (__uint_as_float(v[4 * e]) + mb4.x) + t4[e].x, s1 = (__uint_as_float(v[4 * e + 1]) + mb4.y) + t4[e].y;
+          const float s2 = (__uint_as_float(v[4 * e + 2]) + mb4.z) + t4[e].z, s3 = (__uint_as_float(v[4 * e + 3]) + mb4.w) + t4[e].w;
+          mx = fmaxf(fmaxf(mx, fmaxf(s0, s1)), fmaxf(s2, s3));
+          v[4 * e] = __float_as_uint(s0); v[4 * e + 1] = __float_as_uint(s1); v[4 * e + 2] = __float_as_uint(s2); v[4 * e + 3] = __float_as_uint(s3);
+        }
+        tmem_st32(t_lane + T_S + hf * hw + c, v);
+      }
+      tmem_st_wait();
+      red[hf * 128 + m] = mx;
+      __syncthreads();
+      const float mnew = fmaxf(mrun[h], fmaxf(red[m], red[128 + m]));
+      const float corr = ex2_approx((mrun[h] - mnew) * LOG2E);
+      mrun[h] = mnew;
+      // ---- pass 2: probabilities (bf16) into tensor memory, row sums; O_h rescaled when the maximum moved
+      const float nm = -mnew * LOG2E;
+      float sum = 0.f;
+      for (uint32_t c = 0; c < hw; c += 32) {
+        uint32_t v[32], pk[16];
+        tmem_ld32(t_lane + T_S + hf * hw + c, v);
+        tmem_ld_wait();
+#pragma unroll
+        for (int e = 0; e < 16; ++e) {
+          const float p0 = ex2_approx(fmaf(__uint_as_float(v[2 * e]), LOG2E, nm)), p1 = ex2_approx(fmaf(__uint_as_float(v[2 * e + 1]), LOG2E, nm));
+          pk[e] = pack_bf16(p0, p1);
+          // sum what the tensor core will multiply with: the bf16-rounded probabilities
+          const float2 r = unpack_bf16x2(pk[e]);
+          sum += r.x + r.y;
+        }
+        tmem_st16(t_lane + T_P + ((hf * hw + c) >> 1), pk);
+      }
+      lrun[h] = lrun[h] * corr + sum;
+      if (blk > 0 && hf == 0) {
+        uint32_t o[32];
+        tmem_ld32(t_lane + T_O + h * 32, o);
+        tmem_ld_wait();
+#pragma unroll
+        for (int e = 0; e < 32; ++e) o[e] = __float_as_uint(__uint_as_float(o[e]) * corr);
+        tmem_st32(t_lane + T_O + h * 32, o);
+      }
+      tmem_st_wait();
+      tc_fence_before();
+      __syncthreads();
+      if (warp == 0) {
+        tc_fence_after();
+        if (elect_one()) {
+          // O_h (+)= P . V_h : A = P from tensor memory (16 keys = 8 columns per step), B = rows [32 h, 32 h + 32) of the V^T blocks
+          for (uint32_t kb64 = 0; kb64 < (nk >> 6); ++kb64)
+#pragma unroll
+            for (uint32_t s4 = 0; s4 < 4; ++s4)
+              umma_ts(tm + T_O + h * 32u, tm + T_P + kb64 * 32u + s4 * 8u, umma_desc(vts + kb64 * 16384u + h * 4096u + s4 * 32u), umma_idesc(128, 32),
+                      (blk | (int)kb64 | (int)s4) ? 1u : 0u);
+          if (h == TA_HEADS - 1) umma_commit(bar_o);
+        }
+        __syncwarp();
+        if (h + 1 < TA_HEADS) issue_S(h + 1, nk);
+      }
+    }
+  }
+  mbar_wait(bar_o, (nblk - 1) & 1);
+  tc_fence_after();
+  // ---- og = O / l * gate -> operand image (in place of the Q tile); this thread: row m, heads 2 hf and 2 hf + 1
+  // exchange the partial row sums of the two key halves, one head at a time through red[2][128]
+  float inv[TA_HEADS];
+#pragma unroll
+  for (int h = 0; h < TA_HEADS; ++h) {
+    red[hf * 128 + m] = lrun[h];
+    __syncthreads();
+    inv[h] = 1.f / (red[m] + red[128 + m]);
+    __syncthreads();
+  }
+  {
+    const uint16_t* grow = reinterpret_cast<const uint16_t*>(G) + (rowi * N + (j < N ? j : 0)) * 128;
+#pragma unroll
+    for (int hh = 0; hh < 2; ++hh) {
+      const int h = 2 * hf + hh;
+      uint32_t o[32];
+      tmem_ld32(t_lane + T_O + h * 32, o);
+      uint4 g4[4];
+#pragma unroll
+      for (int e = 0; e < 4; ++e) g4[e] = *reinterpret_cast<const uint4*>(grow + h * 32 + e * 8);
+      tmem_ld_wait();
+      const uint32_t* gw = reinterpret_cast<const uint32_t*>(g4);
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {      // 4 chunks of 8 channels
+        uint32_t w[4];
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const float2 gg = unpack_bf16x2(gw[c * 4 + e]);
+          w[e] = pack_bf16(__uint_as_float(o[c * 8 + 2 * e]) * inv[h] * gg.x, __uint_as_float(o[c * 8 + 2 * e + 1]) * inv[h] * gg.y);
+        }
+        const uint32_t chunk = (uint32_t)(h & 1) * 4u + c;       // channel h*32 + c*8 -> k-block h >> 1, chunk within the 64
+        *reinterpret_cast<uint4*>(Qs + (h >> 1) * 16384u + m * 128u + ((chunk ^ (m & 7u)) << 4)) = make_uint4(w[0], w[1], w[2], w[3]);
+      }
+    }
+  }
+  fence_proxy_async();
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) {
+    mbar_wait(bar_w, 0);
+    tc_fence_after();
+    if (elect_one()) {
+      umma_tile(tm + T_S, qs, smem_u32(Wos), 128, 2, false);
+      umma_commit(bar_s);
+    }
+    __syncwarp();
+  }
+  mbar_wait(bar_s, ns & 1);
+  tc_fence_after();
+  {
+    // (the tensor-memory loads are warp-collective: every lane executes them, only the read-modify-write of p is guarded)
+    float* prow = p + ((size_t)b * N * N + (starting ? (size_t)i * N + jc : (size_t)jc * N + i)) * 128 + hf * 64;
+#pragma unroll 1
+    for (int c = 0; c < 2; ++c) {
+      uint32_t v[32];
+      tmem_ld32(t_lane + T_S + hf * 64 + c * 32, v);
+      tmem_ld_wait();
+      if (j < N) {
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          float4 r = ld4(prow + c * 32 + 4 * e);
+          const float4 b4 = ld4(bo + hf * 64 + c * 32 + 4 * e);
+          r.x += __uint_as_float(v[4 * e]) + b4.x; r.y += __uint_as_float(v[4 * e + 1]) + b4.y;
+          r.z += __uint_as_float(v[4 * e + 2]) + b4.z; r.w += __uint_as_float(v[4 * e + 3]) + b4.w;
+          st4(prow + c * 32 + 4 * e, r);
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem, 512);
+}
+
+// ---------------------------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------------------------
+int tc_triatt_init(gb_ctx* c) {
+  cudaError_t e;
+  if ((e = cudaFuncSetAttribute(triatt_proj_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TAP_SMEM)) != cudaSuccess ||
+      (e = cudaFuncSetAttribute(triatt_core_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TAC_SMEM)) != cudaSuccess)
+    return gb_fail(c, GB_ERR_CUDA, "tc_triatt_init: cudaFuncSetAttribute failed: %s", cudaGetErrorString(e));
+  return GB_OK;
+}
+
+// wq, wk, wv, wg [128 = 4 heads x 32][128 in]; wo [128 out][128 = 4 heads x 32]
+int tc_pack_triatt(gb_ctx* c, TriAttW& w, const std::vector<float>& wq, const std::vector<float>& wk, const std::vector<float>& wv,
+                   const std::vector<float>& wg, const std::vector<float>& wo) {
+  std::vector<uint16_t> img(4 * 16384), io(16384);
+  const float sc = 1.f / sqrtf((float)TA_CH);
+  const std::vector<float>* src[4] = {&wq, &wk, &wv, &wg};
+  for (int t = 0; t < 4; ++t)
+    pack_image(img.data() + (size_t)t * 16384, 128, 128, [&](int r, int k) { return (t == 0 ? sc : 1.f) * (*src[t])[(size_t)r * 128 + k]; });
+  pack_image(io.data(), 128, 128, [&](int r, int k) { return wo[(size_t)r * 128 + k]; });
+  w.tc_Wqkvg = upload_bytes(c, img.data(), img.size() * 2);
+  w.tc_Wo = upload_bytes(c, io.data(), io.size() * 2);
+  if (!w.tc_Wqkvg || !w.tc_Wo) return gb_fail(c, GB_ERR_CUDA, "tc_pack_triatt: device allocation failed");
+  return GB_OK;
+}
+
+// p += TriangleAttention(p) on tensor cores.  Q / K / V^T / gate live in the a / b / x / g planes of the pair workspace
+// (the triangle updates have finished with them), the triangle bias in c->ta_bias ([B][4][N][Np] fp32).
+int tc_tri_attention(gb_ctx* c, const TriAttW& w, bool starting, float* p, cudaStream_t st) {
+  TcState* s = static_cast<TcState*>(c->tc_state);
+  const int B = c->B, N = c->N, Np = s->Np;
+  if (c->shard_world > 1) return gb_fail(c, GB_ERR_UNSUPPORTED, "triangle attention is not row-sharded");
+  if (!w.tc_Wqkvg || !w.tc_Wo || !c->ta_bias) return gb_fail(c, GB_ERR_INVALID, "tc_tri_attention: weights not packed");
+  const dim3 grid((Np + 127) / 128, N, B);
+  launch_pdl(triatt_proj_tc_kernel, grid, 256, TAP_SMEM, st, (const float*)p, N, Np, (const float*)w.ln_g, (const float*)w.ln_b,
+             (const bf16*)w.tc_Wqkvg, (const float*)w.Wbias, (const float*)w.bg, s->a, s->b, s->x, s->g, c->ta_bias, starting ? 1 : 0);
+  GB_LAUNCH_CHECK(c, "triatt_proj_tc");
+  launch_pdl(triatt_core_tc_kernel, grid, 256, TAC_SMEM, st, (const bf16*)s->a, (const bf16*)s->b, (const bf16*)s->x, (const bf16*)s->g,
+             (const float*)c->ta_bias, (const int*)c->mask, (const bf16*)w.tc_Wo, (const float*)w.bo, p, N, Np, starting ? 1 : 0);
+  GB_LAUNCH_CHECK(c, "triatt_core_tc");
+  return GB_OK;
+}

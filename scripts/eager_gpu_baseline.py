@@ -1,28 +1,53 @@
-"""Reference-style PyTorch eager on the B200 ("the reference on the B200 via PyTorch eager CUDA ... the number
-to beat"): the oracle port (a line-by-line restatement of the reference's fp32 eager modules, chunked pair transition
-included) run with its tensors on cuda:0.  The reference itself cannot travel to the GPU box (it lives in /root/reference
-and needs pytorch_lightning).  Not part of bench.py; prints one JSON line.  usage: eager_gpu_baseline.py [B N steps]"""
+"""The UNMODIFIED reference on the B200 through PyTorch eager ("the reference on the B200 via PyTorch eager
+CUDA ... the number to beat"): baseline/_ref (oracle/install_reference.py) with its Genie module moved to cuda:0, timed
+through its own UnconditionalSampler._sample with the schedule shortened to the timed step count -- 2 L B host
+synchronisations per step in compute_frenet_frames (utils/geo_utils.py:63-83) and the 256-chunk launch storm of the pair
+transition (modules/pair_transition.py:77-83) included.  Falls back to the oracle port (un-chunked, closed-form quaternion:
+faster than the reference) when baseline/_ref is absent.  Not part of bench.py; prints one JSON line.
+usage: eager_gpu_baseline.py [B N steps]"""
 import json
 import os
 import sys
+import tempfile
 import time
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 import torch
-from oracle import genie_oracle as O, weights as W
+from oracle import genie_oracle as O, weights as W, reference_bridge as R
 
 
 def main():
     B, N, K = (int(sys.argv[1]), int(sys.argv[2]), int(sys.argv[3])) if len(sys.argv) > 3 else (4, 256, 5)
     dev = torch.device('cuda', 0)
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.backends.cudnn.allow_tf32 = False
+    sd = W.make_state_dict(O.OracleConfig(), 0, 'activated')
+    if R.installed_available():
+        params = {'length': N, 'scale': 0.6, 'num_samples': B, 'outdir': tempfile.gettempdir(), 'prefix': 'ref', 'offset': 0}
+
+        def run(n):
+            genie, sampler = R.load_installed_sampler(n, sd, dev)
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            with torch.no_grad():
+                out = sampler._sample(params)
+            torch.cuda.synchronize()
+            return time.perf_counter() - t0, out
+
+        run(2)
+        dt, out = run(K)
+        fin = all(bool(torch.isfinite(torch.as_tensor(o['atom_positions'])).all()) for o in out)
+        print(json.dumps({'what': 'unmodified reference (baseline/_ref), PyTorch eager fp32 on cuda:0 (TF32 off), UnconditionalSampler._sample',
+                          'B': B, 'N': N, 'steps': K, 'ms_per_step': dt / K * 1e3, 'evals_per_s': K / dt, 'finite': fin}))
+        return
     cfg = O.OracleConfig()
-    sd = {k: v.to(dev) for k, v in W.make_state_dict(cfg, 0, 'activated').items()}
+    sd = {k: v.to(dev) for k, v in sd.items()}
     feats = {k: v.to(dev) for k, v in O.make_features([[N]] * B).items()}
     sched = O.setup_schedule(1000)
     if isinstance(sched, dict):
         sched = {k: (v.to(dev) if torch.is_tensor(v) else v) for k, v in sched.items()}
-    torch.set_default_device(dev)          # tensors the oracle creates on the fly (encodings, index ranges) land on the GPU
+    torch.set_default_device(dev)
     x = torch.randn(B, N, 3, device=dev)
 
     def step(x, t):
@@ -40,8 +65,8 @@ def main():
             x = step(x, 999 - i)
         torch.cuda.synchronize()
         dt = (time.perf_counter() - t0) / K
-    print(json.dumps({'what': 'oracle port, PyTorch eager fp32 on cuda:0 (TF32 off)', 'B': B, 'N': N, 'steps': K, 'ms_per_step': dt * 1e3,
-                      'evals_per_s': 1.0 / dt, 'finite': bool(torch.isfinite(x).all())}))
+    print(json.dumps({'what': 'oracle port (no chunking, closed-form quaternion), PyTorch eager fp32 on cuda:0 (TF32 off)', 'B': B, 'N': N, 'steps': K,
+                      'ms_per_step': dt * 1e3, 'evals_per_s': 1.0 / dt, 'finite': bool(torch.isfinite(x).all())}))
 
 
 if __name__ == '__main__':
