@@ -464,18 +464,18 @@ int tc_pack_triatt(gb_ctx* c, TriAttW& w, const std::vector<float>& wq, const st
   return GB_OK;
 }
 
-// p += TriangleAttention(p) on tensor cores.  Q / K / V^T / gate live in the a / b / x / g planes of the pair workspace
-// (the triangle updates have finished with them), the triangle bias in c->ta_bias ([B][4][N][Np] fp32).
+// p += TriangleAttention(p) on tensor cores.  Q / K / V^T / gate live in planes of their own (TcState::ta_*), the
+// triangle bias in c->ta_bias ([B][4][N][Np] fp32).
 int tc_tri_attention(gb_ctx* c, const TriAttW& w, bool starting, float* p, cudaStream_t st) {
   TcState* s = static_cast<TcState*>(c->tc_state);
   const int B = c->B, N = c->N, Np = s->Np;
   if (c->shard_world > 1) return gb_fail(c, GB_ERR_UNSUPPORTED, "triangle attention is not row-sharded");
-  if (!w.tc_Wqkvg || !w.tc_Wo || !c->ta_bias) return gb_fail(c, GB_ERR_INVALID, "tc_tri_attention: weights not packed");
+  if (!w.tc_Wqkvg || !w.tc_Wo || !c->ta_bias || !s->ta_q) return gb_fail(c, GB_ERR_INVALID, "tc_tri_attention: weights not packed / workspace not bound");
   const dim3 grid((Np + 127) / 128, N, B);
   launch_pdl(triatt_proj_tc_kernel, grid, 256, TAP_SMEM, st, (const float*)p, N, Np, (const float*)w.ln_g, (const float*)w.ln_b,
-             (const bf16*)w.tc_Wqkvg, (const float*)w.Wbias, (const float*)w.bg, s->a, s->b, s->x, s->g, c->ta_bias, starting ? 1 : 0);
+             (const bf16*)w.tc_Wqkvg, (const float*)w.Wbias, (const float*)w.bg, s->ta_q, s->ta_k, s->ta_vt, s->ta_g, c->ta_bias, starting ? 1 : 0);
   GB_LAUNCH_CHECK(c, "triatt_proj_tc");
-  launch_pdl(triatt_core_tc_kernel, grid, 256, TAC_SMEM, st, (const bf16*)s->a, (const bf16*)s->b, (const bf16*)s->x, (const bf16*)s->g,
+  launch_pdl(triatt_core_tc_kernel, grid, 256, TAC_SMEM, st, (const bf16*)s->ta_q, (const bf16*)s->ta_k, (const bf16*)s->ta_vt, (const bf16*)s->ta_g,
              (const float*)c->ta_bias, (const int*)c->mask, (const bf16*)w.tc_Wo, (const float*)w.bo, p, N, Np, starting ? 1 : 0);
   GB_LAUNCH_CHECK(c, "triatt_core_tc");
   return GB_OK;
