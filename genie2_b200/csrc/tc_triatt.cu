@@ -10,7 +10,7 @@
 //                             D_q [px][ch] | D_k [px][ch] | D_g [px][ch] | D_vT [ch][px] = W_v X^T (so V lands key-contiguous)
 //                           outputs: Q, K row images [b][i][2 kb][Np rows][64] (1/sqrt(32) folded into W_q), V^T images
 //                           [b][i][Np/64][128 ch][64 keys], gate sigmoid(.) bf16 [b][i][j][128], and the triangle bias
-//                           b_jk = linear(x_jk) [b][4][j][Np] in fp32 on CUDA cores from the normalised row (4 dot products).
+//                           b_jk = linear(x_jk) [b][4][Np/4][j][4] in fp32 on CUDA cores from the normalised row (4 dot products).
 //   triatt_core_tc_kernel   one CTA = 128 queries j of one row (b, i), all four heads, keys in blocks of 256:
 //                             S = Q_h K_h^T            SS MMA, M = 128, N <= 256, K = 32 (two k steps inside a 64-wide image)
 //                             softmax                  256 threads: thread = (query row, half of the keys); bias and mask
@@ -145,7 +145,9 @@ __global__ void __launch_bounds__(256, 1) triatt_proj_tc_kernel(
   // triangle bias rows (coalesced over the positions of the tile)
   for (int e = tid; e < TA_HEADS * 128; e += 256) {
     const int h = e >> 7, m = e & 127, j = jt * 128 + m;
-    if (j < Np) tb[(((size_t)b * TA_HEADS + h) * N + i) * Np + j] = tbs[e];
+    // layout [b][h][Np / 4 key quads][N query rows][4]: the core's threads (lane = query row) read one 16-byte quad each,
+    // 512 contiguous bytes per warp load (a row-major [j][k] layout costs 32 lines per load instruction)
+    if (j < Np) tb[((((size_t)b * TA_HEADS + h) * (Np >> 2) + (j >> 2)) * N + i) * 4 + (j & 3)] = tbs[e];
   }
   mbar_wait(bar_mma, 0);
   tc_fence_after();
@@ -292,14 +294,14 @@ __global__ void __launch_bounds__(256, 1) triatt_core_tc_kernel(
       ++ns;
       tc_fence_after();
       // ---- pass 1: s = q.k + mask bias + triangle bias (the reference's order), written back; row maximum
-      const float* tbr = tb + (((size_t)b * TA_HEADS + h) * N + jc) * Np + k0 + hf * hw;
+      const float* tbr = tb + ((((size_t)b * TA_HEADS + h) * (Np >> 2) + ((k0 + hf * hw) >> 2)) * N + jc) * 4;   // + key quad * 4 N
       float mx = -3.0e38f;
       for (uint32_t c = 0; c < hw; c += 32) {
         uint32_t v[32];
         tmem_ld32(t_lane + T_S + hf * hw + c, v);
         float4 t4[8];
 #pragma unroll
-        for (int e = 0; e < 8; ++e) t4[e] = ld4(tbr + c + 4 * e);
+        for (int e = 0; e < 8; ++e) t4[e] = ld4(tbr + (size_t)((c >> 2) + e) * N * 4);
         tmem_ld_wait();
 #pragma unroll
         for (int e = 0; e < 8; ++e) {
@@ -414,22 +416,43 @@ __global__ void __launch_bounds__(256, 1) triatt_core_tc_kernel(
   mbar_wait(bar_s, ns & 1);
   tc_fence_after();
   {
-    // (the tensor-memory loads are warp-collective: every lane executes them, only the read-modify-write of p is guarded)
-    float* prow = p + ((size_t)b * N * N + (starting ? (size_t)i * N + jc : (size_t)jc * N + i)) * 128 + hf * 64;
+    // D + b_o -> fp32 staging tile in the (now idle) K buffer, 16-byte chunks XOR-swizzled by the row so that the
+    // thread-per-row writer and the warp-per-row reader are both conflict free; then p[pix] += . with one coalesced
+    // 512-byte row per warp instruction (the ending node's rows are N pixels apart, each still 512 contiguous bytes)
+    uint8_t* S = Ks;
 #pragma unroll 1
     for (int c = 0; c < 2; ++c) {
       uint32_t v[32];
       tmem_ld32(t_lane + T_S + hf * 64 + c * 32, v);
       tmem_ld_wait();
-      if (j < N) {
 #pragma unroll
-        for (int e = 0; e < 8; ++e) {
-          float4 r = ld4(prow + c * 32 + 4 * e);
-          const float4 b4 = ld4(bo + hf * 64 + c * 32 + 4 * e);
-          r.x += __uint_as_float(v[4 * e]) + b4.x; r.y += __uint_as_float(v[4 * e + 1]) + b4.y;
-          r.z += __uint_as_float(v[4 * e + 2]) + b4.z; r.w += __uint_as_float(v[4 * e + 3]) + b4.w;
-          st4(prow + c * 32 + 4 * e, r);
+      for (int e = 0; e < 8; ++e) {
+        const float4 b4 = ld4(bo + hf * 64 + c * 32 + 4 * e);
+        const uint32_t chunk = (uint32_t)(hf * 16 + c * 8 + e);
+        *reinterpret_cast<float4*>(S + m * 512u + ((chunk ^ (m & 31u)) << 4)) =
+            make_float4(__uint_as_float(v[4 * e]) + b4.x, __uint_as_float(v[4 * e + 1]) + b4.y, __uint_as_float(v[4 * e + 2]) + b4.z,
+                        __uint_as_float(v[4 * e + 3]) + b4.w);
+      }
+    }
+    __syncthreads();
+    for (int r0 = warp * 16; r0 < warp * 16 + 16; r0 += 4) {
+      float4 pv[4];
+      float* dst[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int jr = qt * 128 + r0 + u;
+        dst[u] = nullptr;
+        if (jr < N) {
+          dst[u] = p + ((size_t)b * N * N + (starting ? (size_t)i * N + jr : (size_t)jr * N + i)) * 128 + lane * 4;
+          pv[u] = ld4(dst[u]);
         }
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        if (!dst[u]) continue;
+        const uint32_t r = (uint32_t)(r0 + u);
+        const float4 d = *reinterpret_cast<const float4*>(S + r * 512u + (((uint32_t)lane ^ (r & 31u)) << 4));
+        st4(dst[u], make_float4(pv[u].x + d.x, pv[u].y + d.y, pv[u].z + d.z, pv[u].w + d.w));
       }
     }
   }
