@@ -1,5 +1,6 @@
 """Summarise an `ncu --metrics gpu__time_duration.sum --csv` launch list: per-kernel count, total
-time and share.  usage: summarize_launches.py launches.csv [skip_first_n_launches]"""
+time and share.  usage: summarize_launches.py launches.csv [skip_first_n_launches | last]
+`last` = the last whole denoiser eval in the list (from the last single_combine_kernel launch to the end)."""
 import csv, sys, collections, re
 rows = []
 with open(sys.argv[1]) as f:
@@ -11,7 +12,10 @@ for r in rd:
         u = r.get('Metric Unit', 'ns')
         v *= {'ns': 1e-3, 'us': 1.0, 'ms': 1e3, 'msecond': 1e3, 'usecond': 1.0, 'nsecond': 1e-3, 'second': 1e6}.get(u, 1e-3)
         rows.append((re.sub(r'\(.*', '', r['Kernel Name']), v))
-skip = int(sys.argv[2]) if len(sys.argv) > 2 else 0
+if len(sys.argv) > 2 and sys.argv[2] == 'last':
+    skip = max(i for i, (k, _) in enumerate(rows) if k.startswith('single_combine_kernel'))
+else:
+    skip = int(sys.argv[2]) if len(sys.argv) > 2 else 0
 rows = rows[skip:]
 agg = collections.OrderedDict()
 for k, v in rows:
