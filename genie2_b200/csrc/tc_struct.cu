@@ -580,6 +580,18 @@ __global__ void __launch_bounds__(IA_THREADS, 1) ipa_attention_tc_kernel(
     }
   }
   if (warp == 2) tmem_alloc(tslot, TCOLS);
+  if (warp == 3 && lane < ng) {
+    // L2 prefetch of what this CTA will stream later, all of it written by ipa_prep several launches back: the z rows of
+    // its queries (2 k-blocks x Np x 128 B per query and component; phase 3 was bound by their HBM latency through the
+    // two-slot ring) and the pair-bias rows (12 x Np floats per query, read in the logits phase)
+    const size_t row = rowb + i0 + lane;
+#pragma unroll
+    for (int c = 0; c < NS; ++c) {
+      const uint8_t* zr = reinterpret_cast<const uint8_t*>(z_img) + (size_t)c * z_lo * 2 + row * 2 * Np * 128;
+      for (uint32_t off = 0; off < 2u * Np * 128u; off += 32768u) l2_prefetch(zr + off, min(32768u, 2u * Np * 128u - off));
+    }
+    l2_prefetch(pbias + row * 12 * Np, 12u * Np * 4u);
+  }
   pdl_wait();          // the z prefetch above reads what ipa_prep wrote (several launches back); q / k / v come from the previous kernel
   // q, q_pts of the G queries; a_img cleared (rows 12..15 and padded keys must read as zero)
   const float sc_qk = sqrtf(1.f / (3.f * IPA_C));
