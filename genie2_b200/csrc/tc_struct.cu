@@ -47,6 +47,9 @@ struct GemmImgArgs {
   int kvsplit;        // > 0: IPA projection scatter, value = N (keys per sample): columns < IPA_QW go to rows [R][IPA_QW],
                       // the rest to key-major planes [B][IPA_NPLANE][N][4] behind them (see ipa_dims.h)
   size_t A_lo, W_lo, O_lo;   // NS > 1 only
+  int ksplit;         // 3: blockIdx.z takes k-blocks [z nkb / 3, (z + 1) nkb / 3) and writes its partial sums to C / C1 / C2
+                      // (no bias / residual / image: the consumer adds the partials in a fixed order)
+  float *C1, *C2;
 };
 
 template <int NS>
@@ -61,6 +64,7 @@ __global__ void __launch_bounds__(256, 1) gemm_img_tc_kernel(const GemmImgArgs g
   uint32_t* tslot = reinterpret_cast<uint32_t*>(done + 1);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const uint32_t n0 = blockIdx.x * 64u, m0 = (g.mblk0 + blockIdx.y) * 128u;
+  const int nkb = g.ksplit > 1 ? g.nkb / g.ksplit : g.nkb, kb0 = g.ksplit > 1 ? (int)blockIdx.z * nkb : 0;   // this CTA's k-blocks
   if (tid == 0) {
     for (int s = 0; s < GI_STAGES; ++s) { mbar_init(full + s, 1); mbar_init(empty + s, 1); }
     mbar_init(done, 1);
@@ -74,26 +78,26 @@ __global__ void __launch_bounds__(256, 1) gemm_img_tc_kernel(const GemmImgArgs g
   if (warp == 0) {
     if (lane == 0) {
       // the weight halves of the first ring of stages do not depend on the previous kernel: in flight before pdl_wait
-      const int npre = g.nkb < GI_STAGES ? g.nkb : GI_STAGES;
+      const int npre = nkb < GI_STAGES ? nkb : GI_STAGES;
       for (int kb = 0; kb < npre; ++kb) {
         mbar_expect_tx(full + kb, STAGE);
-        const bf16* wsrc = g.W + ((size_t)kb * g.Nw + n0) * 64;
+        const bf16* wsrc = g.W + ((size_t)(kb0 + kb) * g.Nw + n0) * 64;
 #pragma unroll
         for (int c = 0; c < NS; ++c) bulk_g2s(sm + kb * STAGE + c * GI_STAGE_BYTES + 16384, wsrc + c * g.W_lo, 8192, full + kb);
       }
       pdl_wait();
       pdl_launch();
-      for (int kb = 0; kb < g.nkb; ++kb) {
+      for (int kb = 0; kb < nkb; ++kb) {
         const int s = kb % GI_STAGES;
         uint8_t* st = sm + s * STAGE;
         if (kb >= GI_STAGES) {
           mbar_wait(empty + s, ((kb / GI_STAGES) - 1) & 1);
           mbar_expect_tx(full + s, STAGE);
-          const bf16* wsrc = g.W + ((size_t)kb * g.Nw + n0) * 64;
+          const bf16* wsrc = g.W + ((size_t)(kb0 + kb) * g.Nw + n0) * 64;
 #pragma unroll
           for (int c = 0; c < NS; ++c) bulk_g2s(st + c * GI_STAGE_BYTES + 16384, wsrc + c * g.W_lo, 8192, full + s);
         }
-        const bf16* asrc = g.A + ((size_t)kb * g.Rp + m0) * 64;
+        const bf16* asrc = g.A + ((size_t)(kb0 + kb) * g.Rp + m0) * 64;
 #pragma unroll
         for (int c = 0; c < NS; ++c) bulk_g2s(st + c * GI_STAGE_BYTES, asrc + c * g.A_lo, 16384, full + s);
       }
@@ -101,7 +105,7 @@ __global__ void __launch_bounds__(256, 1) gemm_img_tc_kernel(const GemmImgArgs g
     __syncwarp();
   } else if (warp == 1) {
     const uint32_t idesc = umma_idesc(128, 64), tm = warp_uniform(tmem);
-    for (int kb = 0; kb < g.nkb; ++kb) {
+    for (int kb = 0; kb < nkb; ++kb) {
       const int s = kb % GI_STAGES;
       mbar_wait(full + s, (kb / GI_STAGES) & 1);
       tc_fence_after();
@@ -114,7 +118,7 @@ __global__ void __launch_bounds__(256, 1) gemm_img_tc_kernel(const GemmImgArgs g
             umma(tm, umma_desc(sa + SplitPasses<NS>::a(ps) * GI_STAGE_BYTES + k * 32), umma_desc(sb + SplitPasses<NS>::b(ps) * GI_STAGE_BYTES + k * 32),
                  idesc, (kb | k | ps) ? 1u : 0u);
         umma_commit(empty + s);
-        if (kb == g.nkb - 1) umma_commit(done);
+        if (kb == nkb - 1) umma_commit(done);
       }
       __syncwarp();
     }
@@ -151,7 +155,8 @@ __global__ void __launch_bounds__(256, 1) gemm_img_tc_kernel(const GemmImgArgs g
         *reinterpret_cast<float4*>(dst) = make_float4(o[4 * e], o[4 * e + 1], o[4 * e + 2], o[4 * e + 3]);
       }
     } else if (g.C) {
-      float4* c4 = reinterpret_cast<float4*>(g.C + (size_t)m * g.ldc + c0);
+      float* cbase = g.ksplit > 1 && blockIdx.z == 1 ? g.C1 : g.ksplit > 1 && blockIdx.z == 2 ? g.C2 : g.C;
+      float4* c4 = reinterpret_cast<float4*>(cbase + (size_t)m * g.ldc + c0);
 #pragma unroll
       for (int e = 0; e < 8; ++e) c4[e] = make_float4(o[4 * e], o[4 * e + 1], o[4 * e + 2], o[4 * e + 3]);
     }
@@ -183,7 +188,9 @@ __global__ void ln_img_kernel(const float* __restrict__ in, float* __restrict__ 
                               bf16* __restrict__ img, const float* __restrict__ gamma, const float* __restrict__ beta,
                               int R, int C, int Rp, int normalize, const float* __restrict__ Wbb,
                               const float* __restrict__ bbb, float* __restrict__ rots,
-                              float* __restrict__ trans, size_t img_lo, int ns /* split components of the image, img_lo elements apart */) {
+                              float* __restrict__ trans, size_t img_lo, int ns /* split components of the image, img_lo elements apart */,
+                              const float* __restrict__ in2, const float* __restrict__ in3 /* split-K partial sums, or null */,
+                              const float* __restrict__ addb /*[C] bias*/, const float* __restrict__ addr /*[R][C] residual*/) {
   const int row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   pdl_wait();
   pdl_launch();
@@ -194,6 +201,12 @@ __global__ void ln_img_kernel(const float* __restrict__ in, float* __restrict__ 
 #pragma unroll
   for (int q = 0; q < 4; ++q) {
     v[q] = q < nq ? ld4(in + (size_t)row * C + (q * 32 + lane) * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
+    if (in2 && q < nq) {      // the input is a split-K GEMM: (((p0 + p1) + p2) + bias) + residual, always in this order
+      const size_t o = (size_t)row * C + (q * 32 + lane) * 4;
+      const float4 a = ld4(in2 + o), bq = ld4(in3 + o), bi = ld4(addb + (q * 32 + lane) * 4), re = ld4(addr + o);
+      v[q].x = (((v[q].x + a.x) + bq.x) + bi.x) + re.x; v[q].y = (((v[q].y + a.y) + bq.y) + bi.y) + re.y;
+      v[q].z = (((v[q].z + a.z) + bq.z) + bi.z) + re.z; v[q].w = (((v[q].w + a.w) + bq.w) + bi.w) + re.w;
+    }
     sum += v[q].x + v[q].y + v[q].z + v[q].w;
   }
   if (normalize) {
@@ -969,7 +982,8 @@ int tc_pack_ipa_bias(gb_ctx* c, const std::vector<const std::vector<float>*>& wb
 
 // x3: A / O are images with their lo twins `img_lo` elements behind, W is hi | lo images of K * Nw elements each
 static int gemm_img(gb_ctx* c, cudaStream_t st, const bf16* A, int K, const bf16* W, int Nw, const float* bias, const float* res,
-                    int ldr, float* C, int ldc, bf16* O, bool relu, int kvsplit = 0, int mblk0 = 0, int nmblk = 0, bool x3 = false) {
+                    int ldr, float* C, int ldc, bf16* O, bool relu, int kvsplit = 0, int mblk0 = 0, int nmblk = 0, bool x3 = false,
+                    int ksplit = 1, float* C1 = nullptr, float* C2 = nullptr) {
   TcState* s = static_cast<TcState*>(c->tc_state);
   GemmImgArgs g;
   g.mblk0 = mblk0;
@@ -977,7 +991,9 @@ static int gemm_img(gb_ctx* c, cudaStream_t st, const bf16* A, int K, const bf16
   g.Rp = s->Rp; g.Nw = Nw; g.nkb = K / 64; g.R = c->B * c->N; g.ldc = ldc; g.ldr = ldr; g.relu = relu ? 1 : 0; g.kvsplit = kvsplit;
   g.A_lo = g.O_lo = s->img_lo;
   g.W_lo = (size_t)K * Nw;
-  const dim3 grid(Nw / 64, nmblk ? nmblk : s->Rp / 128);
+  g.ksplit = ksplit; g.C1 = C1; g.C2 = C2;
+  if (ksplit > 1 && (ksplit != 3 || !C1 || !C2 || bias || res || O || kvsplit || (K / 64) % 3)) return gb_fail(c, GB_ERR_INVALID, "gemm_img: bad split-K request");
+  const dim3 grid(Nw / 64, nmblk ? nmblk : s->Rp / 128, ksplit);
   if (x3) launch_pdl(gemm_img_tc_kernel<2>, grid, 256, GI<2>::SMEM, st, g);
   else launch_pdl(gemm_img_tc_kernel<1>, grid, 256, GI<1>::SMEM, st, g);
   GB_LAUNCH_CHECK(c, "gemm_img_tc");
@@ -1022,12 +1038,13 @@ int tc_pair_pipj(gb_ctx* c, cudaStream_t st) {
 }
 
 static void launch_ln(gb_ctx* c, cudaStream_t st, const float* in, float* out, float* out2, bf16* img, const float* gamma, const float* beta,
-                      int normalize, const StructLayerW* bb, bool x3) {
+                      int normalize, const StructLayerW* bb, bool x3, const float* in2 = nullptr, const float* in3 = nullptr,
+                      const float* addb = nullptr, const float* addr = nullptr) {
   TcState* s = static_cast<TcState*>(c->tc_state);
   const int R = c->B * c->N;
   launch_pdl(ln_img_kernel, (unsigned)((R * 32 + 255) / 256), 256, 0, st, in, out, out2, img, gamma, beta, R, c->d.c_s, s->Rp, normalize,
              bb ? (const float*)bb->Wbb : (const float*)nullptr, bb ? (const float*)bb->bbb : (const float*)nullptr,
-             bb ? c->rots_w : (float*)nullptr, bb ? c->trans_w : (float*)nullptr, s->img_lo, x3 ? 2 : 1);
+             bb ? c->rots_w : (float*)nullptr, bb ? c->trans_w : (float*)nullptr, s->img_lo, x3 ? 2 : 1, in2, in3, addb, addr);
 }
 
 // StructureNet.forward (structure_net.py:189-243) on c->s / c->p / c->rots_w / c->trans_w, tensor-core modes.
@@ -1082,7 +1099,16 @@ int tc_structure_net(gb_ctx* c, float* states_out, cudaStream_t st) {
       if (W > 1) {
         if ((rc = gemm_img(c, st, s->cat_img, IPA_CAT, t.Wout, cs, w.bout, c->s, cs, c->sA, cs, nullptr, false, 0, row0 / 128, rows / 128))) return rc;
         if ((rc = shard_all_gather(c, c->sA, (size_t)rows * cs * sizeof(float), st))) return rc;
-      } else if ((rc = gemm_img(c, st, s->cat_img, IPA_CAT, t.Wout, cs, w.bout, c->s, cs, c->sA, cs, nullptr, false, 0, 0, 0, x3))) return rc;
+      }
+      // output projection, K = 2112 = 33 k-blocks: split three ways over grid.z (144 CTAs instead of 48, a third of the serial
+      // MMA chain each; also a third of the accumulation length inside the tensor core); the partial sums land in sA / h1 / h2
+      // and the LayerNorm kernel adds them, the bias and the residual in a fixed order
+      const bool ks3 = W == 1 && (IPA_CAT / 64) % 3 == 0;
+      if (W == 1 && !ks3 && (rc = gemm_img(c, st, s->cat_img, IPA_CAT, t.Wout, cs, w.bout, c->s, cs, c->sA, cs, nullptr, false, 0, 0, 0, x3))) return rc;
+      if (ks3) {
+        if ((rc = gemm_img(c, st, s->cat_img, IPA_CAT, t.Wout, cs, nullptr, nullptr, 0, c->sA, cs, nullptr, false, 0, 0, 0, x3, 3, c->h1, c->h2))) return rc;
+        launch_ln(c, st, c->sA, c->sB, nullptr, s->ln1_img, w.ln1_g, w.ln1_b, 1, nullptr, x3, c->h1, c->h2, w.bout, c->s);
+      } else
       launch_ln(c, st, c->sA, c->sB, nullptr, s->ln1_img, w.ln1_g, w.ln1_b, 1, nullptr, x3);
       GB_LAUNCH_CHECK(c, "ipa_layer_norm");
       float* cur = c->sB;
