@@ -647,6 +647,10 @@ __global__ void __launch_bounds__(IA_THREADS, 1) ipa_attention_tc_kernel(
 #pragma unroll
         for (int g = 0; g < G; ++g) out[g] = -3.0e38f;
         if (kv) {
+          // the G pair-bias words of this (head, key) first, all in flight together
+          float pbv[G];
+#pragma unroll
+          for (int g = 0; g < G; ++g) pbv[g] = g < ng ? __ldg(pbias + ((rowb + i0 + g) * 12 + h) * Np + j) : 0.f;
           // packed fp32x2 arithmetic: kk[0..7] = k (two components per register pair), kk[8..13] = -k_pts
           float2 kk[14];
 #pragma unroll
@@ -673,8 +677,7 @@ __global__ void __launch_bounds__(IA_THREADS, 1) ipa_attention_tc_kernel(
               d2 = __ffma2_rn(da, da, d2);
               d2 = __ffma2_rn(db, db, d2);
             }
-            float pb = 0.f;
-            if (g < ng) pb = pbias[((rowb + i0 + g) * 12 + h) * Np + j];
+            const float pb = pbv[g];
             // the reference's order (invariant_point_attention.py:181-212): q.k, + pair bias, + point term, + mask term LAST
             out[g] = (((qk.x + qk.y) + pb) + gam * (d2.x + d2.y)) + 1e5f * (mq[g] * mk - 1.f);
           }
