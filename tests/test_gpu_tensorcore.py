@@ -128,7 +128,7 @@ def test_forward_bf16_vs_oracle_and_fp32_path():
 
 
 def test_forward_bf16_with_triangle_attention_fixture():
-    """include_tri_att configuration in bf16 mode (K8 itself stays fp32) against the reference fixture."""
+    """include_tri_att configuration in bf16 mode (K8 on tensor cores, csrc/tc_triatt.cu) against the reference fixture."""
     from common import load_forward_case
     cfg, sd, feats, t = load_forward_case('triatt')
     model = make_denoiser(cfg, sd, precision='bf16')
