@@ -609,8 +609,9 @@ static int check_ready(gb_ctx* c, const char* who) {
   return GB_OK;
 }
 
+static int x3diag() { static const int v = [] { const char* e = getenv("GB_X3_DIAG"); return e ? atoi(e) : 0; }(); return v; }
 static int run_trimul(gb_ctx* c, const TriMulW& w, bool outgoing, float* p, cudaStream_t st) {
-  if (c->precision != GB_PREC_FP32) return tc_trimul(c, w, outgoing, p, st);
+  if (c->precision != GB_PREC_FP32 && !((x3diag() & 2) && c->precision == GB_PREC_BF16X3)) return tc_trimul(c, w, outgoing, p, st);
   const int B = c->B, N = c->N;
   const size_t M = (size_t)B * N * N;
   const unsigned tiles = (unsigned)((M + 127) / 128);
@@ -648,7 +649,7 @@ static int run_triatt(gb_ctx* c, const TriAttW& w, bool starting, float* p, cuda
 }
 
 static int run_transition(gb_ctx* c, const TransitionW& w, float* p, cudaStream_t st) {
-  if (c->precision != GB_PREC_FP32) return tc_pair_transition(c, w, p, st);
+  if (c->precision != GB_PREC_FP32 && !((x3diag() & 4) && c->precision == GB_PREC_BF16X3)) return tc_pair_transition(c, w, p, st);
   const size_t M = (size_t)c->B * c->N * c->N;
   const unsigned tiles = (unsigned)((M + 127) / 128);
   pair_transition_simt_kernel<<<tiles, 256, kSmemTrans, st>>>(p, M, c->N, c->mask, w.ln_g, w.ln_b, w.W1T, w.b1, w.W2T, w.b2,
@@ -781,7 +782,7 @@ extern "C" int gb_denoise(gb_ctx* c, const float* rots, const float* trans, cons
   // StructureNet
   float* s = c->s;
   int state_idx = 1;
-  if (tcmode) {
+  if (tcmode && !((x3diag() & 1) && c->precision == GB_PREC_BF16X3)) {
     if ((rc = tc_structure_net(c, aux ? aux->states : nullptr, st))) return rc;
   } else
   for (int blk = 0; blk < d.n_structure_block; ++blk)

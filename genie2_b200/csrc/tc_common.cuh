@@ -263,12 +263,15 @@ __device__ __forceinline__ void split_bf16x2_n(float a, float b, uint32_t (&c)[N
     b -= __uint_as_float(c[i] & 0xffff0000u);
   }
 }
-// operand components (A, B) of pass i of an NS-way split product, largest terms first.  A third component was tried for the
-// structure net (six passes) and bought nothing: the fp32 accumulation of tcgen05.mma itself leaves ~1e-5 on a K = 2112
-// product, above the 2^-17 of the hi | lo operands.
+// operand components (A, B) of pass i of an NS-way split product, largest terms first.  The structure-net kernels that use
+// this table (gemm_img, ipa_prep, ipa_attention) also run the lo x lo pass: they are latency-bound, the pass is nearly free
+// (+38 us per eval) and, with the accumulation chains cut short (GI<2>::NACC), it took the 1000-step trajectory from 0.128 to
+// 0.10 A.  The pair-stack kernels (K4 - K7) keep three passes: a fourth there cost 120 us and did not help the trajectory.
+// A third component (six passes) was tried in round 1 and bought nothing while the fp32 accumulation of tcgen05.mma itself
+// left ~1e-5 on a K = 2112 product.
 template <int NS> struct SplitPasses;
 template <> struct SplitPasses<1> { static constexpr int N = 1; __device__ static constexpr int a(int) { return 0; } __device__ static constexpr int b(int) { return 0; } };
-template <> struct SplitPasses<2> { static constexpr int N = 3; __device__ static constexpr int a(int i) { return i == 1 ? 1 : 0; } __device__ static constexpr int b(int i) { return i == 2 ? 1 : 0; } };
+template <> struct SplitPasses<2> { static constexpr int N = 4; __device__ static constexpr int a(int i) { return (i == 1 || i == 3) ? 1 : 0; } __device__ static constexpr int b(int i) { return (i == 2 || i == 3) ? 1 : 0; } };
 __device__ __forceinline__ float2 unpack_bf16x2(uint32_t v) { return make_float2(__uint_as_float(v << 16), __uint_as_float(v & 0xffff0000u)); }
 // sigmoid to ~1e-6 relative (ex2.approx + rcp.approx): the split mode cannot use the 2^-11 tanh.approx of the bf16 mode
 __device__ __forceinline__ float sigmoid_acc(float x) { return __fdividef(1.f, 1.f + __expf(-x)); }

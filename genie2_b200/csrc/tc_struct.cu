@@ -30,6 +30,11 @@ using namespace tc;
 // elements behind component c - 1; a stage holds NS x [A_c 16K | W_c 8K] and every k step issues the passes of SplitPasses.
 #define GI_STAGE_BYTES (16384 + 8192)
 template <int NS> struct GI {
+  // GB_PREC_BF16X3: the k-blocks are spread round robin over NACC tensor-memory accumulators that the epilogue adds in fp32
+  // (round to nearest).  tcgen05.mma adds into its fp32 accumulator without rounding to nearest, so a long chain drifts
+  // (1e-5 relative on K = 2112, above the 2^-17 of the hi | lo operands); short chains + an IEEE sum keep the split mode's
+  // accuracy where its operands put it.
+  static constexpr int NACC = NS == 1 ? 1 : 4;
   static constexpr int STAGES = NS == 1 ? 8 : 4;
   static constexpr uint32_t STAGE = NS * GI_STAGE_BYTES;
   static constexpr uint32_t SMEM = STAGES * STAGE + 1024 + 256;
@@ -70,7 +75,8 @@ __global__ void __launch_bounds__(256, 1) gemm_img_tc_kernel(const GemmImgArgs g
     mbar_init(done, 1);
     fence_mbar_init();
   }
-  if (warp == 2) tmem_alloc(tslot, 64);
+  constexpr int NACC = GI<NS>::NACC;
+  if (warp == 2) tmem_alloc(tslot, 64 * NACC);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -115,8 +121,8 @@ __global__ void __launch_bounds__(256, 1) gemm_img_tc_kernel(const GemmImgArgs g
         for (int k = 0; k < 4; ++k)
 #pragma unroll
           for (int ps = 0; ps < SplitPasses<NS>::N; ++ps)
-            umma(tm, umma_desc(sa + SplitPasses<NS>::a(ps) * GI_STAGE_BYTES + k * 32), umma_desc(sb + SplitPasses<NS>::b(ps) * GI_STAGE_BYTES + k * 32),
-                 idesc, (kb | k | ps) ? 1u : 0u);
+            umma(tm + (uint32_t)(kb % NACC) * 64u, umma_desc(sa + SplitPasses<NS>::a(ps) * GI_STAGE_BYTES + k * 32),
+                 umma_desc(sb + SplitPasses<NS>::b(ps) * GI_STAGE_BYTES + k * 32), idesc, ((kb / NACC) | k | ps) ? 1u : 0u);
         umma_commit(empty + s);
         if (kb == nkb - 1) umma_commit(done);
       }
@@ -131,6 +137,16 @@ __global__ void __launch_bounds__(256, 1) gemm_img_tc_kernel(const GemmImgArgs g
   uint32_t v[32];
   tmem_ld32(tmem + ((q * 32u) << 16) + h * 32, v);
   tmem_ld_wait();
+#pragma unroll
+  for (int a = 1; a < NACC; ++a) {
+    if (a < nkb) {                       // (warp-uniform) accumulators no k-block went to hold nothing
+      uint32_t w[32];
+      tmem_ld32(tmem + ((q * 32u) << 16) + a * 64 + h * 32, w);
+      tmem_ld_wait();
+#pragma unroll
+      for (int e = 0; e < 32; ++e) v[e] = __float_as_uint(__uint_as_float(v[e]) + __uint_as_float(w[e]));
+    }
+  }
   if (m < (uint32_t)g.R) {
     float o[32];
 #pragma unroll
@@ -177,7 +193,7 @@ __global__ void __launch_bounds__(256, 1) gemm_img_tc_kernel(const GemmImgArgs g
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 2) tmem_dealloc(tmem, 64);
+  if (warp == 2) tmem_dealloc(tmem, 64 * NACC);
 }
 
 // ---------------------------------------------------------------------------------------------
