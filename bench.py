@@ -421,12 +421,16 @@ def run_b200(args):
     m2 = measure(other) if not args.single_mode else None
     genie.model.set_precision(prec)
     # ---- blocks of the other multi-GPU configurations, measured after the contract's timed region; every rank takes part
-    sweep = c5 = None
+    sweep = c5 = scaf = None
     if not args.no_extra_blocks:
         try:
             sweep = measure_length_sweep(genie, dev, world, rank, barrier, args.sweep_steps, prec)
         except Exception as e:      # never lose the contract line to an extra block
             sweep = {'error': '%s: %s' % (type(e).__name__, e)}
+        try:
+            scaf = measure_scaffold(genie, dev, rank, barrier, 50, prec)
+        except Exception as e:
+            scaf = {'error': '%s: %s' % (type(e).__name__, e)}
         genie.model.set_precision(prec)
         ctx = genie.model.bind_features(feats, dev)      # the sweep re-bound the context to its own batches
         genie.bind_schedule(ctx)
@@ -469,6 +473,8 @@ def run_b200(args):
     }
     if sweep is not None:
         line['length_sweep'] = sweep
+    if scaf is not None:
+        line['scaffold'] = scaf
     if c5 is not None:
         line['c5'] = c5
     if m2 is not None:
@@ -617,6 +623,48 @@ def run_c5(args):
         print(json.dumps(out), flush=True)
     if world > 1:
         dist.destroy_process_group()
+
+
+def measure_scaffold(genie, dev, rank, barrier, steps, prec):
+    """BASELINE configs[3]: motif scaffolding with motif pair conditioning, batch 8, scale 0.4 (sample_scaffold.py,
+    sampler/scaffold.py:12-168).  The design25 problem files are not in the reference snapshot, so the problem is the
+    synthetic two-group one of tests/golden/io_problem.pdb (its parsing and seeded placement are pinned to the reference by
+    tests/test_host_io_golden.py); the ragged batch of 8 placements is built by the package's own host path.  Every rank
+    runs its own batch (no collective); rank 0 reports."""
+    import torch
+    import genie2_b200
+    from genie2_b200 import _lib, feat_utils as F
+    prob = os.path.join(ROOT, 'tests', 'golden', 'io_problem.pdb')
+    if not os.path.exists(prob):
+        return {'unavailable': 'tests/golden/io_problem.pdb missing'}
+    lib = _lib.load()
+    genie.model.set_precision(prec)
+    np.random.seed(5 + rank)
+    feats = F.convert_np_features_to_tensor(F.batchify_np_features([F.create_np_features_from_motif_pdb(prob) for _ in range(8)]), dev)
+    nb, n = feats['residue_mask'].shape
+    ctx = genie.model.bind_features(feats, dev)
+    genie.bind_schedule(ctx)
+    x = torch.randn(nb, n, 3, device=dev) * feats['residue_mask'].unsqueeze(-1)
+    rots = genie2_b200.compute_frenet_frames(genie.model, feats, x)
+    stream = torch.cuda.current_stream(dev).cuda_stream
+
+    def loop(t, k):
+        _lib.check(lib.gb_sample_loop(ctx, x.data_ptr(), rots.data_ptr(), t, t - k + 1, 0.4, None, 31 + rank, stream), ctx, 'gb_sample_loop')
+    loop(T_STEPS, 5)
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    loop(T_STEPS - 5, steps)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / steps
+    barrier()
+    if rank != 0:
+        return None
+    lens = [int(v) for v in feats['num_residues'].reshape(-1).tolist()] if 'num_residues' in feats else []
+    return {'workload': 'motif scaffolding, synthetic two-group problem, batch 8 (BASELINE configs[3]), scale 0.4', 'precision': prec, 'batch': nb,
+            'padded_length': n, 'lengths': lens, 'steps': steps, 'ms_per_step': ms, 'evals_per_s_per_gpu': 1e3 / ms,
+            'seconds_per_1000_step_batch': ms, 'finite': bool(torch.isfinite(x).all()), 'motif_pair_conditioning': bool(feats['fixed_structure_mask'].any())}
 
 
 def measure_length_sweep(genie, dev, world, rank, barrier, steps, prec):
