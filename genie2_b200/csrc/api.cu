@@ -626,10 +626,10 @@ static int run_trimul(gb_ctx* c, const TriMulW& w, bool outgoing, float* p, cuda
   return GB_OK;
 }
 
-// K8: p += TriangleAttention(p) (pair_transform_net.py:109-119).  GB_PREC_BF16: tcgen05 kernels (tc_triatt.cu).  fp32 and
-// bf16x3: the fp32 CUDA-core kernels below (a three-pass split attention is not built; the fp32 path keeps the 1e-3 gate).
+// K8: p += TriangleAttention(p) (pair_transform_net.py:109-119).  bf16 and bf16x3: tcgen05 kernels (tc_triatt.cu, the latter
+// with split hi | lo operands and three passes per product); fp32: the CUDA-core kernels below.
 static int run_triatt(gb_ctx* c, const TriAttW& w, bool starting, float* p, cudaStream_t st) {
-  if (c->precision == GB_PREC_BF16) return tc_tri_attention(c, w, starting, p, st);
+  if (c->precision != GB_PREC_FP32) return tc_tri_attention(c, w, starting, p, st);
   const int B = c->B, N = c->N;
   const size_t M = (size_t)B * N * N;
   if (M > (size_t)INT32_MAX) return gb_fail(c, GB_ERR_UNSUPPORTED, "triangle attention: B*N*N too large");

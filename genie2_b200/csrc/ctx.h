@@ -34,6 +34,7 @@ struct TransitionW {
 struct TriAttW {
   float *ln_g, *ln_b, *Wbias /*[H][128]*/, *Wqkvg /*[4*H*C][128]: q|k|v|g*/, *bg, *Wo /*[128][H*C]*/, *bo, *bqkvg /*[4*H*C]: 0|0|0|bg*/;
   void *tc_Wqkvg = nullptr, *tc_Wo = nullptr;   // bf16 operand images of the tensor-core kernels (tc_triatt.cu)
+  void *x3_Wqkvg = nullptr, *x3_Wo = nullptr;   // hi | lo image pairs (GB_PREC_BF16X3)
 };
 struct PairLayerW {
   TriMulW mul_out, mul_in;

@@ -877,7 +877,7 @@ size_t tc_workspace_bytes(const gb_ctx* c, int B, int N) {
   const size_t gb = align256((size_t)B * N * N * 128 * 2);
   // triangle attention (tc_triatt.cu) keeps Q / K / V^T / gate in planes of its own: the a / b / x planes rely on their
   // k-padding staying zero from one triangle update to the next
-  const size_t ta = c->d.include_tri_att ? 3 * align256(plane) + gb : 0;
+  const size_t ta = c->d.include_tri_att ? 2 * (3 * align256(plane) + gb) : 0;     // hi planes, then their lo twins (bf16x3)
   return 6 * align256(plane) + gb + ta + 1024 + tc_struct_workspace_bytes(c, B, N);
 }
 
@@ -902,12 +902,13 @@ int tc_bind_workspace(gb_ctx* c, void* base, size_t bytes, int B, int N) {
   size_t used = 6 * plane + gbytes;
   s->ta_q = s->ta_k = s->ta_vt = s->ta_g = nullptr;
   if (c->d.include_tri_att) {
-    if (bytes < used + 3 * plane + gbytes) return gb_fail(c, GB_ERR_INVALID, "tc_bind_workspace: too small");
+    if (bytes < used + 2 * (3 * plane + gbytes)) return gb_fail(c, GB_ERR_INVALID, "tc_bind_workspace: too small");
     s->ta_q = reinterpret_cast<bf16*>(q + used);
     s->ta_k = reinterpret_cast<bf16*>(q + used + plane);
     s->ta_vt = reinterpret_cast<bf16*>(q + used + 2 * plane);
     s->ta_g = reinterpret_cast<bf16*>(q + used + 3 * plane);
-    used += 3 * plane + gbytes;
+    s->ta_lo = (3 * plane + gbytes) / 2;
+    used += 2 * (3 * plane + gbytes);
   }
   return tc_struct_bind(c, q + used, bytes - used, B, N);
 }

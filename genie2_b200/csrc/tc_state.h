@@ -19,6 +19,7 @@ struct TcState {
   bf16 *g = nullptr;                 // [B*N*N][128]
   size_t ab_bytes = 0;
   bf16 *ta_q = nullptr, *ta_k = nullptr, *ta_vt = nullptr, *ta_g = nullptr;   // triangle attention (tc_triatt.cu), only with include_tri_att
+  size_t ta_lo = 0;                  // elements from any of them to its lo twin (GB_PREC_BF16X3)
   size_t lo_plane = 0;               // GB_PREC_BF16X3: elements from a / b / x (the hi planes) to their lo planes
   int num_sms = 0;
   // structure net

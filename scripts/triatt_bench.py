@@ -1,5 +1,5 @@
 """Triangle attention (includeTriangularAttention True, off in the base configuration) at the C2 shape: per-module time of the
-tensor-core kernels (bf16 mode, csrc/tc_triatt.cu) and of the fp32 CUDA-core kernels through gb_k_tri_attention, and the
+tensor-core kernels (bf16x3 and bf16 modes, csrc/tc_triatt.cu) and of the fp32 CUDA-core kernels through gb_k_tri_attention, and the
 whole denoiser eval with the modules on.  Prints one JSON line.  usage: triatt_bench.py [B N]"""
 import json
 import os
@@ -28,7 +28,7 @@ def main():
     # algorithmic work of one module: projections 128 -> 512 + out 128 -> 128 (2 * 640 * 128 per pixel), Q K^T and P V (2 * 2 * N * 128 per pixel)
     M = B * N * N
     flops = M * (2.0 * 640 * 128 + 4.0 * N * 128)
-    for prec in ('bf16', 'fp32'):
+    for prec in ('bf16x3', 'bf16', 'fp32'):
         model = make_denoiser(cfg, sd, precision=prec)
         model.return_intermediates = False
         ctx = model.bind_features(feats, torch.device('cuda:0'))

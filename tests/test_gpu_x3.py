@@ -139,7 +139,7 @@ def test_forward_x3_vs_oracle_L64():
     assert errs['states'] < 1e-2 and errs['z'] < 1e-2
 
 
-@pytest.mark.parametrize('name', ['uncond_base_ragged', 'motif_base', 'multichain'])
+@pytest.mark.parametrize('name', ['uncond_base_ragged', 'motif_base', 'multichain', 'triatt'])
 def test_forward_x3_matches_reference_fixture(name):
     """bf16x3 forward vs the unmodified reference's recorded outputs (quaternion sign replayed), north-star gate."""
     cfg, sd, feats, t = load_forward_case(name)
