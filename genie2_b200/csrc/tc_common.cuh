@@ -317,25 +317,53 @@ __device__ __forceinline__ PixTile pix_tile(uint32_t blk, const TileRange& tr) {
 }
 static inline TileRange full_tile_range(int N, int Np) { return TileRange{0u, (uint32_t)(N + 1) >> 1, 0u, (uint32_t)Np >> 6}; }
 
-// Addressing of the a / b operand tile images (elements).  One GPU: [b][ch][kb][Np rows][64].  Row-sharded
-// runs cut the image into `world` contiguous blocks, one per producing rank, so that an in-place all-gather
-// assembles it: by rows for the outgoing update (RL = rows per rank), by k-blocks for the incoming one
-// (KBL = k-blocks per rank).  Inside a block: [b][ch][KBL][RL][64].
+// Addressing of the a / b operand tile images (elements).  One GPU: [b][ch][kb][Np rows][64].  Row-sharded runs cut the
+// image into contiguous blocks so that an in-place exchange assembles it without packing kernels: by the producing
+// rank's rows (outgoing update, RL = rows per rank) or k-blocks (incoming update, KBL = k-blocks per rank), and by
+// channel groups of CG = 128 / world channels, the unit the channel-sharded contraction consumes:
+//   [channel group][row block][k block] [b][CG][KBL][RL][64]
+// Rank s writes blocks (d, s) for every channel group d; the all-to-all moves block (d, s) to rank d, which then holds
+// its CG channels for all rows and all k.  CG = 128, one block: the plain image.
 struct ImgLayout {
-  uint32_t RL, KBL, nkblk;
+  uint32_t RL, KBL, nkblk, CG, nsrc;
   size_t blk;
 };
-static inline ImgLayout img_layout(int B, int Np, int row_split, int k_split) {
+static inline ImgLayout img_layout(int B, int Np, int row_split, int k_split, int cg_split = 1) {
   ImgLayout L;
   L.RL = (uint32_t)Np / row_split;
   L.KBL = (uint32_t)(Np >> 6) / k_split;
   L.nkblk = k_split;
-  L.blk = (size_t)B * 128 * L.KBL * L.RL * 64;
+  L.CG = 128u / cg_split;
+  L.nsrc = (uint32_t)(row_split * k_split);
+  L.blk = (size_t)B * L.CG * L.KBL * L.RL * 64;
   return L;
 }
 __device__ __forceinline__ size_t img_off(const ImgLayout& L, uint32_t b, uint32_t ch, uint32_t kb, uint32_t row) {
-  const uint32_t rb = row / L.RL, kq = kb / L.KBL;
-  return ((size_t)rb * L.nkblk + kq) * L.blk + ((((size_t)b * 128 + ch) * L.KBL + (kb - kq * L.KBL)) * L.RL + (row - rb * L.RL)) * 64;
+  const uint32_t rb = row / L.RL, kq = kb / L.KBL, cg = ch / L.CG;
+  return ((size_t)cg * L.nsrc + rb * L.nkblk + kq) * L.blk +
+         ((((size_t)b * L.CG + (ch - cg * L.CG)) * L.KBL + (kb - kq * L.KBL)) * L.RL + (row - rb * L.RL)) * 64;
+}
+
+// Addressing of the contraction result x (elements of the 128-byte row of 64 columns j of channel ch, image row i, column
+// block jb64).  One GPU: pixel-tile images [b][i / 2][jb64][i & 1][128 ch][64] (the 32 KB of one tile are K6's MN-major A
+// operand).  Channel-sharded: [row block s][channel group d][b][local i / 2][jb64][i & 1][CG][64]: rank d (owner of
+// channel group d) writes blocks (s, d) for every row block s, the all-to-all returns block (s, d) to rank s.
+struct XLayout {
+  uint32_t RL, CG, W, njb;     // rows per rank (Np when unsharded), channels per group, world, Np / 64
+  size_t blk;
+};
+static inline XLayout x_layout(int B, int Np, int world) {
+  XLayout L;
+  L.RL = (uint32_t)Np / world;
+  L.CG = 128u / world;
+  L.W = (uint32_t)world;
+  L.njb = (uint32_t)Np >> 6;
+  L.blk = (size_t)B * (L.RL >> 1) * L.njb * 2 * L.CG * 64;
+  return L;
+}
+__device__ __forceinline__ size_t x_off(const XLayout& L, uint32_t b, uint32_t i, uint32_t jb64, uint32_t ch) {
+  const uint32_t rb = i / L.RL, il = i - rb * L.RL, cg = ch / L.CG;
+  return ((size_t)rb * L.W + cg) * L.blk + (((((size_t)b * (L.RL >> 1) + (il >> 1)) * L.njb + jb64) * 2 + (il & 1)) * L.CG + (ch - cg * L.CG)) * 64;
 }
 
 

@@ -127,7 +127,8 @@ __device__ __forceinline__ void tmem_to_stage(uint8_t* S, uint32_t taddr, uint32
 
 __global__ void __launch_bounds__(256, 2) trimul_contract_tc_kernel(const bf16* __restrict__ a, const bf16* __restrict__ b,
                                                                     bf16* __restrict__ x, int N, int Np, int NJ,
-                                                                    const ImgLayout La, const ImgLayout Lb, int ib0, int nib) {
+                                                                    const ImgLayout La, const ImgLayout Lb, int ib0, int nib,
+                                                                    int ch0, int nchs, const XLayout Lx) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* sm = smem_base_1024(smem_raw);
   uint64_t* full = reinterpret_cast<uint64_t*>(sm + K5_STAGES * K5_STAGE_BYTES);
@@ -138,9 +139,9 @@ __global__ void __launch_bounds__(256, 2) trimul_contract_tc_kernel(const bf16* 
   const int nkb = Np >> 6, njb = (Np + NJ - 1) / NJ;
   uint32_t blk = blockIdx.x;
   const uint32_t jb = blk % njb; blk /= njb;
-  const uint32_t ib = ib0 + blk % nib; blk /= nib;  // blk = b * 128 + c; a row-sharded launch owns row blocks [ib0, ib0 + nib)
+  const uint32_t ib = ib0 + blk % nib; blk /= nib;  // blk = b * nchs + c; a sharded launch owns channels [ch0, ch0 + nchs)
   const uint32_t nj = min((uint32_t)NJ, (uint32_t)Np - jb * NJ);   // columns of this block (multiple of 64)
-  const uint32_t bb = blk >> 7, cch = blk & 127;
+  const uint32_t bb = blk / (uint32_t)nchs, cch = (uint32_t)ch0 + blk % (uint32_t)nchs;
   const uint32_t bpiece = (Lb.RL % nj == 0) ? nj : 128u;            // B rows that are contiguous in the (possibly row-split) image
   const uint32_t a_rows = min(128u, (uint32_t)Np - ib * 128u);      // rows present in the plane (64 or 128)
 
@@ -200,8 +201,7 @@ __global__ void __launch_bounds__(256, 2) trimul_contract_tc_kernel(const bf16* 
     tmem_ld_wait();
     if (i < (uint32_t)N) {
       const uint32_t j = jb * NJ + c0, jb64 = j >> 6, q0 = (j & 63) >> 3;
-      uint8_t* dst = reinterpret_cast<uint8_t*>(x) +
-                     (((((size_t)bb * (Np >> 1) + (i >> 1)) * (Np >> 6) + jb64) * 2 + (i & 1)) * 128 + cch) * 128;
+      uint8_t* dst = reinterpret_cast<uint8_t*>(x + x_off(Lx, bb, i, jb64, cch));
       const uint32_t sw = cch & 7u;
 #pragma unroll
       for (int kp = 0; kp < 2; ++kp) {     // two 16-byte chunks = one 32-byte sector per store
@@ -243,7 +243,7 @@ template <bool SPLIT> struct K5P {
 template <bool SPLIT>
 __global__ void __launch_bounds__(K5P_THREADS, 1) trimul_contract_pers_tc_kernel(
     const bf16* __restrict__ a, const bf16* __restrict__ b, bf16* __restrict__ x, int N, int Np, int NJ, const ImgLayout La,
-    const ImgLayout Lb, int ib0, int nib, uint32_t nunits, size_t lo_ab, size_t lo_x) {
+    const ImgLayout Lb, int ib0, int nib, uint32_t nunits, size_t lo_ab, size_t lo_x, int ch0, int nchs, const XLayout Lx) {
   constexpr uint32_t K5P_STAGES = K5P<SPLIT>::STAGES, STAGE_BYTES = K5P<SPLIT>::STAGE_BYTES;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* sm = smem_base_1024(smem_raw);
@@ -276,7 +276,7 @@ __global__ void __launch_bounds__(K5P_THREADS, 1) trimul_contract_pers_tc_kernel
         const uint32_t jb = blk % njb; blk /= njb;
         const uint32_t ib = ib0 + blk % nib; blk /= nib;
         const uint32_t nj = min((uint32_t)NJ, (uint32_t)Np - jb * NJ);
-        const uint32_t bb = blk >> 7, cch = blk & 127;
+        const uint32_t bb = blk / (uint32_t)nchs, cch = (uint32_t)ch0 + blk % (uint32_t)nchs;
         const uint32_t bpiece = (Lb.RL % nj == 0) ? nj : 128u;
         const uint32_t a_rows = min(128u, (uint32_t)Np - ib * 128u);
         for (uint32_t kb = 0; kb < nkb; ++kb, ++it) {
@@ -336,7 +336,7 @@ __global__ void __launch_bounds__(K5P_THREADS, 1) trimul_contract_pers_tc_kernel
       const uint32_t jb = blk % njb; blk /= njb;
       const uint32_t ib = ib0 + blk % nib; blk /= nib;
       const uint32_t nj = min((uint32_t)NJ, (uint32_t)Np - jb * NJ);
-      const uint32_t bb = blk >> 7, cch = blk & 127, slot = n & 1u;
+      const uint32_t bb = blk / (uint32_t)nchs, cch = (uint32_t)ch0 + blk % (uint32_t)nchs, slot = n & 1u;
       const uint32_t i = ib * 128 + q * 32 + lane;
       const uint32_t t_lane = tmem + ((q * 32u) << 16) + slot * 256u;
       mbar_wait(acc_full + slot, (n >> 1) & 1);
@@ -348,8 +348,7 @@ __global__ void __launch_bounds__(K5P_THREADS, 1) trimul_contract_pers_tc_kernel
         tmem_ld_wait();
         if (i < (uint32_t)N) {
           const uint32_t j = jb * NJ + c0, jb64 = j >> 6, q0 = (j & 63) >> 3;
-          uint8_t* dst = reinterpret_cast<uint8_t*>(x) +
-                         (((((size_t)bb * (Np >> 1) + (i >> 1)) * (Np >> 6) + jb64) * 2 + (i & 1)) * 128 + cch) * 128;
+          uint8_t* dst = reinterpret_cast<uint8_t*>(x + x_off(Lx, bb, i, jb64, cch));
           const uint32_t sw = cch & 7u;
 #pragma unroll
           for (int kp = 0; kp < 2; ++kp) {
@@ -402,7 +401,7 @@ __global__ void __launch_bounds__(K5P_THREADS, 1) trimul_contract_pers_tc_kernel
 
 __global__ void __launch_bounds__(256, 3) trimul_out_tc_kernel(
     const bf16* __restrict__ x, const bf16* __restrict__ g, float* __restrict__ p, int N, int Np,
-    const bf16* __restrict__ Wzimg, const float* __restrict__ uvec, const float* __restrict__ vvec, const TileRange tr) {
+    const bf16* __restrict__ Wzimg, const float* __restrict__ uvec, const float* __restrict__ vvec, const TileRange tr, const XLayout Lx) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* sm = smem_base_1024(smem_raw);
   uint8_t* X = sm;
@@ -440,7 +439,14 @@ __global__ void __launch_bounds__(256, 3) trimul_out_tc_kernel(
   const uint32_t tmem = *tslot;
   pdl_wait();            // x comes from the contraction kernel
   pdl_launch();
-  if (tid == 0) bulk_g2s(X, x + (((size_t)T.b * (Np >> 1) + T.t2) * (Np >> 6) + T.jb) * 16384, 32768, bar_w);
+  if (tid == 0) {
+    // one 32 KB tile; channel-sharded runs receive it as W x 2 pieces [i & 1][CG channels][64], one per channel group
+    if (Lx.W == 1) bulk_g2s(X, x + x_off(Lx, T.b, 2 * T.t2, T.jb, 0), 32768, bar_w);
+    else
+      for (uint32_t cg = 0; cg < Lx.W; ++cg)
+        for (uint32_t ii = 0; ii < 2; ++ii)
+          bulk_g2s(X + ii * 16384u + cg * Lx.CG * 128u, x + x_off(Lx, T.b, 2 * T.t2 + ii, T.jb, cg * Lx.CG), Lx.CG * 128u, bar_w);
+  }
   if (tid == 0) {
     mbar_wait(bar_w, 0);
     tc_fence_after();
@@ -663,7 +669,7 @@ __global__ void __launch_bounds__(K6S_THREADS, 2) trimul_out_x3_kernel(
     pdl_wait();            // x comes from the contraction kernel
     pdl_launch();
     if (lane == 0) {
-      const size_t off = (((size_t)T.b * (Np >> 1) + T.t2) * (Np >> 6) + T.jb) * 16384;
+      const size_t off = (((size_t)T.b * (Np >> 1) + T.t2) * (Np >> 6) + T.jb) * 16384;   // (the split mode is not sharded)
       bulk_g2s(X, x + off, 32768, bar_w);
       bulk_g2s(X + 32768, x + lo_x + off, 32768, bar_w);
     }
@@ -918,40 +924,44 @@ int tc_trimul_stage(gb_ctx* c, const TriMulW& w, bool outgoing, int stage, float
   const int B = c->B, N = c->N, Np = s->Np, W = c->shard_world;
   const bool x3 = c->precision == GB_PREC_BF16X3;
   if (x3 && W > 1) return gb_fail(c, GB_ERR_UNSUPPORTED, "row sharding is built for the bf16 pair stack only");
+  // Row-sharded (W > 1, B == 1): K4 runs on this rank's rows of p and writes blocks (d, me) of the operand images for every
+  // channel group d; an in-place all-to-all hands every rank ITS 128 / W channels for all rows and all k; the contraction is
+  // sharded by channel (x^c = a^c b^cT is independent per channel); a second all-to-all returns x to the row owners for K6.
+  // Per rank and update 3 (W - 1) / W^2 of an image travel (a, b, x) instead of the (W - 1) / W of the all-gather of b.
+  const ImgLayout Lab = W > 1 ? (outgoing ? img_layout(B, Np, W, 1, W) : img_layout(B, Np, 1, W, W)) : img_layout(B, Np, 1, 1);
+  const XLayout Lx = x_layout(B, Np, W);
   if (stage == 0 || stage == 1) {
     int rc = x3 ? tc_launch_trimul_proj_x3(c, w, outgoing, p, st) : tc_launch_trimul_proj(c, w, outgoing, p, st);
     if (rc != GB_OK) return rc;
     if (W > 1) {
-      // each rank wrote its block of the operand images.  K5 needs every row of b: in-place all-gather over NVLink.
-      // For the incoming update it also needs its own rows of a for every k: a is a W x W grid of blocks
-      // (destination row block, source k block) and block (d, s) travels from rank s to rank d: in-place all-to-all.
-      const size_t piece = (size_t)B * 128 * Np * Np * 2 / W;
-      if (!outgoing && (rc = shard_all_to_all(c, s->a, piece / W, st)) != GB_OK) return rc;
-      if ((rc = shard_all_gather(c, s->b, piece, st)) != GB_OK) return rc;
+      if ((rc = shard_all_to_all(c, s->a, Lab.blk * 2, st)) != GB_OK) return rc;
+      if ((rc = shard_all_to_all(c, s->b, Lab.blk * 2, st)) != GB_OK) return rc;
     }
   }
   if (stage == 0 || stage == 2) {
     const int NJ = 256;
-    // sharded: both operand images are complete after the all-gather; this rank contracts its own 128-row blocks
-    const ImgLayout Lb = W > 1 ? (outgoing ? img_layout(B, Np, W, 1) : img_layout(B, Np, 1, W)) : img_layout(B, Np, 1, 1);
-    const ImgLayout La = W > 1 && !outgoing ? img_layout(B, Np, W, W) : Lb;
-    const int nib = W > 1 ? (N / W) / 128 : (Np + 127) / 128, ib0 = W > 1 ? c->shard_rank * nib : 0;
-    const unsigned cgrid = (unsigned)B * 128 * nib * ((Np + NJ - 1) / NJ);
+    const int nib = (Np + 127) / 128, ib0 = 0;
+    const int nchs = 128 / W, ch0 = W > 1 ? c->shard_rank * nchs : 0;     // sharded: this rank's channel group, every row block
+    const unsigned cgrid = (unsigned)B * nchs * nib * ((Np + NJ - 1) / NJ);
     static const int k5pers = [] { const char* e = getenv("GB_K5_PERS"); return e ? atoi(e) : 1; }();
     if (k5pers || x3) {
       const unsigned pgrid = cgrid < (unsigned)s->num_sms ? cgrid : (unsigned)s->num_sms;
-      if (x3) launch_pdl_cls(2, trimul_contract_pers_tc_kernel<true>, pgrid, K5P_THREADS, K5P<true>::SMEM, st, s->a, s->b, s->x, N, Np, NJ, La, Lb, ib0, nib, (uint32_t)cgrid, s->lo_plane, s->lo_plane);
-      else launch_pdl_cls(2, trimul_contract_pers_tc_kernel<false>, pgrid, K5P_THREADS, K5P<false>::SMEM, st, s->a, s->b, s->x, N, Np, NJ, La, Lb, ib0, nib, (uint32_t)cgrid, (size_t)0, (size_t)0);
+      if (x3) launch_pdl_cls(2, trimul_contract_pers_tc_kernel<true>, pgrid, K5P_THREADS, K5P<true>::SMEM, st, s->a, s->b, s->x, N, Np, NJ, Lab, Lab, ib0, nib, (uint32_t)cgrid, s->lo_plane, s->lo_plane, ch0, nchs, Lx);
+      else launch_pdl_cls(2, trimul_contract_pers_tc_kernel<false>, pgrid, K5P_THREADS, K5P<false>::SMEM, st, s->a, s->b, s->x, N, Np, NJ, Lab, Lab, ib0, nib, (uint32_t)cgrid, (size_t)0, (size_t)0, ch0, nchs, Lx);
     } else
-    launch_pdl_cls(2, trimul_contract_tc_kernel, cgrid, 256, K5_SMEM, st, s->a, s->b, s->x, N, Np, NJ, La, Lb, ib0, nib);
+    launch_pdl_cls(2, trimul_contract_tc_kernel, cgrid, 256, K5_SMEM, st, s->a, s->b, s->x, N, Np, NJ, Lab, Lab, ib0, nib, ch0, nchs, Lx);
     GB_LAUNCH_CHECK(c, "trimul_contract_tc");
+    if (W > 1) {
+      const int rc = shard_all_to_all(c, s->x, Lx.blk * 2, st);
+      if (rc != GB_OK) return rc;
+    }
   }
   if (stage == 0 || stage == 3) {
     TileRange tr = full_tile_range(N, Np);
     if (W > 1) { tr.nt2 = (uint32_t)(N / W) >> 1; tr.t2_0 = c->shard_rank * tr.nt2; }
     const unsigned tiles = (unsigned)B * tr.nt2 * tr.njb;
     if (x3) launch_pdl_cls(3, trimul_out_x3_kernel, tiles, K6S_THREADS, K6S_SMEM, st, s->x, s->lo_plane, c->g, p, N, Np, (const bf16*)w.x3_Wz_hi, (const bf16*)w.x3_Wz_lo, w.x3_uv, w.x3_uv + 128, tr);
-    else launch_pdl_cls(3, trimul_out_tc_kernel, tiles, 256, K6_SMEM, st, s->x, s->g, p, N, Np, (const bf16*)w.tc_Wz, w.tc_uv, w.tc_uv + 128, tr);
+    else launch_pdl_cls(3, trimul_out_tc_kernel, tiles, 256, K6_SMEM, st, s->x, s->g, p, N, Np, (const bf16*)w.tc_Wz, w.tc_uv, w.tc_uv + 128, tr, Lx);
     GB_LAUNCH_CHECK(c, "trimul_out_tc");
   }
   return GB_OK;

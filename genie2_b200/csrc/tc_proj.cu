@@ -358,8 +358,9 @@ int tc_launch_trimul_proj(gb_ctx* c, const TriMulW& w, bool outgoing, const floa
   if (W > 1) {
     // this rank's rows of p: image rows [r0, r0 + RB) (outgoing) or k-blocks [r0 / 64, ...) of every image row (incoming)
     const uint32_t RB = (uint32_t)N / W, r0 = c->shard_rank * RB;
-    if (outgoing) { tr = TileRange{r0 >> 1, RB >> 1, 0u, (uint32_t)Np >> 6}; La = Lb = img_layout(B, Np, W, 1); }
-    else { tr = TileRange{0u, (uint32_t)(N + 1) >> 1, r0 >> 6, RB >> 6}; La = img_layout(B, Np, W, W); Lb = img_layout(B, Np, 1, W); }
+    // blocks (channel group d, me) of both images, cut by rows (outgoing) or by k-blocks (incoming): tc_common.cuh ImgLayout
+    if (outgoing) { tr = TileRange{r0 >> 1, RB >> 1, 0u, (uint32_t)Np >> 6}; La = Lb = img_layout(B, Np, W, 1, W); }
+    else { tr = TileRange{0u, (uint32_t)(N + 1) >> 1, r0 >> 6, RB >> 6}; La = Lb = img_layout(B, Np, 1, W, W); }
   }
   const int tiles = B * (int)(tr.nt2 * tr.njb);
   const int grid = tiles < s->num_sms ? tiles : s->num_sms;

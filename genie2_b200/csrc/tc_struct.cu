@@ -196,6 +196,23 @@ __global__ void __launch_bounds__(256, 1) gemm_img_tc_kernel(const GemmImgArgs g
   if (warp == 2) tmem_dealloc(tmem, 64 * NACC);
 }
 
+// Row-sharded runs: the split-K partial sums of this rank's rows are added here, in ln_img_kernel's order
+// ((((p0 + p1) + p2) + bias) + residual), so that the all-gathered rows are bit-identical to the one-GPU result.
+__global__ void sum_partials_kernel(float* __restrict__ p0, const float* __restrict__ p1, const float* __restrict__ p2,
+                                    const float* __restrict__ bias, const float* __restrict__ res, int row0, int rows, int C) {
+  pdl_wait();
+  pdl_launch();
+  const int i = blockIdx.x * blockDim.x + threadIdx.x, per_row = C >> 2;
+  if (i >= rows * per_row) return;
+  const int c = (i % per_row) * 4;
+  const size_t o = (size_t)(row0 + i / per_row) * C + c;
+  float4 v = ld4(p0 + o);
+  const float4 a = ld4(p1 + o), b = ld4(p2 + o), bi = ld4(bias + c), re = ld4(res + o);
+  v.x = (((v.x + a.x) + b.x) + bi.x) + re.x; v.y = (((v.y + a.y) + b.y) + bi.y) + re.y;
+  v.z = (((v.z + a.z) + b.z) + bi.z) + re.z; v.w = (((v.w + a.w) + b.w) + bi.w) + re.w;
+  st4(p0 + o, v);
+}
+
 // ---------------------------------------------------------------------------------------------
 // ln_img_kernel: one warp per row of [R, C] (C % 128 == 0, C <= 512): optional LayerNorm, then any
 // of: fp32 out, second fp32 out (the 'states' list), bf16 operand image [C/64][Rp][64].
@@ -1115,14 +1132,20 @@ int tc_structure_net(gb_ctx* c, float* states_out, cudaStream_t st) {
 #undef IA_LAUNCH
       }
       GB_LAUNCH_CHECK(c, "ipa_attention_tc");
-      if (W > 1) {
-        if ((rc = gemm_img(c, st, s->cat_img, IPA_CAT, t.Wout, cs, w.bout, c->s, cs, c->sA, cs, nullptr, false, 0, row0 / 128, rows / 128))) return rc;
-        if ((rc = shard_all_gather(c, c->sA, (size_t)rows * cs * sizeof(float), st))) return rc;
-      }
       // output projection, K = 2112 = 33 k-blocks: split three ways over grid.z (144 CTAs instead of 48, a third of the serial
       // MMA chain each; also a third of the accumulation length inside the tensor core); the partial sums land in sA / h1 / h2
       // and the LayerNorm kernel adds them, the bias and the residual in a fixed order
-      const bool ks3 = W == 1 && (IPA_CAT / 64) % 3 == 0;
+      const bool split3 = (IPA_CAT / 64) % 3 == 0, ks3 = W == 1 && split3;
+      if (W > 1) {
+        // this rank's query rows only, same split and same order of additions as on one GPU, then the rows are all-gathered
+        if (split3) {
+          if ((rc = gemm_img(c, st, s->cat_img, IPA_CAT, t.Wout, cs, nullptr, nullptr, 0, c->sA, cs, nullptr, false, 0, row0 / 128, rows / 128, false, 3, c->h1, c->h2))) return rc;
+          launch_pdl(sum_partials_kernel, (unsigned)((rows * (cs / 4) + 255) / 256), 256, 0, st, c->sA, (const float*)c->h1, (const float*)c->h2,
+                     (const float*)w.bout, (const float*)c->s, row0, rows, cs);
+          GB_LAUNCH_CHECK(c, "sum_partials");
+        } else if ((rc = gemm_img(c, st, s->cat_img, IPA_CAT, t.Wout, cs, w.bout, c->s, cs, c->sA, cs, nullptr, false, 0, row0 / 128, rows / 128))) return rc;
+        if ((rc = shard_all_gather(c, c->sA, (size_t)rows * cs * sizeof(float), st))) return rc;
+      }
       if (W == 1 && !ks3 && (rc = gemm_img(c, st, s->cat_img, IPA_CAT, t.Wout, cs, w.bout, c->s, cs, c->sA, cs, nullptr, false, 0, 0, 0, x3))) return rc;
       if (ks3) {
         if ((rc = gemm_img(c, st, s->cat_img, IPA_CAT, t.Wout, cs, nullptr, nullptr, 0, c->sA, cs, nullptr, false, 0, 0, 0, x3, 3, c->h1, c->h2))) return rc;

@@ -8,6 +8,11 @@ Host-side logic only; the exchange itself is NCCL inside the CUDA library (csrc/
 * ``exchange_unique_id(group)``    rank 0 draws the 128-byte NCCL unique id, every rank receives it over the
                                    process group that launched the job (``nccl`` under torchrun, ``gloo`` in tests);
 * ``traffic_bytes(N, world, ...)`` bytes each rank receives per denoiser eval (for the bench line).
+
+Exchange pattern (round 2): the triangle contraction is sharded by CHANNEL (x^c = a^c b^cT is independent per channel):
+K4 on a rank's rows -> all-to-all of a and b to the owners of the 128 / world channel groups -> contraction of own channels
+over all rows -> all-to-all of x back to the row owners -> K6 on own rows.  3 (W - 1) / W^2 of an image per rank and update
+instead of the (W - 1) / W of round 1's all-gather of b.
 """
 import ctypes as C
 
@@ -34,15 +39,15 @@ def check_shardable(B, N, world):
 
 
 def traffic_bytes(N, world, n_pair_layer=5, n_struct_layer=8, c_p=128, c_s=384):
-    """Bytes RECEIVED per rank per denoiser eval: per pair layer the bf16 b image of the outgoing update, the b
-    image of the incoming one (all-gathers) and this rank's rows of the incoming a image (all-to-all); per
-    structure layer the fp32 single representation."""
+    """Bytes RECEIVED per rank per denoiser eval.  Per triangle update three in-place all-to-alls (the bf16 a and b operand
+    images to the owners of the channel groups, the contraction result x back to the row owners): (world - 1) of the
+    world^2 blocks of an image each; per structure layer the all-gather of the fp32 single representation."""
     if world == 1:
         return 0
     image = N * N * c_p * 2
-    gathered = n_pair_layer * 2 * image + n_struct_layer * N * c_s * 4       # all-gathers: (world - 1) / world of it arrives
-    exchanged = n_pair_layer * image // world                                # all-to-all of a: this rank's row block
-    return (gathered + exchanged) * (world - 1) // world
+    exchanged = n_pair_layer * 2 * 3 * (image // (world * world)) * (world - 1)
+    gathered = n_struct_layer * N * c_s * 4 * (world - 1) // world
+    return exchanged + gathered
 
 
 def _draw_unique_id():

@@ -79,7 +79,8 @@ def main():
             ok = ok and torch.equal(one['p'], many['p'])
         if not ok:
             dz = float((one['z'] - many['z']).abs().max())
-            print('rank %d: MISMATCH max |dz| = %g' % (rank, dz), flush=True)
+            dp = float((one['p'] - many['p']).abs().max()) if with_p else float('nan')
+            print('rank %d: MISMATCH max |dz| = %g, max |dp| = %g (pair stack)' % (rank, dz, dp), flush=True)
     n_coll = model.collective_count()
     model.return_intermediates = False
     ms_many = timed(a.time) if a.time else None

@@ -28,61 +28,78 @@ def test_row_ranges_and_rules():
         shard.check_shardable(1, 768, 4)             # 192 rows per rank: not whole 128-row blocks
     assert shard.traffic_bytes(1024, 1) == 0
     img = 1024 * 1024 * 128 * 2
-    assert shard.traffic_bytes(1024, 8) == (5 * 2 * img + 8 * 1024 * 384 * 4 + 5 * img // 8) * 7 // 8
+    assert shard.traffic_bytes(1024, 8) == 5 * 2 * 3 * (img // 64) * 7 + 8 * 1024 * 384 * 4 * 7 // 8
+    assert shard.traffic_bytes(1024, 8) < 0.4 * (5 * 2 * img * 7 // 8)      # well under the all-gather of b alone (round 1)
 
 
-def img_off(Np, B, row_split, k_split, b, ch, kb, row):
-    """Python restatement of tc::img_off (element offset of a (b, channel, k-block, row) row of 64)."""
-    RL, KBL = Np // row_split, (Np // 64) // k_split
-    blk = B * 128 * KBL * RL * 64
-    rb, kq = row // RL, kb // KBL
-    return (rb * k_split + kq) * blk + (((b * 128 + ch) * KBL + kb % KBL) * RL + row % RL) * 64
+def img_off(Np, B, row_split, k_split, b, ch, kb, row, cg_split=1):
+    """Python restatement of tc::img_off (element offset of a (b, channel, k-block, row) row of 64):
+    [channel group][row block][k block] [b][CG][KBL][RL][64]."""
+    RL, KBL, CG = Np // row_split, (Np // 64) // k_split, 128 // cg_split
+    blk = B * CG * KBL * RL * 64
+    rb, kq, cg = row // RL, kb // KBL, ch // CG
+    return ((cg * row_split * k_split) + rb * k_split + kq) * blk + (((b * CG + ch % CG) * KBL + kb % KBL) * RL + row % RL) * 64
 
 
-@pytest.mark.parametrize('world', [2, 4])
+def x_off(Np, B, world, b, i, jb64, ch):
+    """Python restatement of tc::x_off: [row block][channel group][b][local i / 2][jb64][i & 1][CG][64]."""
+    RL, CG, njb = Np // world, 128 // world, Np // 64
+    blk = B * (RL // 2) * njb * 2 * CG * 64
+    rb, il, cg = i // RL, i % RL, ch // CG
+    return (rb * world + cg) * blk + ((((b * (RL // 2) + il // 2) * njb + jb64) * 2 + (il & 1)) * CG + ch % CG) * 64
+
+
+@pytest.mark.parametrize('world', [2, 4, 8])
 @pytest.mark.parametrize('mode', ['rows', 'kblocks'])
-def test_image_layout_is_a_partition(world, mode):
-    Np, B, nch = 128 * world, 1, 3                   # 3 of the 128 channels are enough to catch a stride error
+def test_image_layout_is_a_block_grid_by_channel_group_and_producer(world, mode):
+    """Both operand images of a sharded triangle update: the producer (rank s: its rows for the outgoing update, its k-blocks
+    for the incoming one) writes block (d, s) for every channel group d; block (d, s) is contiguous, so the in-place all-to-all
+    of csrc/shard.cu (block (d, s) travels from rank s to rank d) needs no packing; afterwards rank d reads blocks (d, *) only."""
+    Np, B = 128 * world, 1
     rs, ks = (world, 1) if mode == 'rows' else (1, world)
+    CG = 128 // world
     total = B * 128 * (Np // 64) * Np * 64
-    piece = total // world
+    blk = total // (world * world)
     seen = np.zeros(total // 64, dtype=np.int32)
-    for rank in range(world):
-        rows = range(rank * Np // world, (rank + 1) * Np // world) if mode == 'rows' else range(Np)
-        kbs = range(Np // 64) if mode == 'rows' else range(rank * (Np // 64) // world, (rank + 1) * (Np // 64) // world)
-        for ch in list(range(nch)) + [127]:
+    for src in range(world):
+        rows = range(src * Np // world, (src + 1) * Np // world) if mode == 'rows' else range(Np)
+        kbs = range(Np // 64) if mode == 'rows' else range(src * (Np // 64) // world, (src + 1) * (Np // 64) // world)
+        for ch in sorted({0, 1, CG - 1, CG, 127}):
+            d = ch // CG
             for kb in kbs:
                 for row in rows:
-                    off = img_off(Np, B, rs, ks, 0, ch, kb, row)
-                    assert off % 64 == 0 and rank * piece <= off < (rank + 1) * piece      # inside this rank's all-gather piece
+                    off = img_off(Np, B, rs, ks, 0, ch, kb, row, world)
+                    assert off % 64 == 0 and (d * world + src) * blk <= off < (d * world + src + 1) * blk
                     seen[off // 64] += 1
     assert seen.max() == 1
     # unsharded layout is the plain [b][ch][kb][row][64] image
     assert img_off(Np, 1, 1, 1, 0, 5, 1, 7) == ((5 * (Np // 64) + 1) * Np + 7) * 64
-    # 128-row operand tiles stay contiguous in both sharded layouts
+    # the 128-row operand tiles of the contraction stay contiguous
     for row0 in range(0, Np, 128):
-        a = img_off(Np, B, rs, ks, 0, 9, 1, row0)
-        assert img_off(Np, B, rs, ks, 0, 9, 1, row0 + 127) == a + 127 * 64
+        a = img_off(Np, B, rs, ks, 0, 9, 1, row0, world)
+        assert img_off(Np, B, rs, ks, 0, 9, 1, row0 + 127, world) == a + 127 * 64
 
 
-@pytest.mark.parametrize('world', [2, 4])
-def test_incoming_a_image_is_a_block_grid(world):
-    """Incoming update: a is cut by destination row block AND source k block; rank s writes column s of the
-    world x world block grid, the in-place all-to-all moves block (d, s) to rank d, whose contraction then reads
-    row d only (csrc/shard.cu, shard_all_to_all)."""
+@pytest.mark.parametrize('world', [2, 4, 8])
+def test_x_layout_returns_blocks_to_the_row_owners(world):
+    """Contraction result: rank d (channel group d) writes block (s, d) for every row block s; the all-to-all returns block
+    (s, d) to rank s, which reads its tiles as world x 2 contiguous pieces of CG x 128 bytes."""
     Np, B = 128 * world, 1
-    blk = B * 128 * ((Np // 64) // world) * (Np // world) * 64
-    for src in range(world):                                      # writer: k blocks of rank src, every image row
-        for kb in range(src * (Np // 64) // world, (src + 1) * (Np // 64) // world):
-            for row in (0, Np // world - 1, Np // world, Np - 1):
-                off = img_off(Np, B, world, world, 0, 17, kb, row)
-                d = row // (Np // world)
-                assert (d * world + src) * blk <= off < (d * world + src + 1) * blk
-    for dst in range(world):                                      # reader: its own rows, every k block
-        lo, hi = dst * world * blk, (dst + 1) * world * blk
-        for kb in range(Np // 64):
-            for row in range(dst * Np // world, (dst + 1) * Np // world, 37):
-                assert lo <= img_off(Np, B, world, world, 0, 3, kb, row) < hi
+    CG = 128 // world
+    total = B * Np * (Np // 64) * 128 * 64
+    blk = total // (world * world)
+    seen = np.zeros(total // 64, dtype=np.int32)
+    for i in range(0, Np):
+        for jb in range(Np // 64):
+            for ch in sorted({0, CG - 1, CG, 127}):
+                off = x_off(Np, B, world, 0, i, jb, ch)
+                s_, d = i // (Np // world), ch // CG
+                assert (s_ * world + d) * blk <= off < (s_ * world + d + 1) * blk
+                seen[off // 64] += 1
+            a = x_off(Np, B, world, 0, i, jb, CG)                     # a piece: CG consecutive channel rows
+            assert x_off(Np, B, world, 0, i, jb, 2 * CG - 1) == a + (CG - 1) * 64 if world > 1 else True
+    assert seen.max() == 1
+    assert x_off(256, 1, 1, 0, 5, 2, 77) == ((((5 // 2) * 4 + 2) * 2 + 1) * 128 + 77) * 64      # one GPU: the tile images
 
 
 def _free_port():
