@@ -1,16 +1,22 @@
 // Row sharding of one long sample (B = 1) over `world` GPUs of one box: NCCL communicator owned by the
-// context, in-place all-gathers enqueued on the caller's stream between the kernels of gb_denoise.
+// context, in-place exchanges enqueued on the caller's stream between the kernels of gb_denoise.
 //
 // What is sharded (rows [rank * N / world, (rank + 1) * N / world) of the pair map p on each rank):
-//   pair embedding, K4 / K5 / K6 of both triangle updates, the pair transition, the IPA attention and
-//   its output projection.  What is exchanged:
-//     outgoing update   all-gather of the b operand image      (bf16, N^2 * 128 * 2 bytes in total)
-//     incoming update   all-gather of b, all-to-all of a       ((1 + 1 / world) x that)
-//     each IPA layer    all-gather of the [N, c_s] fp32 result (1.5 MB at N = 1024)
-//   p itself never moves (only when the caller asks for aux.p).  The operand images are laid out so that
-//   each rank's contribution is one contiguous block (tc_common.cuh, ImgLayout), hence plain in-place
-//   ncclAllGather calls and no packing kernels.  The same kernels run on the same tiles in the same
-//   k order as on one GPU, so the sharded result is bit-identical to the single-GPU one.
+//   pair embedding, K4 / K6 of both triangle updates, the pair transition, the IPA attention and its
+//   output projection.  The contraction K5 is sharded by CHANNEL instead (x^c = a^c b^cT is independent
+//   per channel): rank d contracts channels [d * 128 / world, (d + 1) * 128 / world) for all rows.
+//   What is exchanged:
+//     each triangle update   all-to-all of the a and b operand images (one NCCL group: every rank ends up
+//                            with its channel group for all rows and all k), all-to-all of x back to the
+//                            row owners: 3 (W - 1) / W^2 of an image (N^2 * 128 * 2 bytes) received per
+//                            rank, against (W - 1) / W .. (W^2 - 1) / W^2 for the all-gather of b (+ the
+//                            all-to-all of a) that row-sharding the contraction needs
+//     each IPA layer         all-gather of the [N, c_s] fp32 result (1.5 MB at N = 1024)
+//   p itself never moves (only when the caller asks for aux.p).  The operand images and x are laid out
+//   as W x W grids of contiguous blocks (tc_common.cuh, ImgLayout / XLayout): block (dest, source) is
+//   written in place by the source rank and travels as is, so there are no packing kernels.  The same
+//   kernels run on the same tiles in the same k order as on one GPU, so the sharded result is
+//   bit-identical to the single-GPU one.
 //
 // libnccl is resolved at run time (dlopen) so that single-GPU users need no NCCL at all; inside a
 // torch process this picks up the libnccl.so.2 torch already loaded.
@@ -123,17 +129,21 @@ int shard_all_gather(gb_ctx* c, void* base, size_t piece_bytes, cudaStream_t st)
   return GB_OK;
 }
 
-int shard_all_to_all(gb_ctx* c, void* base, size_t block_bytes, cudaStream_t st) {
+int shard_all_to_all(gb_ctx* c, void* base, size_t block_bytes, cudaStream_t st, void* base2) {
   const int W = c->shard_world, me = c->shard_rank;
   if (W <= 1) return GB_OK;
   if (!c->shard_comm) return gb_fail(c, GB_ERR_INVALID, "shard_all_to_all: no communicator");
   ncclComm_t comm = (ncclComm_t)c->shard_comm;
-  char* b = (char*)base;
+  char* bases[2] = {(char*)base, (char*)base2};
   ncclResult_t r = g_nccl.GroupStart();
-  for (int peer = 0; peer < W && r == 0; ++peer) {
-    if (peer == me) continue;
-    r = g_nccl.Send(b + ((size_t)peer * W + me) * block_bytes, block_bytes, ncclUint8, peer, comm, st);
-    if (r == 0) r = g_nccl.Recv(b + ((size_t)me * W + peer) * block_bytes, block_bytes, ncclUint8, peer, comm, st);
+  for (int i = 0; i < 2; ++i) {
+    char* b = bases[i];
+    if (!b) continue;
+    for (int peer = 0; peer < W && r == 0; ++peer) {
+      if (peer == me) continue;
+      r = g_nccl.Send(b + ((size_t)peer * W + me) * block_bytes, block_bytes, ncclUint8, peer, comm, st);
+      if (r == 0) r = g_nccl.Recv(b + ((size_t)me * W + peer) * block_bytes, block_bytes, ncclUint8, peer, comm, st);
+    }
   }
   const ncclResult_t e = g_nccl.GroupEnd();
   if (r == 0) r = e;

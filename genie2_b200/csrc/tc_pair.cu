@@ -934,8 +934,7 @@ int tc_trimul_stage(gb_ctx* c, const TriMulW& w, bool outgoing, int stage, float
     int rc = x3 ? tc_launch_trimul_proj_x3(c, w, outgoing, p, st) : tc_launch_trimul_proj(c, w, outgoing, p, st);
     if (rc != GB_OK) return rc;
     if (W > 1) {
-      if ((rc = shard_all_to_all(c, s->a, Lab.blk * 2, st)) != GB_OK) return rc;
-      if ((rc = shard_all_to_all(c, s->b, Lab.blk * 2, st)) != GB_OK) return rc;
+      if ((rc = shard_all_to_all(c, s->a, Lab.blk * 2, st, s->b)) != GB_OK) return rc;
     }
   }
   if (stage == 0 || stage == 2) {
