@@ -76,6 +76,7 @@ SYMBOLS = {
     'gb_shard_init': (C.c_int, [_P, C.c_int, C.c_int, _P]),
     'gb_shard_info': (C.c_int, [_P, C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     'gb_collective_count': (C.c_int64, [_P]),
+    'gb_peer_barrier_count': (C.c_int64, [_P]),
 }
 
 _lib = None

@@ -45,6 +45,7 @@ extern "C" const char* gb_last_error(const gb_ctx* ctx) { return ctx ? ctx->err.
 extern "C" int64_t gb_launch_count(const gb_ctx* ctx) { return ctx ? ctx->launches : 0; }
 extern "C" int64_t gb_workspace_bytes(const gb_ctx* ctx) { return ctx ? (int64_t)ctx->ws_bytes : 0; }
 extern "C" int64_t gb_collective_count(const gb_ctx* ctx) { return ctx ? ctx->collectives : 0; }
+extern "C" int64_t gb_peer_barrier_count(const gb_ctx* ctx) { return ctx ? ctx->peer_barriers : 0; }
 
 // Scratch of gb_k_ipa_static (the entry point that allocates nothing): the fused projection rows [rows][1152] followed by
 // the concat rows [rows][2112], rows <= GB_K_IPA_STATIC_MAX_ROWS: 13,369,344 bytes that every GPU which loads this library
@@ -504,6 +505,8 @@ extern "C" int gb_set_features(gb_ctx* c, const gb_features* f) {
     // grow-only: a batch that fits in what an earlier, larger batch allocated is re-carved in place (a length sweep that
     // runs its largest batches first allocates once)
     if (kf.off + 256 > c->feat_cap || kw.off + 512 + tcb > c->ws_cap) {
+      // row-sharded: the peers read this workspace over NVLink (shard.cu); they let go of the old one first (collective)
+      if (c->shard_world > 1 && c->ws_alloc) { const int urc = shard_unmap_workspace(c, true); if (urc != GB_OK) return urc; }
       free_features(c);
       GB_CUDA(c, cudaMalloc(&c->feat_alloc, kf.off + 256));
       cudaError_t e = cudaMalloc(&c->ws_alloc, kw.off + 512 + tcb);
@@ -513,6 +516,7 @@ extern "C" int gb_set_features(gb_ctx* c, const gb_features* f) {
       }
       c->feat_cap = kf.off + 256;
       c->ws_cap = kw.off + 512 + tcb;
+      if (c->shard_world > 1) { const int mrc = shard_map_workspace(c); if (mrc != GB_OK) return mrc; }
     } else {
       drop_step_graph(c);
       c->features_set = false;
@@ -775,6 +779,9 @@ extern "C" int gb_denoise(gb_ctx* c, const float* rots, const float* trans, cons
     }
     if ((rc = run_transition(c, c->pair[l].tr, c->p, st))) return rc;
   }
+  // row-sharded: no rank leaves the pair stack while a peer's last K6 may still be reading its x (its memory stays valid for
+  // the peers for as long as work of this eval is in flight anywhere)
+  if (W > 1 && d.include_mul_update && (rc = shard_barrier(c, st))) return rc;
   if (aux && aux->p) {
     if (W > 1 && (rc = shard_all_gather(c, c->p, (size_t)rows_l * N * 128 * 4, st))) return rc;   // every rank returns the whole map
     GB_CUDA(c, cudaMemcpyAsync(aux->p, c->p, (size_t)R * N * 128 * 4, cudaMemcpyDeviceToDevice, st));

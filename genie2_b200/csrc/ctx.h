@@ -110,7 +110,13 @@ struct gb_ctx {
   // row sharding of one long sample over `shard_world` GPUs (shard.cu); 1 = off
   int shard_world = 1, shard_rank = 0;
   void* shard_comm = nullptr;   // ncclComm_t
-  int64_t collectives = 0;      // all-gathers enqueued since creation
+  // peer-mapped memory of the other ranks (CUDA IPC; shard.cu): peer_ws[r] = rank r's workspace allocation as seen from this
+  // GPU (own entry = ws_alloc), peer_flags[r] = rank r's barrier flags (own entry = flag_alloc)
+  void* peer_ws[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+  unsigned* peer_flags[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+  void* flag_alloc = nullptr;
+  long long peer_barriers = 0;
+  int64_t collectives = 0;      // NCCL collectives enqueued since creation
   // tensor-core scratch (bf16/tf32 operand copies), owned by the tc module
   void* tc_state = nullptr;
   // device address of the file-scope static scratch of gb_k_ipa_static (api.cu), resolved once in gb_create

@@ -80,6 +80,14 @@ __device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src_gmem, u
                "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar))
                : "memory");
 }
+// shared -> global bulk copy (bulk async-group completion): commit, then wait until all but `Pending` groups have finished
+// READING shared memory (the slot may be refilled) or have finished altogether
+__device__ __forceinline__ void bulk_s2g(void* dst_gmem, const void* src_smem, uint32_t bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst_gmem), "r"(smem_u32(src_smem)), "r"(bytes) : "memory");
+  asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+}
+template <int Pending> __device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(Pending) : "memory"); }
+template <int Pending> __device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group %0;" ::"n"(Pending) : "memory"); }
 // ask L2 for [src, src + bytes) (bytes % 16 == 0, src 16-byte aligned); no completion, no destination
 __device__ __forceinline__ void l2_prefetch(const void* src_gmem, uint32_t bytes) {
   asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src_gmem), "r"(bytes) : "memory");
@@ -343,6 +351,10 @@ __device__ __forceinline__ size_t img_off(const ImgLayout& L, uint32_t b, uint32
   return ((size_t)cg * L.nsrc + rb * L.nkblk + kq) * L.blk +
          ((((size_t)b * L.CG + (ch - cg * L.CG)) * L.KBL + (kb - kq * L.KBL)) * L.RL + (row - rb * L.RL)) * 64;
 }
+
+// Row-sharded runs read blocks other ranks produced straight from those ranks' memory (peer-mapped over NVLink, shard.cu):
+// p[r] = rank r's copy of the buffer; one GPU: p[0].
+struct PeerImg { const __nv_bfloat16* p[8]; };
 
 // Addressing of the contraction result x (elements of the 128-byte row of 64 columns j of channel ch, image row i, column
 // block jb64).  One GPU: pixel-tile images [b][i / 2][jb64][i & 1][128 ch][64] (the 32 KB of one tile are K6's MN-major A

@@ -400,7 +400,7 @@ __global__ void __launch_bounds__(K5P_THREADS, 1) trimul_contract_pers_tc_kernel
 #define K6_SMEM (65536 + 1024 + 64 + 5120)
 
 __global__ void __launch_bounds__(256, 3) trimul_out_tc_kernel(
-    const bf16* __restrict__ x, const bf16* __restrict__ g, float* __restrict__ p, int N, int Np,
+    const PeerImg px, const bf16* __restrict__ g, float* __restrict__ p, int N, int Np,
     const bf16* __restrict__ Wzimg, const float* __restrict__ uvec, const float* __restrict__ vvec, const TileRange tr, const XLayout Lx) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* sm = smem_base_1024(smem_raw);
@@ -440,12 +440,13 @@ __global__ void __launch_bounds__(256, 3) trimul_out_tc_kernel(
   pdl_wait();            // x comes from the contraction kernel
   pdl_launch();
   if (tid == 0) {
-    // one 32 KB tile; channel-sharded runs receive it as W x 2 pieces [i & 1][CG channels][64], one per channel group
-    if (Lx.W == 1) bulk_g2s(X, x + x_off(Lx, T.b, 2 * T.t2, T.jb, 0), 32768, bar_w);
+    // one 32 KB tile; channel-sharded runs fetch it as W x 2 pieces [i & 1][CG channels][64], each from the rank that
+    // contracted that channel group (peer memory over NVLink)
+    if (Lx.W == 1) bulk_g2s(X, px.p[0] + x_off(Lx, T.b, 2 * T.t2, T.jb, 0), 32768, bar_w);
     else
       for (uint32_t cg = 0; cg < Lx.W; ++cg)
         for (uint32_t ii = 0; ii < 2; ++ii)
-          bulk_g2s(X + ii * 16384u + cg * Lx.CG * 128u, x + x_off(Lx, T.b, 2 * T.t2 + ii, T.jb, cg * Lx.CG), Lx.CG * 128u, bar_w);
+          bulk_g2s(X + ii * 16384u + cg * Lx.CG * 128u, px.p[cg] + x_off(Lx, T.b, 2 * T.t2 + ii, T.jb, cg * Lx.CG), Lx.CG * 128u, bar_w);
   }
   if (tid == 0) {
     mbar_wait(bar_w, 0);
@@ -924,17 +925,32 @@ int tc_trimul_stage(gb_ctx* c, const TriMulW& w, bool outgoing, int stage, float
   const int B = c->B, N = c->N, Np = s->Np, W = c->shard_world;
   const bool x3 = c->precision == GB_PREC_BF16X3;
   if (x3 && W > 1) return gb_fail(c, GB_ERR_UNSUPPORTED, "row sharding is built for the bf16 pair stack only");
-  // Row-sharded (W > 1, B == 1): K4 runs on this rank's rows of p and writes blocks (d, me) of the operand images for every
-  // channel group d; an in-place all-to-all hands every rank ITS 128 / W channels for all rows and all k; the contraction is
-  // sharded by channel (x^c = a^c b^cT is independent per channel); a second all-to-all returns x to the row owners for K6.
-  // Per rank and update 3 (W - 1) / W^2 of an image travel (a, b, x) instead of the (W - 1) / W of the all-gather of b.
+  // Row-sharded (W > 1, B == 1): K4 runs on this rank's rows of p and writes blocks (d, me) of the operand images, in its own
+  // memory, for every channel group d; the contraction is sharded by CHANNEL (x^c = a^c b^cT is independent per channel):
+  // rank d takes its 128 / W channels for all rows and all k.  It first pulls blocks (d, s) of a and b out of rank s's memory
+  // (peer-mapped over NVLink, shard.cu: one copy kernel, bulk copies both ways, no staging buffers, no rendezvous) because
+  // K5 reads every operand block 4 - 8 times and peer reads bypass the local L2; K5 then runs on local memory and writes x
+  // blocks (s, d) locally; K6 of rank s fetches its rows of x straight from every channel owner (each tile is read once).
+  // Two device-side barriers per update (operands ready / x ready) replace every collective; per rank and update
+  // 3 (W - 1) / W^2 of an image cross NVLink (a, b, x) against (W - 1) / W for an all-gather of b.  Write-after-read across
+  // updates is covered by the same barriers: K4 of update n + 1 follows this rank's "x ready" barrier of update n, which every
+  // rank reaches only after its pull and K5 of update n; K5 of update n + 1 follows "operands ready", which follows every
+  // rank's K6 of update n.
   const ImgLayout Lab = W > 1 ? (outgoing ? img_layout(B, Np, W, 1, W) : img_layout(B, Np, 1, W, W)) : img_layout(B, Np, 1, 1);
   const XLayout Lx = x_layout(B, Np, W);
+  PeerImg px;
+  for (int r = 0; r < 8; ++r) {
+    const char* base = W > 1 ? (const char*)c->peer_ws[r < W ? r : 0] : (const char*)c->ws_alloc;
+    if (W > 1 && !base) return gb_fail(c, GB_ERR_INVALID, "row sharding: peer workspaces are not mapped");
+    px.p[r] = (const bf16*)(base + ((const char*)s->x - (const char*)c->ws_alloc));
+  }
+  int rc;
   if (stage == 0 || stage == 1) {
-    int rc = x3 ? tc_launch_trimul_proj_x3(c, w, outgoing, p, st) : tc_launch_trimul_proj(c, w, outgoing, p, st);
+    rc = x3 ? tc_launch_trimul_proj_x3(c, w, outgoing, p, st) : tc_launch_trimul_proj(c, w, outgoing, p, st);
     if (rc != GB_OK) return rc;
     if (W > 1) {
-      if ((rc = shard_all_to_all(c, s->a, Lab.blk * 2, st, s->b)) != GB_OK) return rc;
+      if ((rc = shard_barrier(c, st)) != GB_OK) return rc;                 // operands ready on every rank
+      if ((rc = shard_pull_blocks(c, s->a, s->b, Lab.blk * 2, st)) != GB_OK) return rc;
     }
   }
   if (stage == 0 || stage == 2) {
@@ -950,17 +966,14 @@ int tc_trimul_stage(gb_ctx* c, const TriMulW& w, bool outgoing, int stage, float
     } else
     launch_pdl_cls(2, trimul_contract_tc_kernel, cgrid, 256, K5_SMEM, st, s->a, s->b, s->x, N, Np, NJ, Lab, Lab, ib0, nib, ch0, nchs, Lx);
     GB_LAUNCH_CHECK(c, "trimul_contract_tc");
-    if (W > 1) {
-      const int rc = shard_all_to_all(c, s->x, Lx.blk * 2, st);
-      if (rc != GB_OK) return rc;
-    }
+    if (W > 1 && (rc = shard_barrier(c, st)) != GB_OK) return rc;        // x ready on every rank
   }
   if (stage == 0 || stage == 3) {
     TileRange tr = full_tile_range(N, Np);
     if (W > 1) { tr.nt2 = (uint32_t)(N / W) >> 1; tr.t2_0 = c->shard_rank * tr.nt2; }
     const unsigned tiles = (unsigned)B * tr.nt2 * tr.njb;
     if (x3) launch_pdl_cls(3, trimul_out_x3_kernel, tiles, K6S_THREADS, K6S_SMEM, st, s->x, s->lo_plane, c->g, p, N, Np, (const bf16*)w.x3_Wz_hi, (const bf16*)w.x3_Wz_lo, w.x3_uv, w.x3_uv + 128, tr);
-    else launch_pdl_cls(3, trimul_out_tc_kernel, tiles, 256, K6_SMEM, st, s->x, s->g, p, N, Np, (const bf16*)w.tc_Wz, w.tc_uv, w.tc_uv + 128, tr, Lx);
+    else launch_pdl_cls(3, trimul_out_tc_kernel, tiles, 256, K6_SMEM, st, px, s->g, p, N, Np, (const bf16*)w.tc_Wz, w.tc_uv, w.tc_uv + 128, tr, Lx);
     GB_LAUNCH_CHECK(c, "trimul_out_tc");
   }
   return GB_OK;

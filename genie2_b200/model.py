@@ -317,6 +317,9 @@ class Denoiser(nn.Module):
     def collective_count(self):
         return int(_lib.load().gb_collective_count(self._ctx)) if self._ctx is not None else 0
 
+    def peer_barrier_count(self):
+        return int(_lib.load().gb_peer_barrier_count(self._ctx)) if self._ctx is not None else 0
+
     def launch_count(self):
         return int(_lib.load().gb_launch_count(self._ctx)) if self._ctx is not None else 0
 

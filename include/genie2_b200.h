@@ -178,7 +178,8 @@ int64_t gb_workspace_bytes(const gb_ctx* ctx);
 int gb_shard_unique_id(void* out128);
 int gb_shard_init(gb_ctx* ctx, int world, int rank, const void* id128);
 int gb_shard_info(const gb_ctx* ctx, int* world, int* rank);
-int64_t gb_collective_count(const gb_ctx* ctx); /* all-gathers enqueued by this context */
+int64_t gb_collective_count(const gb_ctx* ctx);   /* NCCL collectives enqueued by this context */
+int64_t gb_peer_barrier_count(const gb_ctx* ctx); /* device-side barriers of the ranks (flags in peer-mapped memory) enqueued */
 
 /* ---- per-kernel entry points (unit parity tests; same kernels the forward uses) ---- */
 
