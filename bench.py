@@ -562,7 +562,7 @@ def measure_c5(K, W_, world, rank, local, barrier):
     loop(T_STEPS, W_)
     barrier()
     wall0 = time.time()
-    l0, c0 = genie.model.launch_count(), genie.model.collective_count()
+    l0, c0, b0 = genie.model.launch_count(), genie.model.collective_count(), genie.model.peer_barrier_count()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     loop(T_STEPS - W_, K)
@@ -590,10 +590,12 @@ def measure_c5(K, W_, world, rank, local, barrier):
             'warmup': W_, 'ms_per_step': ms / K, 'higher_is_better': True, 'scaling': 'strong', 'vs_baseline': None, 'dtype': 'bf16',
             'data': 'synthetic',
             'config': {'workload': 'unconditional L=1024 batch 1, base config, scale 0.6 (BASELINE configs[4])',
-                       'parallelism': 'pair rows sharded over %d GPUs, NCCL all-gather / all-to-all' % world if world > 1 else 'single GPU',
+                       'parallelism': ('pair rows sharded over %d GPUs (triangle contraction by channel), operands pulled from peer-mapped '
+                                       'memory over NVLink, device-side barriers' % world) if world > 1 else 'single GPU',
                        'weights': 'seeded activated random init'},
             'seconds_per_1000_step_sample': ms / K,
             'gpu_launches': int(genie.model.launch_count() - l0), 'collectives': int(genie.model.collective_count() - c0),
+            'peer_barriers': int(genie.model.peer_barrier_count() - b0),
             'recv_bytes_per_rank_per_step': shard.traffic_bytes(n, world), 'ranks_agree_bitwise': same,
             'finite': bool(torch.isfinite(x).all()), 'clocks': clk,
             'whole_eval': {'algorithmic_tflop_per_eval': fl / 1e12, 'achieved_tflops': fl / (ms / K * 1e-3) / 1e12,

@@ -462,6 +462,8 @@ static void carve_workspace(gb_ctx* c, Carver& k, int B, int N) {
   c->sB = k.take<float>(R * cs);
   c->h1 = k.take<float>(R * cs);
   c->h2 = k.take<float>(R * cs);
+  c->sX[0] = k.take<float>(R * cs);      // row-sharded structure net: the rows the ranks exchange, alternating per layer
+  c->sX[1] = k.take<float>(R * cs);
   c->pipj = k.take<float>(R * 256);
   c->qkv = k.take<float>(R * IPA_QKV);
   c->cat = k.take<float>(R * IPA_CAT);

@@ -85,6 +85,7 @@ struct gb_ctx {
   size_t ws_bytes = 0;
   size_t feat_cap = 0, ws_cap = 0;   // bytes behind feat_alloc / ws_alloc (grow-only across gb_set_features calls)
   float *s = nullptr, *sA = nullptr, *sB = nullptr, *h1 = nullptr, *h2 = nullptr, *pipj = nullptr;
+  float* sX[2] = {nullptr, nullptr};
   float *p = nullptr, *a = nullptr, *b = nullptr, *x = nullptr, *g = nullptr;
   float *ta_x = nullptr, *ta_bias = nullptr;   // triangle attention: LN(p) / gated o [M][128], bias [M][4]
   float *qkv = nullptr, *cat = nullptr, *rots_w = nullptr, *trans_w = nullptr, *z = nullptr;

@@ -244,6 +244,21 @@ int shard_unmap_workspace(gb_ctx* c, bool barrier) {
   return GB_OK;
 }
 
+static int launch_pull(gb_ctx* c, const PullJob& job, cudaStream_t st) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    GB_CUDA(c, cudaFuncSetAttribute(peer_pull_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PULL_SMEM));
+    attr_set = true;
+  }
+  int sms = 148;
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device);
+  const size_t chunks = job.bytes / PULL_CHUNK * (size_t)job.n;
+  const unsigned grid = (unsigned)(chunks < (size_t)(2 * sms) ? chunks : (size_t)(2 * sms));
+  peer_pull_kernel<<<grid, 32, PULL_SMEM, st>>>(job);
+  GB_LAUNCH_CHECK(c, "peer_pull");
+  return GB_OK;
+}
+
 // Blocks (me, s), s != me, of two W x W block grids (same layout as shard_all_to_all) are copied from rank s's memory into
 // this rank's: after it this rank holds row `me` of both grids.  The caller has put a shard_barrier behind the producers.
 int shard_pull_blocks(gb_ctx* c, void* base, void* base2, size_t block_bytes, cudaStream_t st) {
@@ -264,16 +279,26 @@ int shard_pull_blocks(gb_ctx* c, void* base, void* base2, size_t block_bytes, cu
       ++job.n;
     }
   }
-  static bool attr_set = false;
-  if (!attr_set) {
-    GB_CUDA(c, cudaFuncSetAttribute(peer_pull_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PULL_SMEM));
-    attr_set = true;
+  return launch_pull(c, job, st);
+}
+
+// In-place all-gather by pulling: rank s's piece lies at base + s * piece_bytes in every rank's workspace.
+int shard_pull_gather(gb_ctx* c, void* base, size_t piece_bytes, cudaStream_t st) {
+  const int W = c->shard_world, me = c->shard_rank;
+  if (W <= 1) return GB_OK;
+  if (piece_bytes % PULL_CHUNK) return gb_fail(c, GB_ERR_INVALID, "shard_pull_gather: piece of %zu bytes", piece_bytes);
+  PullJob job;
+  job.n = 0;
+  job.bytes = piece_bytes;
+  const size_t off = (const char*)base - (const char*)c->ws_alloc;
+  for (int k = 1; k < W; ++k) {
+    const int peer = (me + k) % W;
+    if (!c->peer_ws[peer]) return gb_fail(c, GB_ERR_INVALID, "shard_pull_gather: peer workspaces are not mapped");
+    job.src[job.n] = (const char*)c->peer_ws[peer] + off + (size_t)peer * piece_bytes;
+    job.dst[job.n] = (char*)base + (size_t)peer * piece_bytes;
+    ++job.n;
   }
-  int sms = 148;
-  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device);
-  peer_pull_kernel<<<2 * sms, 32, PULL_SMEM, st>>>(job);
-  GB_LAUNCH_CHECK(c, "peer_pull");
-  return GB_OK;
+  return launch_pull(c, job, st);
 }
 
 int shard_barrier(gb_ctx* c, cudaStream_t st) {

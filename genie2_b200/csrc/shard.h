@@ -21,4 +21,6 @@ int shard_barrier(gb_ctx* c, cudaStream_t st);
 // Copy blocks (me, s), s != me, of one or two world x world block grids (layout of shard_all_to_all) out of rank s's
 // workspace into this rank's over NVLink (one kernel).  Put a shard_barrier between the producers and this.
 int shard_pull_blocks(gb_ctx* c, void* base, void* base2, size_t block_bytes, cudaStream_t st);
+// In-place all-gather by pulling (rank s's piece at base + s * piece_bytes of every rank's workspace); same rule.
+int shard_pull_gather(gb_ctx* c, void* base, size_t piece_bytes, cudaStream_t st);
 void shard_destroy(gb_ctx* c);

@@ -1136,22 +1136,28 @@ int tc_structure_net(gb_ctx* c, float* states_out, cudaStream_t st) {
       // MMA chain each; also a third of the accumulation length inside the tensor core); the partial sums land in sA / h1 / h2
       // and the LayerNorm kernel adds them, the bias and the residual in a fixed order
       const bool split3 = (IPA_CAT / 64) % 3 == 0, ks3 = W == 1 && split3;
+      float* ln_in = c->sA;
       if (W > 1) {
-        // this rank's query rows only, same split and same order of additions as on one GPU, then the rows are all-gathered
+        // this rank's query rows only, same split and same order of additions as on one GPU; then every rank pulls the other
+        // ranks' rows out of their memory (peer-mapped, shard.cu).  Two exchange buffers alternate from layer to layer: a
+        // rank rewrites its rows two layers later, after a barrier that every rank reaches only once its pull has finished.
+        float* X = c->sX[(blk * d.n_structure_layer + l) & 1];
+        ln_in = X;
         if (split3) {
-          if ((rc = gemm_img(c, st, s->cat_img, IPA_CAT, t.Wout, cs, nullptr, nullptr, 0, c->sA, cs, nullptr, false, 0, row0 / 128, rows / 128, false, 3, c->h1, c->h2))) return rc;
-          launch_pdl(sum_partials_kernel, (unsigned)((rows * (cs / 4) + 255) / 256), 256, 0, st, c->sA, (const float*)c->h1, (const float*)c->h2,
+          if ((rc = gemm_img(c, st, s->cat_img, IPA_CAT, t.Wout, cs, nullptr, nullptr, 0, X, cs, nullptr, false, 0, row0 / 128, rows / 128, false, 3, c->h1, c->h2))) return rc;
+          launch_pdl(sum_partials_kernel, (unsigned)((rows * (cs / 4) + 255) / 256), 256, 0, st, X, (const float*)c->h1, (const float*)c->h2,
                      (const float*)w.bout, (const float*)c->s, row0, rows, cs);
           GB_LAUNCH_CHECK(c, "sum_partials");
-        } else if ((rc = gemm_img(c, st, s->cat_img, IPA_CAT, t.Wout, cs, w.bout, c->s, cs, c->sA, cs, nullptr, false, 0, row0 / 128, rows / 128))) return rc;
-        if ((rc = shard_all_gather(c, c->sA, (size_t)rows * cs * sizeof(float), st))) return rc;
+        } else if ((rc = gemm_img(c, st, s->cat_img, IPA_CAT, t.Wout, cs, w.bout, c->s, cs, X, cs, nullptr, false, 0, row0 / 128, rows / 128))) return rc;
+        if ((rc = shard_barrier(c, st))) return rc;
+        if ((rc = shard_pull_gather(c, X, (size_t)rows * cs * sizeof(float), st))) return rc;
       }
       if (W == 1 && !ks3 && (rc = gemm_img(c, st, s->cat_img, IPA_CAT, t.Wout, cs, w.bout, c->s, cs, c->sA, cs, nullptr, false, 0, 0, 0, x3))) return rc;
       if (ks3) {
         if ((rc = gemm_img(c, st, s->cat_img, IPA_CAT, t.Wout, cs, nullptr, nullptr, 0, c->sA, cs, nullptr, false, 0, 0, 0, x3, 3, c->h1, c->h2))) return rc;
         launch_ln(c, st, c->sA, c->sB, nullptr, s->ln1_img, w.ln1_g, w.ln1_b, 1, nullptr, x3, c->h1, c->h2, w.bout, c->s);
       } else
-      launch_ln(c, st, c->sA, c->sB, nullptr, s->ln1_img, w.ln1_g, w.ln1_b, 1, nullptr, x3);
+      launch_ln(c, st, ln_in, c->sB, nullptr, s->ln1_img, w.ln1_g, w.ln1_b, 1, nullptr, x3);
       GB_LAUNCH_CHECK(c, "ipa_layer_norm");
       float* cur = c->sB;
       float* other = c->sA;

@@ -1,7 +1,7 @@
 """Row sharding of ONE long sample over the GPUs of a box (BASELINE config C5).
 
 No reference counterpart: the reference only farms whole samples (genie/utils/multiprocessor.py:73-100).
-Host-side logic only; the exchange itself is NCCL inside the CUDA library (csrc/shard.cu):
+Host-side logic only; the exchange itself happens inside the CUDA library (csrc/shard.cu):
 
 * ``row_range(N, world, rank)``    rows of the pair representation a rank owns;
 * ``check_shardable(B, N, world)`` the constraints of the kernels (one sample, whole 128-row blocks per rank);
@@ -10,9 +10,10 @@ Host-side logic only; the exchange itself is NCCL inside the CUDA library (csrc/
 * ``traffic_bytes(N, world, ...)`` bytes each rank receives per denoiser eval (for the bench line).
 
 Exchange pattern (round 2): the triangle contraction is sharded by CHANNEL (x^c = a^c b^cT is independent per channel):
-K4 on a rank's rows -> all-to-all of a and b to the owners of the 128 / world channel groups -> contraction of own channels
-over all rows -> all-to-all of x back to the row owners -> K6 on own rows.  3 (W - 1) / W^2 of an image per rank and update
-instead of the (W - 1) / W of round 1's all-gather of b.
+K4 on a rank's rows -> the owner of each 128 / world channel group pulls its blocks of a and b out of the producers' memory
+(peer-mapped over NVLink, device-side barrier first) -> contraction of own channels over all rows -> K6 on own rows fetches
+its x tiles from the channel owners.  3 (W - 1) / W^2 of an image per rank and update instead of the (W - 1) / W of
+round 1's all-gather of b; NCCL only carries the setup (unique id here, CUDA IPC handles inside the library).
 """
 import ctypes as C
 
@@ -39,9 +40,9 @@ def check_shardable(B, N, world):
 
 
 def traffic_bytes(N, world, n_pair_layer=5, n_struct_layer=8, c_p=128, c_s=384):
-    """Bytes RECEIVED per rank per denoiser eval.  Per triangle update three in-place all-to-alls (the bf16 a and b operand
-    images to the owners of the channel groups, the contraction result x back to the row owners): (world - 1) of the
-    world^2 blocks of an image each; per structure layer the all-gather of the fp32 single representation."""
+    """Bytes each rank reads from its peers per denoiser eval.  Per triangle update (world - 1) of the world^2 blocks of three
+    bf16 images (its channel group of a and b from the row owners, its rows of x from the channel owners); per structure
+    layer the other ranks' rows of the fp32 single representation."""
     if world == 1:
         return 0
     image = N * N * c_p * 2

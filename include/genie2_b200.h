@@ -167,13 +167,16 @@ int64_t gb_workspace_bytes(const gb_ctx* ctx);
  * (genie/utils/multiprocessor.py:73-100), and a length-1024 sample runs on a single device.
  * One process per GPU; every rank creates its own context on its own device, loads the same
  * weights, binds the same features and makes the same calls.  Rank r owns rows
- * [r N / world, (r+1) N / world) of the pair representation; gb_denoise all-gathers the triangle
- * operands (bf16) and the per-layer IPA result over NCCL on the caller's stream, and every rank
- * returns the full z.  The result is bit-identical to the single-GPU one.
+ * [r N / world, (r+1) N / world) of the pair representation and channels [r 128 / world, ...) of the
+ * triangle contraction; the ranks read each other's operand blocks and per-layer IPA rows straight
+ * from peer-mapped memory over NVLink (CUDA IPC, set up by gb_set_features; device-side barriers and
+ * copy kernels on the caller's stream; NCCL only carries the setup), and every rank returns the
+ * full z.  The result is bit-identical to the single-GPU one.
  *   gb_shard_unique_id: rank 0 fills 128 bytes (an ncclUniqueId) that the caller distributes
  *                       to the other ranks by any means (torch.distributed, a file, MPI).
  *   gb_shard_init:      collective; before gb_set_features.  world == 1 turns sharding off.
- * Requirements: bf16 precision, B == 1, N a multiple of 128 * world, no triangle attention.
+ * Requirements: bf16 precision, B == 1, N a multiple of 128 * world, world <= 8 GPUs of one box with
+ * peer access, no triangle attention; gb_set_features is collective on a sharded context.
  * libnccl.so.2 is resolved with dlopen on first use (GB_ERR_MISSING if absent). */
 int gb_shard_unique_id(void* out128);
 int gb_shard_init(gb_ctx* ctx, int world, int rank, const void* id128);

@@ -81,14 +81,14 @@ def main():
             dz = float((one['z'] - many['z']).abs().max())
             dp = float((one['p'] - many['p']).abs().max()) if with_p else float('nan')
             print('rank %d: MISMATCH max |dz| = %g, max |dp| = %g (pair stack)' % (rank, dz, dp), flush=True)
-    n_coll = model.collective_count()
+    n_coll, n_bar = model.collective_count(), model.peer_barrier_count()
     model.return_intermediates = False
     ms_many = timed(a.time) if a.time else None
     flag = torch.tensor([1 if ok else 0], device=dev)
     dist.all_reduce(flag, op=dist.ReduceOp.MIN)
     if rank == 0:
         line = {'workload': 'C5 row-sharded denoiser eval, L=%d B=1, bf16' % N, 'world': world, 'ok': bool(int(flag)),
-                'collectives_per_eval': n_coll, 'recv_bytes_per_rank_per_eval': shard.traffic_bytes(N, world),
+                'nccl_collectives_per_eval': n_coll, 'peer_barriers_per_eval': n_bar, 'recv_bytes_per_rank_per_eval': shard.traffic_bytes(N, world),
                 'ms_per_eval_one_gpu': ms_one, 'ms_per_eval_sharded': ms_many}
         print(json.dumps(line), flush=True)
         if a.out:
