@@ -24,6 +24,8 @@ def main():
     ap.add_argument('--check', action='store_true')
     ap.add_argument('--time', type=int, default=0)
     ap.add_argument('--out', default='')
+    ap.add_argument('--regrow', type=int, default=0, help='then run the SAME sharded model at this larger length (the workspace is '
+                    're-allocated and re-mapped between the ranks) and again at --length (re-carved in place)')
     a = ap.parse_args()
     import genie2_b200
     from genie2_b200 import shard
@@ -37,16 +39,19 @@ def main():
     shard.check_shardable(1, N, world)
     cfg = O.OracleConfig()
     sd = W.make_state_dict(cfg, 2, 'activated')
-    g = torch.Generator().manual_seed(4)
-    feats = O.make_features([[N]])
-    trans = torch.randn(1, N, 3, generator=g) * 12
-    rots = O.compute_frenet_frames(trans, feats['chain_index'], feats['residue_mask'])
     ts = torch.tensor([400], dtype=torch.int32, device=dev)
+
+    def inputs(n):
+        g = torch.Generator().manual_seed(4)
+        feats = O.make_features([[n]])
+        trans = torch.randn(1, n, 3, generator=g) * 12
+        rots = O.compute_frenet_frames(trans, feats['chain_index'], feats['residue_mask'])
+        return feats_to(feats, dev), genie2_b200.T(rots.to(dev), trans.to(dev))
+
     model = make_denoiser(cfg, sd, precision='bf16', device=dev)
     with_p = a.check and N <= 512
     model.return_intermediates = with_p
-    f = feats_to(feats, dev)
-    t = genie2_b200.T(rots.to(dev), trans.to(dev))
+    f, t = inputs(N)
 
     def timed(k):
         for _ in range(3):
@@ -82,6 +87,18 @@ def main():
             dp = float((one['p'] - many['p']).abs().max()) if with_p else float('nan')
             print('rank %d: MISMATCH max |dz| = %g, max |dp| = %g (pair stack)' % (rank, dz, dp), flush=True)
     n_coll, n_bar = model.collective_count(), model.peer_barrier_count()
+    if a.regrow:
+        # a larger sample on the same sharded context, then the first one again: same bits as fresh single-GPU runs
+        shard.check_shardable(1, a.regrow, world)
+        model.return_intermediates = False
+        f2, t2 = inputs(a.regrow)
+        big = model(t2, ts, f2)['z'].clone()
+        again = model(t, ts, f)['z'].clone()
+        fresh = make_denoiser(cfg, sd, precision='bf16', device=dev)
+        ok = ok and torch.equal(again, one['z']) and torch.equal(big, fresh(t2, ts, f2)['z'])
+        del fresh
+        if not ok:
+            print('rank %d: MISMATCH after re-growing the workspace' % rank, flush=True)
     model.return_intermediates = False
     ms_many = timed(a.time) if a.time else None
     flag = torch.tensor([1 if ok else 0], device=dev)
