@@ -44,6 +44,42 @@ extern "C" int gb_version(void) { return GB_VERSION; }
 extern "C" const char* gb_last_error(const gb_ctx* ctx) { return ctx ? ctx->err.c_str() : g_create_err.c_str(); }
 extern "C" int64_t gb_launch_count(const gb_ctx* ctx) { return ctx ? ctx->launches : 0; }
 extern "C" int64_t gb_workspace_bytes(const gb_ctx* ctx) { return ctx ? (int64_t)ctx->ws_bytes : 0; }
+namespace {
+struct PhaseMarks {
+  bool on = false;
+  std::vector<std::pair<const char*, cudaEvent_t>> marks;
+  PhaseMarks() { const char* e = getenv("GB_PHASE_TIMING"); on = e && e[0] == '1'; }
+} g_phases;
+}  // namespace
+
+void ph_mark(cudaStream_t st, const char* name) {
+  if (!g_phases.on) return;
+  cudaEvent_t ev;
+  if (cudaEventCreate(&ev) != cudaSuccess) return;
+  cudaEventRecord(ev, st);
+  g_phases.marks.emplace_back(name, ev);
+}
+
+void ph_report(const gb_ctx* ctx, cudaStream_t st) {
+  if (!g_phases.on) return;
+  ph_mark(st, "end");
+  cudaStreamSynchronize(st);
+  std::vector<std::pair<std::string, std::pair<float, int>>> rows;
+  float total = 0.f;
+  for (size_t i = 0; i + 1 < g_phases.marks.size(); ++i) {
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, g_phases.marks[i].second, g_phases.marks[i + 1].second);
+    total += ms;
+    bool found = false;
+    for (auto& r : rows) if (r.first == g_phases.marks[i].first) { r.second.first += ms; r.second.second++; found = true; break; }
+    if (!found) rows.push_back({g_phases.marks[i].first, {ms, 1}});
+  }
+  fprintf(stderr, "[gb phases] rank %d of %d, N = %d: %.3f ms\n", ctx->shard_rank, ctx->shard_world, ctx->N, total);
+  for (auto& r : rows) fprintf(stderr, "[gb phases]   %-16s %8.3f ms  x%d\n", r.first.c_str(), r.second.first, r.second.second);
+  for (auto& m : g_phases.marks) cudaEventDestroy(m.second);
+  g_phases.marks.clear();
+}
+
 extern "C" int64_t gb_collective_count(const gb_ctx* ctx) { return ctx ? ctx->collectives : 0; }
 extern "C" int64_t gb_peer_barrier_count(const gb_ctx* ctx) { return ctx ? ctx->peer_barriers : 0; }
 
@@ -734,6 +770,7 @@ extern "C" int gb_denoise(gb_ctx* c, const float* rots, const float* trans, cons
   const gb_dims& d = c->d;
   const int B = c->B, N = c->N, R = B * N, cs = d.c_s;
   const size_t Rcs = (size_t)R * cs;
+  ph_mark(st, "embed");
   init_frames_kernel<<<(R * 9 + 255) / 256, 256, 0, st>>>(rots, trans, c->rots_w, c->trans_w, d.rescale, R);
   GB_LAUNCH_CHECK(c, "init_frames");
   // SingleFeatureNet
@@ -779,8 +816,10 @@ extern "C" int gb_denoise(gb_ctx* c, const float* rots, const float* trans, cons
       if ((rc = run_triatt(c, c->pair[l].att_start, true, c->p, st))) return rc;
       if ((rc = run_triatt(c, c->pair[l].att_end, false, c->p, st))) return rc;
     }
+    ph_mark(st, "K7 transition");
     if ((rc = run_transition(c, c->pair[l].tr, c->p, st))) return rc;
   }
+  ph_mark(st, "barrier");
   // row-sharded: no rank leaves the pair stack while a peer's last K6 may still be reading its x (its memory stays valid for
   // the peers for as long as work of this eval is in flight anywhere)
   if (W > 1 && d.include_mul_update && (rc = shard_barrier(c, st))) return rc;
@@ -822,6 +861,7 @@ extern "C" int gb_denoise(gb_ctx* c, const float* rots, const float* trans, cons
   finish_kernel<<<(R * 9 + 255) / 256, 256, 0, st>>>(trans, c->trans_w, c->rots_w, z_out, aux ? aux->out_trans : nullptr,
                                                      aux ? aux->out_rots : nullptr, 1.f / d.rescale, R);
   GB_LAUNCH_CHECK(c, "finish");
+  ph_report(c, st);
   return GB_OK;
 }
 

@@ -124,6 +124,11 @@ struct gb_ctx {
   float* static_scratch = nullptr;
 };
 
+// GB_PHASE_TIMING=1: gb_denoise prints, per call, the device time between consecutive marks summed by name (stderr; the
+// eval is synchronised for it -- a diagnosis switch, not a mode).  ph_mark closes the running phase and opens `name`.
+void ph_mark(cudaStream_t st, const char* name);
+void ph_report(const gb_ctx* ctx, cudaStream_t st);
+
 // set ctx->err (printf style) and return code
 int gb_fail(const gb_ctx* ctx, int code, const char* fmt, ...);
 

@@ -946,14 +946,18 @@ int tc_trimul_stage(gb_ctx* c, const TriMulW& w, bool outgoing, int stage, float
   }
   int rc;
   if (stage == 0 || stage == 1) {
+    ph_mark(st, "K4 proj");
     rc = x3 ? tc_launch_trimul_proj_x3(c, w, outgoing, p, st) : tc_launch_trimul_proj(c, w, outgoing, p, st);
     if (rc != GB_OK) return rc;
     if (W > 1) {
+      ph_mark(st, "barrier");
       if ((rc = shard_barrier(c, st)) != GB_OK) return rc;                 // operands ready on every rank
+      ph_mark(st, "pull a, b");
       if ((rc = shard_pull_blocks(c, s->a, s->b, Lab.blk * 2, st)) != GB_OK) return rc;
     }
   }
   if (stage == 0 || stage == 2) {
+    ph_mark(st, "K5 contract");
     const int NJ = 256;
     const int nib = (Np + 127) / 128, ib0 = 0;
     const int nchs = 128 / W, ch0 = W > 1 ? c->shard_rank * nchs : 0;     // sharded: this rank's channel group, every row block
@@ -966,9 +970,11 @@ int tc_trimul_stage(gb_ctx* c, const TriMulW& w, bool outgoing, int stage, float
     } else
     launch_pdl_cls(2, trimul_contract_tc_kernel, cgrid, 256, K5_SMEM, st, s->a, s->b, s->x, N, Np, NJ, Lab, Lab, ib0, nib, ch0, nchs, Lx);
     GB_LAUNCH_CHECK(c, "trimul_contract_tc");
+    if (W > 1) ph_mark(st, "barrier");
     if (W > 1 && (rc = shard_barrier(c, st)) != GB_OK) return rc;        // x ready on every rank
   }
   if (stage == 0 || stage == 3) {
+    ph_mark(st, "K6 out");
     TileRange tr = full_tile_range(N, Np);
     if (W > 1) { tr.nt2 = (uint32_t)(N / W) >> 1; tr.t2_0 = c->shard_rank * tr.nt2; }
     const unsigned tiles = (unsigned)B * tr.nt2 * tr.njb;

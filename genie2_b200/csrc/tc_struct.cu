@@ -1100,6 +1100,7 @@ int tc_structure_net(gb_ctx* c, float* states_out, cudaStream_t st) {
   TileRange tr = full_tile_range(N, Np);
   if (W > 1) { tr.nt2 = (uint32_t)rows >> 1; tr.t2_0 = (uint32_t)row0 >> 1; }
   const unsigned ptiles = (unsigned)B * tr.nt2 * tr.njb;
+  ph_mark(st, "ipa_prep");
   if (x3) launch_pdl_cls(5, ipa_prep_tc_kernel<2>, ptiles, 256, PrepSmem<2>::TOTAL, st, (const float*)c->p, B, N, Np, (const bf16*)s->Wb_img,
                          (const float*)s->bias96, s->pbias, s->z_img, d.n_structure_layer * IPA_H, tr, s->img_lo);
   else launch_pdl_cls(5, ipa_prep_tc_kernel<1>, ptiles, 256, PrepSmem<1>::TOTAL, st, (const float*)c->p, B, N, Np, (const bf16*)s->Wb_img,
@@ -1115,9 +1116,11 @@ int tc_structure_net(gb_ctx* c, float* states_out, cudaStream_t st) {
     for (int l = 0; l < d.n_structure_layer; ++l) {
       const StructLayerW& w = c->st[l];
       const TcStructW& t = s->st[l];
+      ph_mark(st, "qkv + points");
       if ((rc = gemm_img(c, st, s->s_img, cs, t.Wqkv, IPA_QKV, t.bqkv, nullptr, 0, c->qkv, IPA_QKV, nullptr, false, N, 0, 0, x3))) return rc;
       launch_pdl(ipa_points_planes_kernel, (R * IPA_H + 255) / 256, 256, 0, st, c->qkv, c->rots_w, c->trans_w, R, N);
       GB_LAUNCH_CHECK(c, "ipa_points_planes");
+      ph_mark(st, "ipa_attention");
       {
         const int nq = W > 1 ? rows : N, G = ia_queries_per_cta(Np, B, nq, s->num_sms, x3 ? 2 : 1);
         const dim3 grid((nq + G - 1) / G, B);
@@ -1132,6 +1135,7 @@ int tc_structure_net(gb_ctx* c, float* states_out, cudaStream_t st) {
 #undef IA_LAUNCH
       }
       GB_LAUNCH_CHECK(c, "ipa_attention_tc");
+      ph_mark(st, "out_proj");
       // output projection, K = 2112 = 33 k-blocks: split three ways over grid.z (144 CTAs instead of 48, a third of the serial
       // MMA chain each; also a third of the accumulation length inside the tensor core); the partial sums land in sA / h1 / h2
       // and the LayerNorm kernel adds them, the bias and the residual in a fixed order
@@ -1149,8 +1153,11 @@ int tc_structure_net(gb_ctx* c, float* states_out, cudaStream_t st) {
                      (const float*)w.bout, (const float*)c->s, row0, rows, cs);
           GB_LAUNCH_CHECK(c, "sum_partials");
         } else if ((rc = gemm_img(c, st, s->cat_img, IPA_CAT, t.Wout, cs, w.bout, c->s, cs, X, cs, nullptr, false, 0, row0 / 128, rows / 128))) return rc;
+        ph_mark(st, "barrier");
         if ((rc = shard_barrier(c, st))) return rc;
+        ph_mark(st, "pull rows");
         if ((rc = shard_pull_gather(c, X, (size_t)rows * cs * sizeof(float), st))) return rc;
+        ph_mark(st, "out_proj");
       }
       if (W == 1 && !ks3 && (rc = gemm_img(c, st, s->cat_img, IPA_CAT, t.Wout, cs, w.bout, c->s, cs, c->sA, cs, nullptr, false, 0, 0, 0, x3))) return rc;
       if (ks3) {
@@ -1159,6 +1166,7 @@ int tc_structure_net(gb_ctx* c, float* states_out, cudaStream_t st) {
       } else
       launch_ln(c, st, ln_in, c->sB, nullptr, s->ln1_img, w.ln1_g, w.ln1_b, 1, nullptr, x3);
       GB_LAUNCH_CHECK(c, "ipa_layer_norm");
+      ph_mark(st, "transition + bb");
       float* cur = c->sB;
       float* other = c->sA;
       for (int tl = 0; tl < d.n_structure_transition_layer; ++tl) {
