@@ -42,10 +42,6 @@ struct NcclApi {
   ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
   ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
   ncclResult_t (*AllGather)(const void*, void*, size_t, int, ncclComm_t, cudaStream_t) = nullptr;
-  ncclResult_t (*Send)(const void*, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
-  ncclResult_t (*Recv)(void*, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
-  ncclResult_t (*GroupStart)() = nullptr;
-  ncclResult_t (*GroupEnd)() = nullptr;
   const char* (*GetErrorString)(ncclResult_t) = nullptr;
   ncclResult_t (*GetVersion)(int*) = nullptr;
 };
@@ -63,14 +59,9 @@ const char* load_nccl() {
   a.CommInitRank = (decltype(a.CommInitRank))dlsym(h, "ncclCommInitRank");
   a.CommDestroy = (decltype(a.CommDestroy))dlsym(h, "ncclCommDestroy");
   a.AllGather = (decltype(a.AllGather))dlsym(h, "ncclAllGather");
-  a.Send = (decltype(a.Send))dlsym(h, "ncclSend");
-  a.Recv = (decltype(a.Recv))dlsym(h, "ncclRecv");
-  a.GroupStart = (decltype(a.GroupStart))dlsym(h, "ncclGroupStart");
-  a.GroupEnd = (decltype(a.GroupEnd))dlsym(h, "ncclGroupEnd");
   a.GetErrorString = (decltype(a.GetErrorString))dlsym(h, "ncclGetErrorString");
   a.GetVersion = (decltype(a.GetVersion))dlsym(h, "ncclGetVersion");
-  if (!a.GetUniqueId || !a.CommInitRank || !a.CommDestroy || !a.AllGather || !a.GetErrorString || !a.Send || !a.Recv || !a.GroupStart ||
-      !a.GroupEnd) return "libnccl: missing symbols";
+  if (!a.GetUniqueId || !a.CommInitRank || !a.CommDestroy || !a.AllGather || !a.GetErrorString) return "libnccl: missing symbols";
   g_nccl = a;
   return nullptr;
 }
@@ -135,8 +126,8 @@ __global__ void peer_barrier_kernel(gb_peer_flags pf, int W, int me) {
 }
 
 // Pull n blocks of `bytes` each out of peer memory into local memory: peer -> shared -> local, bulk copies both ways, one
-// issuing thread per CTA, PULL_STAGES chunks of PULL_CHUNK bytes in flight per CTA (148 x 5 x 16 KB = 12 MB in flight against
-// the ~2 MB that NVLink's bandwidth-delay product asks for).  Chunks are dealt round-robin over the blocks so that every
+// issuing thread per CTA, a ring of PULL_STAGES chunks of PULL_CHUNK bytes per CTA with the loads four chunks ahead (296 CTAs x
+// 64 KB = 19 MB in flight against the ~2 MB that NVLink's bandwidth-delay product asks for).  Chunks are dealt round-robin over the blocks so that every
 // peer link is busy from the start.
 constexpr uint32_t PULL_CHUNK = 16384, PULL_STAGES = 6;
 constexpr size_t PULL_SMEM = PULL_STAGES * PULL_CHUNK + 1024 + 128;
@@ -259,7 +250,8 @@ static int launch_pull(gb_ctx* c, const PullJob& job, cudaStream_t st) {
   return GB_OK;
 }
 
-// Blocks (me, s), s != me, of two W x W block grids (same layout as shard_all_to_all) are copied from rank s's memory into
+// Blocks (me, s), s != me, of two W x W grids of blocks (block (d, s) at base + (d * W + s) * block_bytes, written by rank s,
+// wanted by rank d) are copied from rank s's memory into
 // this rank's: after it this rank holds row `me` of both grids.  The caller has put a shard_barrier behind the producers.
 int shard_pull_blocks(gb_ctx* c, void* base, void* base2, size_t block_bytes, cudaStream_t st) {
   const int W = c->shard_world, me = c->shard_rank;
@@ -333,29 +325,6 @@ int shard_all_gather(gb_ctx* c, void* base, size_t piece_bytes, cudaStream_t st)
   const ncclResult_t r = g_nccl.AllGather((const char*)base + (size_t)c->shard_rank * piece_bytes, base, piece_bytes, ncclUint8,
                                           (ncclComm_t)c->shard_comm, st);
   if (r != 0) return gb_fail(c, GB_ERR_CUDA, "ncclAllGather: %s", g_nccl.GetErrorString(r));
-  c->collectives++;
-  return GB_OK;
-}
-
-int shard_all_to_all(gb_ctx* c, void* base, size_t block_bytes, cudaStream_t st, void* base2) {
-  const int W = c->shard_world, me = c->shard_rank;
-  if (W <= 1) return GB_OK;
-  if (!c->shard_comm) return gb_fail(c, GB_ERR_INVALID, "shard_all_to_all: no communicator");
-  ncclComm_t comm = (ncclComm_t)c->shard_comm;
-  char* bases[2] = {(char*)base, (char*)base2};
-  ncclResult_t r = g_nccl.GroupStart();
-  for (int i = 0; i < 2; ++i) {
-    char* b = bases[i];
-    if (!b) continue;
-    for (int peer = 0; peer < W && r == 0; ++peer) {
-      if (peer == me) continue;
-      r = g_nccl.Send(b + ((size_t)peer * W + me) * block_bytes, block_bytes, ncclUint8, peer, comm, st);
-      if (r == 0) r = g_nccl.Recv(b + ((size_t)me * W + peer) * block_bytes, block_bytes, ncclUint8, peer, comm, st);
-    }
-  }
-  const ncclResult_t e = g_nccl.GroupEnd();
-  if (r == 0) r = e;
-  if (r != 0) return gb_fail(c, GB_ERR_CUDA, "all-to-all (ncclSend / ncclRecv): %s", g_nccl.GetErrorString(r));
   c->collectives++;
   return GB_OK;
 }
