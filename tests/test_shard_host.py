@@ -53,8 +53,8 @@ def x_off(Np, B, world, b, i, jb64, ch):
 @pytest.mark.parametrize('mode', ['rows', 'kblocks'])
 def test_image_layout_is_a_block_grid_by_channel_group_and_producer(world, mode):
     """Both operand images of a sharded triangle update: the producer (rank s: its rows for the outgoing update, its k-blocks
-    for the incoming one) writes block (d, s) for every channel group d; block (d, s) is contiguous, so the in-place all-to-all
-    of csrc/shard.cu (block (d, s) travels from rank s to rank d) needs no packing; afterwards rank d reads blocks (d, *) only."""
+    for the incoming one) writes block (d, s) for every channel group d; block (d, s) is contiguous, so the pull of csrc/shard.cu
+    (rank d copies block (d, s) out of rank s's memory) needs no packing; afterwards rank d reads blocks (d, *) only."""
     Np, B = 128 * world, 1
     rs, ks = (world, 1) if mode == 'rows' else (1, world)
     CG = 128 // world
@@ -82,8 +82,8 @@ def test_image_layout_is_a_block_grid_by_channel_group_and_producer(world, mode)
 
 @pytest.mark.parametrize('world', [2, 4, 8])
 def test_x_layout_returns_blocks_to_the_row_owners(world):
-    """Contraction result: rank d (channel group d) writes block (s, d) for every row block s; the all-to-all returns block
-    (s, d) to rank s, which reads its tiles as world x 2 contiguous pieces of CG x 128 bytes."""
+    """Contraction result: rank d (channel group d) writes block (s, d) for every row block s in its own memory; rank s fetches
+    its tiles from there as world x 2 contiguous pieces of CG x 128 bytes."""
     Np, B = 128 * world, 1
     CG = 128 // world
     total = B * Np * (Np // 64) * 128 * 64
@@ -100,6 +100,58 @@ def test_x_layout_returns_blocks_to_the_row_owners(world):
             assert x_off(Np, B, world, 0, i, jb, 2 * CG - 1) == a + (CG - 1) * 64 if world > 1 else True
     assert seen.max() == 1
     assert x_off(256, 1, 1, 0, 5, 2, 77) == ((((5 // 2) * 4 + 2) * 2 + 1) * 128 + 77) * 64      # one GPU: the tile images
+
+
+def pull_pairs(world, me, block):
+    """Python restatement of shard_pull_blocks (csrc/shard.cu): (peer, offset) of every block this rank copies out of a peer's
+    buffer into the same offset of its own: blocks (me, s), s != me, of the world x world grid, starting on another peer per rank."""
+    return [((me + k) % world, (me * world + (me + k) % world) * block) for k in range(1, world)]
+
+
+@pytest.mark.parametrize('world', [2, 4])
+@pytest.mark.parametrize('mode', ['rows', 'kblocks'])
+def test_exchange_model_every_rank_ends_up_with_what_its_kernels_read(world, mode):
+    """The whole exchange of one triangle update on `world` model ranks with separate buffers (one 64-element row = one number):
+    K4 writes its blocks locally, every rank pulls blocks (me, s), K5 finds ITS channels for all rows and all k, writes x blocks
+    (s, me) locally, and K6 finds every piece of its rows in the memory of the channel's owner."""
+    Np, B, CG = 128 * world, 1, 128 // world
+    njb, rs, ks = Np // 64, *((world, 1) if mode == 'rows' else (1, world))
+    rows64 = B * 128 * njb * Np                       # rows of 64 elements in an image
+    blk = rows64 // (world * world)
+    value = lambda ch, kb, row: (ch * njb + kb) * Np + row + 1
+    a = [np.zeros(rows64, dtype=np.int64) for _ in range(world)]
+    for me in range(world):                           # K4: own rows (outgoing) or own k-blocks (incoming), all channels
+        rows = range(me * Np // world, (me + 1) * Np // world) if mode == 'rows' else range(Np)
+        kbs = range(njb) if mode == 'rows' else range(me * njb // world, (me + 1) * njb // world)
+        for ch in range(0, 128, 3):
+            for kb in kbs:
+                for row in rows:
+                    a[me][img_off(Np, B, rs, ks, 0, ch, kb, row, world) // 64] = value(ch, kb, row)
+    snap = [v.copy() for v in a]                      # the pull reads what the producers wrote, not what other pulls wrote
+    for me in range(world):
+        for peer, off in pull_pairs(world, me, blk):
+            a[me][off:off + blk] = snap[peer][off:off + blk]
+    for me in range(world):                           # K5: this rank's channel group, every k-block, every row
+        for ch in range(me * CG, (me + 1) * CG):
+            if ch % 3:
+                continue
+            for kb in range(njb):
+                for row in range(0, Np, 5):
+                    assert a[me][img_off(Np, B, rs, ks, 0, ch, kb, row, world) // 64] == value(ch, kb, row)
+    xrows = B * Np * njb * 128
+    xv = lambda i, jb, ch: (i * njb + jb) * 128 + ch + 1
+    x = [np.zeros(xrows, dtype=np.int64) for _ in range(world)]
+    for me in range(world):                           # K5 epilogue: own channels, all rows, into its own memory
+        for ch in range(me * CG, (me + 1) * CG):
+            for i in range(Np):
+                for jb in range(njb):
+                    x[me][x_off(Np, B, world, 0, i, jb, ch) // 64] = xv(i, jb, ch)
+    for me in range(world):                           # K6: own rows; the piece of channel group cg lies in rank cg's memory
+        for i in range(me * Np // world, (me + 1) * Np // world, 3):
+            for jb in range(njb):
+                for cg in range(world):
+                    base = x_off(Np, B, world, 0, i, jb, cg * CG) // 64
+                    assert list(x[cg][base:base + CG]) == [xv(i, jb, cg * CG + c) for c in range(CG)]
 
 
 def _free_port():
