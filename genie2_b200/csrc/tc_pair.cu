@@ -443,10 +443,18 @@ __global__ void __launch_bounds__(256, 3) trimul_out_tc_kernel(
     // one 32 KB tile; channel-sharded runs fetch it as W x 2 pieces [i & 1][CG channels][64], each from the rank that
     // contracted that channel group (peer memory over NVLink)
     if (Lx.W == 1) bulk_g2s(X, px.p[0] + x_off(Lx, T.b, 2 * T.t2, T.jb, 0), 32768, bar_w);
-    else
-      for (uint32_t cg = 0; cg < Lx.W; ++cg)
+    else {
+      // the W - 1 remote pieces first, starting on another owner per rank and per tile (the requests of all ranks spread over
+      // all memories instead of arriving at rank 0 first), the local piece last
+      const uint32_t me = (2u * T.t2) / Lx.RL;
+      for (uint32_t k = 0; k + 1u < Lx.W; ++k) {
+        const uint32_t cg = (me + 1u + (k + blockIdx.x) % (Lx.W - 1u)) % Lx.W;
         for (uint32_t ii = 0; ii < 2; ++ii)
           bulk_g2s(X + ii * 16384u + cg * Lx.CG * 128u, px.p[cg] + x_off(Lx, T.b, 2 * T.t2 + ii, T.jb, cg * Lx.CG), Lx.CG * 128u, bar_w);
+      }
+      for (uint32_t ii = 0; ii < 2; ++ii)
+        bulk_g2s(X + ii * 16384u + me * Lx.CG * 128u, px.p[me] + x_off(Lx, T.b, 2 * T.t2 + ii, T.jb, me * Lx.CG), Lx.CG * 128u, bar_w);
+    }
   }
   if (tid == 0) {
     mbar_wait(bar_w, 0);
