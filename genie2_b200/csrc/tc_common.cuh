@@ -355,6 +355,14 @@ __device__ __forceinline__ size_t img_off(const ImgLayout& L, uint32_t b, uint32
 // Row-sharded runs read blocks other ranks produced straight from those ranks' memory (peer-mapped over NVLink, shard.cu):
 // p[r] = rank r's copy of the buffer; one GPU: p[0].
 struct PeerImg { const __nv_bfloat16* p[8]; };
+// p[r] with r known only at run time, through static indices: indexing the kernel parameter dynamically makes the compiler
+// copy the array to local memory at kernel entry, for every thread
+__device__ __forceinline__ const __nv_bfloat16* peer_ptr(const PeerImg& im, uint32_t r) {
+  const __nv_bfloat16* q = im.p[0];
+#pragma unroll
+  for (uint32_t k = 1; k < 8; ++k) q = (r == k) ? im.p[k] : q;
+  return q;
+}
 
 // Addressing of the contraction result x (elements of the 128-byte row of 64 columns j of channel ch, image row i, column
 // block jb64).  One GPU: pixel-tile images [b][i / 2][jb64][i & 1][128 ch][64] (the 32 KB of one tile are K6's MN-major A

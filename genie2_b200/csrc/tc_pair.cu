@@ -450,10 +450,10 @@ __global__ void __launch_bounds__(256, 3) trimul_out_tc_kernel(
       for (uint32_t k = 0; k + 1u < Lx.W; ++k) {
         const uint32_t cg = (me + 1u + (k + blockIdx.x) % (Lx.W - 1u)) % Lx.W;
         for (uint32_t ii = 0; ii < 2; ++ii)
-          bulk_g2s(X + ii * 16384u + cg * Lx.CG * 128u, px.p[cg] + x_off(Lx, T.b, 2 * T.t2 + ii, T.jb, cg * Lx.CG), Lx.CG * 128u, bar_w);
+          bulk_g2s(X + ii * 16384u + cg * Lx.CG * 128u, peer_ptr(px, cg) + x_off(Lx, T.b, 2 * T.t2 + ii, T.jb, cg * Lx.CG), Lx.CG * 128u, bar_w);
       }
       for (uint32_t ii = 0; ii < 2; ++ii)
-        bulk_g2s(X + ii * 16384u + me * Lx.CG * 128u, px.p[me] + x_off(Lx, T.b, 2 * T.t2 + ii, T.jb, me * Lx.CG), Lx.CG * 128u, bar_w);
+        bulk_g2s(X + ii * 16384u + me * Lx.CG * 128u, peer_ptr(px, me) + x_off(Lx, T.b, 2 * T.t2 + ii, T.jb, me * Lx.CG), Lx.CG * 128u, bar_w);
     }
   }
   if (tid == 0) {
